@@ -1,0 +1,359 @@
+/*
+ * zangcu.h — C ABI of the B200-native batch synthesis engine behind zang's module contract.
+ *
+ * The reference (dbandstra/zang) has no FFI; its boundary is the comptime module contract
+ *   paint(self, span, outputs, temps, note_id_changed, params)            (src/modules/SineOsc.zig:24-31)
+ * applied to ONE voice and ONE span at a time.  This ABI is the batched form of that contract:
+ *
+ *   voice  -> a column of a [frame][voice] f32 device buffer (voice is the fastest axis)
+ *   self   -> row v of a "bank" (one POD state struct per voice, same fields as the Zig struct)
+ *   span + note_id_changed + params -> one zcu_span record per reference paint() call of that voice;
+ *            `param` indexes a caller-supplied array of the module's Params struct
+ *   outputs/temps -> zcu_buf handles; every paint ACCUMULATES (+=) exactly like the reference
+ *
+ * One call paints every span of every voice for a whole block of mix buffers.  All calls are
+ * asynchronous on the context's CUDA stream, return an int error code (0 = ok) and never abort.
+ * There is NO CPU fallback: without a CUDA device every entry point that would compute returns
+ * ZCU_ERR_NO_DEVICE.
+ *
+ * Plain C types only (pointers, sizes, PODs); usable from Zig via @cImport, from Python via ctypes.
+ */
+#ifndef ZANGCU_H
+#define ZANGCU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZCU_ABI_VERSION 1
+
+/* ---- error codes ------------------------------------------------------------------------- */
+enum {
+    ZCU_OK = 0,
+    ZCU_ERR_INVALID = 1,     /* bad argument (null handle, size mismatch, unknown enum) */
+    ZCU_ERR_NO_DEVICE = 2,   /* no CUDA device / driver: there is no CPU fallback */
+    ZCU_ERR_CUDA = 3,        /* a CUDA runtime call failed; see zcu_last_error() */
+    ZCU_ERR_OOM = 4,
+    ZCU_ERR_UNSUPPORTED = 5,
+    ZCU_ERR_NCCL = 6
+};
+
+/* ---- module kinds (src/modules.zig:1-13) -------------------------------------------------- */
+enum {
+    ZCU_MOD_SINE_OSC = 0,    /* src/modules/SineOsc.zig */
+    ZCU_MOD_PULSE_OSC = 1,   /* src/modules/PulseOsc.zig */
+    ZCU_MOD_TRISAW_OSC = 2,  /* src/modules/TriSawOsc.zig */
+    ZCU_MOD_NOISE = 3,       /* src/modules/Noise.zig */
+    ZCU_MOD_ENVELOPE = 4,    /* src/modules/Envelope.zig */
+    ZCU_MOD_GATE = 5,        /* src/modules/Gate.zig */
+    ZCU_MOD_FILTER = 6,      /* src/modules/Filter.zig */
+    ZCU_MOD_PORTAMENTO = 7,  /* src/modules/Portamento.zig */
+    ZCU_MOD_CURVE = 8,       /* src/modules/Curve.zig */
+    ZCU_MOD_SAMPLER = 9,     /* src/modules/Sampler.zig */
+    ZCU_MOD_DECIMATOR = 10,  /* src/modules/Decimator.zig */
+    ZCU_MOD_DISTORTION = 11, /* src/modules/Distortion.zig */
+    ZCU_MOD_CYCLE = 12,      /* src/modules/Cycle.zig */
+    ZCU_MOD_COUNT = 13
+};
+
+/* ---- opaque handles ----------------------------------------------------------------------- */
+typedef struct zcu_ctx zcu_ctx;       /* device + stream (+ optional NCCL communicator) */
+typedef struct zcu_buf zcu_buf;       /* [frames][voices] f32 device buffer */
+typedef struct zcu_bank zcu_bank;     /* per-voice module state, one struct per voice */
+typedef struct zcu_spans zcu_spans;   /* device span table of one block */
+typedef struct zcu_sample zcu_sample; /* PCM sample data for the Sampler (Sampler.zig:16-21) */
+
+/* ---- span record: one reference paint() call of one voice ---------------------------------- */
+/* zang.Span (src/zang/basics.zig:3-10) + note_id_changed + params of Trigger.NewPaintReturnValue
+ * (src/zang/trigger.zig:50-54).  start/end are frame indices inside the block's device buffers;
+ * a span never crosses a mix-buffer boundary because the reference paints buffer by buffer. */
+typedef struct zcu_span {
+    uint32_t start;
+    uint32_t end;   /* exclusive; start < end */
+    uint32_t flags; /* ZCU_SPAN_* */
+    uint32_t param; /* row of the params array passed to the paint call */
+} zcu_span;
+#define ZCU_SPAN_NOTE_ID_CHANGED 1u
+
+/* ---- per-voice state PODs (field-for-field the Zig structs; also the checkpoint format) ---- */
+typedef struct { float t; } zcu_sine_state;                     /* SineOsc.zig:16 */
+typedef struct { uint32_t cnt; } zcu_pulse_state;               /* PulseOsc.zig:36 */
+typedef struct { uint32_t cnt; float t; } zcu_trisaw_state;     /* TriSawOsc.zig:36-37 */
+typedef struct { uint64_t s[4]; } zcu_noise_state;              /* Noise.zig:22 (b[7] never persists, Noise.zig:68) */
+typedef struct { float t, last_value, start; } zcu_painter_state; /* painter.zig:33-36 */
+typedef struct { int32_t state; zcu_painter_state painter; } zcu_envelope_state; /* Envelope.zig:15-24 */
+typedef struct { float l, b; } zcu_filter_state;                /* Filter.zig:34-35 */
+typedef struct { zcu_painter_state painter; } zcu_portamento_state; /* Portamento.zig:13 */
+typedef struct {                                                /* Curve.zig:36-41 */
+    float t;
+    uint32_t current_song_note;
+    int32_t current_song_note_offset;
+    uint32_t next_song_note;
+} zcu_curve_state;
+typedef struct { float t; } zcu_sampler_state;                  /* Sampler.zig:69 */
+typedef struct { float dval, dcount; } zcu_decimator_state;     /* Decimator.zig:11-12 */
+typedef struct { float t; } zcu_cycle_state;                    /* Cycle.zig:14 */
+
+enum { ZCU_ENV_IDLE = 0, ZCU_ENV_ATTACK = 1, ZCU_ENV_DECAY = 2, ZCU_ENV_SUSTAIN = 3, ZCU_ENV_RELEASE = 4 };
+
+/* ---- Params PODs (one row per distinct params value; spans refer to rows) ------------------ */
+/* ConstantOrBuffer (src/zang/constant_or_buffer.zig:4-7): the scalar lives in the params row and is
+ * used when the corresponding buffer argument of the paint call is NULL (.constant); a non-NULL
+ * zcu_buf selects the .buffer variant for every span of the call. */
+enum { ZCU_CURVE_INSTANTANEOUS = 0, ZCU_CURVE_LINEAR = 1, ZCU_CURVE_SQUARED = 2, ZCU_CURVE_CUBED = 3 };
+typedef struct { int32_t kind; float duration; } zcu_painter_curve;       /* painter.zig:25-30 */
+
+typedef struct { float sample_rate, freq, phase; } zcu_sine_params;     /* SineOsc.zig:10-14 */
+typedef struct { float sample_rate, freq, color; } zcu_pulse_params;    /* PulseOsc.zig:30-34 */
+typedef zcu_pulse_params zcu_trisaw_params;                             /* TriSawOsc.zig:30-34 */
+enum { ZCU_NOISE_WHITE = 0, ZCU_NOISE_PINK = 1 };
+typedef struct { int32_t color; } zcu_noise_params;                     /* Noise.zig:18-20 */
+typedef struct {                                                        /* Envelope.zig:6-13 */
+    float sample_rate;
+    zcu_painter_curve attack, decay, release;
+    float sustain_volume;
+    int32_t note_on;
+} zcu_envelope_params;
+typedef struct { int32_t note_on; } zcu_gate_params;                    /* Gate.zig:7-9 */
+enum { ZCU_FILTER_BYPASS = 0, ZCU_FILTER_LOW_PASS = 1, ZCU_FILTER_BAND_PASS = 2,
+       ZCU_FILTER_HIGH_PASS = 3, ZCU_FILTER_NOTCH = 4, ZCU_FILTER_ALL_PASS = 5 };
+typedef struct { int32_t type; float cutoff, res; } zcu_filter_params;  /* Filter.zig:27-32 */
+typedef struct {                                                        /* Portamento.zig:5-11 */
+    float sample_rate;
+    zcu_painter_curve curve;
+    float goal;
+    int32_t note_on, prev_note_on;
+} zcu_portamento_params;
+enum { ZCU_INTERP_LINEAR = 0, ZCU_INTERP_SMOOTHSTEP = 1 };
+typedef struct { float value, t; } zcu_curve_node;                      /* src/zang/curve.zig:3-6 */
+typedef struct {                                                        /* Curve.zig:29-33 */
+    float sample_rate;
+    int32_t function;
+    uint32_t node_start, node_count; /* slice of the nodes array passed to zcu_paint_curve */
+} zcu_curve_params;
+enum { ZCU_FMT_UNSIGNED8 = 0, ZCU_FMT_SIGNED16_LSB = 1, ZCU_FMT_SIGNED24_LSB = 2, ZCU_FMT_SIGNED32_LSB = 3 };
+typedef struct { float sample_rate; uint32_t channel; int32_t loop; } zcu_sampler_params; /* Sampler.zig:62-67 */
+typedef struct { float sample_rate, fake_sample_rate; } zcu_decimator_params;             /* Decimator.zig:5-9 */
+enum { ZCU_DIST_OVERDRIVE = 0, ZCU_DIST_CLIP = 1 };
+typedef struct { int32_t type; float ingain, outgain, offset; } zcu_distortion_params;   /* Distortion.zig:13-19 */
+typedef struct { float sample_rate, speed; } zcu_cycle_params;                            /* Cycle.zig:9-12 */
+
+/* ---- library / context --------------------------------------------------------------------- */
+int zcu_abi_version(void);
+int zcu_device_count(void); /* 0 when no CUDA device is usable */
+int zcu_ctx_create(int device, zcu_ctx** out);
+void zcu_ctx_destroy(zcu_ctx* ctx);
+int zcu_ctx_sync(zcu_ctx* ctx);
+const char* zcu_last_error(zcu_ctx* ctx); /* never NULL */
+void* zcu_ctx_stream(zcu_ctx* ctx);       /* the cudaStream_t every call is enqueued on */
+uint64_t zcu_ctx_launch_count(zcu_ctx* ctx); /* kernels launched by this library on this ctx so far */
+
+/* device-side timing (CUDA events on the context stream) */
+int zcu_timer_start(zcu_ctx* ctx);
+int zcu_timer_stop_ms(zcu_ctx* ctx, float* ms); /* records, synchronises, returns elapsed */
+
+/* ---- buffers: the batched form of the caller-owned []f32 (README.md:4-6) -------------------- */
+int zcu_buf_alloc(zcu_ctx* ctx, uint32_t frames, uint32_t voices, zcu_buf** out);
+int zcu_buf_wrap(zcu_ctx* ctx, void* device_ptr, uint32_t frames, uint32_t voices, zcu_buf** out);
+void zcu_buf_free(zcu_buf* buf);
+int zcu_buf_upload(zcu_ctx* ctx, zcu_buf* buf, const float* host);   /* host is [frames][voices] */
+int zcu_buf_download(zcu_ctx* ctx, const zcu_buf* buf, float* host); /* synchronises the stream */
+void* zcu_buf_device_ptr(const zcu_buf* buf);
+uint32_t zcu_buf_frames(const zcu_buf* buf);
+uint32_t zcu_buf_voices(const zcu_buf* buf);
+
+/* ---- banks: `init()` of the Zig module for every voice -------------------------------------- */
+/* Noise: voice v is seeded with first_seed + v, mirroring the global counter of Noise.zig:9,26. */
+int zcu_bank_create(zcu_ctx* ctx, int module_kind, uint32_t voices, uint32_t first_seed, zcu_bank** out);
+void zcu_bank_free(zcu_bank* bank);
+int zcu_bank_reset(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed);
+size_t zcu_bank_state_size(int module_kind); /* sizeof the per-voice state POD (0 = stateless) */
+int zcu_bank_get_state(zcu_ctx* ctx, const zcu_bank* bank, void* host, size_t bytes); /* checkpoint */
+int zcu_bank_set_state(zcu_ctx* ctx, zcu_bank* bank, const void* host, size_t bytes); /* resume */
+
+/* ---- span tables ----------------------------------------------------------------------------- */
+/* voice_off has voices+1 entries; spans of voice v are spans[voice_off[v] .. voice_off[v+1]), sorted
+ * by start, non-overlapping, each inside [0, frames). */
+int zcu_spans_upload(zcu_ctx* ctx, uint32_t voices, uint32_t frames, const uint32_t* voice_off,
+                     const zcu_span* spans, zcu_spans** out);
+/* every voice paints [0,buffer_frames) of each of num_buffers consecutive buffers with param row 0
+ * (the un-triggered call pattern, e.g. examples/example_polyphony.zig:147-160) */
+int zcu_spans_full(zcu_ctx* ctx, uint32_t voices, uint32_t num_buffers, uint32_t buffer_frames,
+                   zcu_spans** out);
+void zcu_spans_free(zcu_spans* spans);
+
+/* ---- zang basics (src/zang/basics.zig:12-78) -------------------------------------------------- */
+/* spans == NULL: whole buffer, fully vectorised.  spans != NULL: only inside each voice's spans. */
+int zcu_zero(zcu_ctx*, const zcu_spans*, zcu_buf* dest);
+int zcu_set(zcu_ctx*, const zcu_spans*, zcu_buf* dest, float a);
+int zcu_copy(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* src);
+int zcu_add(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b);
+int zcu_add_into(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* src);
+int zcu_add_scalar(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, float b);
+int zcu_add_scalar_into(zcu_ctx*, const zcu_spans*, zcu_buf* dest, float a);
+int zcu_multiply(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b);
+int zcu_multiply_with(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a);
+int zcu_multiply_scalar(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, float b);
+int zcu_multiply_with_scalar(zcu_ctx*, const zcu_spans*, zcu_buf* dest, float a);
+
+/* ---- module paints (each replaces <Module>.paint of src/modules/<Module>.zig) ---------------- */
+/* params: host array of nparams rows, copied to the device by the call.  Buffer arguments that model
+ * ConstantOrBuffer may be NULL (= .constant from the params row). */
+int zcu_paint_sine_osc(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_sine_params*, uint32_t nparams,
+                       zcu_buf* out, const zcu_buf* freq, const zcu_buf* phase);
+int zcu_paint_pulse_osc(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_pulse_params*, uint32_t nparams,
+                        zcu_buf* out, const zcu_buf* freq);
+int zcu_paint_trisaw_osc(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_trisaw_params*, uint32_t nparams,
+                         zcu_buf* out, const zcu_buf* freq);
+int zcu_paint_noise(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_noise_params*, uint32_t nparams,
+                    zcu_buf* out);
+int zcu_paint_envelope(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_envelope_params*, uint32_t nparams,
+                       zcu_buf* out);
+int zcu_paint_gate(zcu_ctx*, const zcu_spans*, const zcu_gate_params*, uint32_t nparams, zcu_buf* out);
+int zcu_paint_filter(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_filter_params*, uint32_t nparams,
+                     zcu_buf* out, const zcu_buf* input, const zcu_buf* cutoff, const zcu_buf* res);
+int zcu_paint_portamento(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_portamento_params*,
+                         uint32_t nparams, zcu_buf* out);
+int zcu_paint_curve(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_curve_params*, uint32_t nparams,
+                    const zcu_curve_node* nodes, uint32_t nnodes, zcu_buf* out);
+int zcu_paint_sampler(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_sampler_params*, uint32_t nparams,
+                      const zcu_sample* sample, zcu_buf* out);
+int zcu_paint_decimator(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_decimator_params*,
+                        uint32_t nparams, zcu_buf* out, const zcu_buf* input);
+int zcu_paint_distortion(zcu_ctx*, const zcu_spans*, const zcu_distortion_params*, uint32_t nparams,
+                         zcu_buf* out, const zcu_buf* input);
+int zcu_paint_cycle(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_cycle_params*, uint32_t nparams,
+                    zcu_buf* out, const zcu_buf* speed);
+
+/* Filter.cutoffFromFrequency (Filter.zig:20-23): host scalar, f32 arithmetic */
+float zcu_filter_cutoff_from_frequency(float frequency, float sample_rate);
+
+/* Sampler.Sample (Sampler.zig:16-21): data is copied to the device */
+int zcu_sample_create(zcu_ctx*, const uint8_t* data, size_t len, uint32_t num_channels,
+                      uint32_t sample_rate, int format, zcu_sample** out);
+void zcu_sample_free(zcu_sample*);
+
+/* ---- voice mix: what the shared outputs[0] accumulation does (example_polyphony.zig:80-91) ---- */
+/* dst[f][c] += sum_v gains[v*channels + c] * src[f][v];  dst is a [frames][channels] buffer.
+ * gains == NULL means 1.0 for every voice/channel. */
+int zcu_mix_reduce(zcu_ctx*, const zcu_buf* src, const float* gains_host, uint32_t channels, zcu_buf* dst);
+
+/* ---- zang.mixDown (src/zang/mixdown.zig:8-86): f32 -> s16le / s8 with clamping ---------------- */
+enum { ZCU_AUDIO_SIGNED8 = 0, ZCU_AUDIO_SIGNED16_LSB = 1 };
+int zcu_mix_down(zcu_ctx*, const zcu_buf* mix /* [frames][channels] */, int audio_format, float vol,
+                 uint8_t* dst_host, size_t dst_len);
+
+/* ---- host-side event layer (bit-exact index logic of src/zang/notes.zig, src/zang/trigger.zig) - */
+typedef struct zcu_impulse {  /* notes.zig:58-62 */
+    uint32_t frame;    /* frame inside the current mix buffer */
+    uint32_t note_id;
+    uint32_t event_id;
+} zcu_impulse;
+
+/* Trigger(P) (trigger.zig:26-198).  P is represented by a param row index carried with each impulse. */
+typedef struct zcu_trigger { int32_t has_note; uint32_t note_id; uint32_t param; } zcu_trigger;
+void zcu_trigger_init(zcu_trigger* t);   /* trigger.zig:56-60 */
+void zcu_trigger_reset(zcu_trigger* t);  /* trigger.zig:62-64 */
+/* Runs Trigger.counter + the whole `while (trigger.next(&ctr))` loop for the span [start,end).
+ * impulse_params[i] is the param row of impulses[i].  Writes at most max_out spans (frame indices are
+ * offset by frame_base, so a block of buffers can share one table) and returns how many it produced. */
+uint32_t zcu_trigger_run(zcu_trigger* t, uint32_t start, uint32_t end, const zcu_impulse* impulses,
+                         const uint32_t* impulse_params, uint32_t n, uint32_t frame_base, zcu_span* out,
+                         uint32_t max_out);
+
+/* ImpulseQueue (notes.zig:72-128): capacity 32, drops when full or pushed out of order. */
+typedef struct zcu_impulse_queue {
+    zcu_impulse impulses[32];
+    uint32_t params[32];
+    uint32_t length;
+    uint32_t next_event_id;
+} zcu_impulse_queue;
+void zcu_impulse_queue_init(zcu_impulse_queue* q);
+void zcu_impulse_queue_push(zcu_impulse_queue* q, uint32_t impulse_frame, uint32_t note_id, uint32_t param);
+/* returns the number of queued impulses (caller reads q->impulses / q->params) and empties the queue */
+uint32_t zcu_impulse_queue_consume(zcu_impulse_queue* q, zcu_impulse* out_impulses, uint32_t* out_params);
+
+/* IdGenerator (notes.zig:43-56) */
+typedef struct zcu_id_generator { uint32_t next_id; } zcu_id_generator;
+void zcu_id_generator_init(zcu_id_generator* g);
+uint32_t zcu_id_generator_next(zcu_id_generator* g);
+
+/* NoteTracker (notes.zig:138-207).  song events: time in seconds, note id, param row. */
+typedef struct zcu_song_event { float t; uint32_t note_id; uint32_t param; } zcu_song_event;
+typedef struct zcu_note_tracker { const zcu_song_event* song; uint32_t song_len; uint32_t next_song_event; float t; } zcu_note_tracker;
+void zcu_note_tracker_init(zcu_note_tracker* nt, const zcu_song_event* song, uint32_t song_len);
+void zcu_note_tracker_reset(zcu_note_tracker* nt);
+/* returns the number of impulses written (at most max_out; the reference has no bound check at 32,
+ * notes.zig:184-187 — events beyond max_out are consumed but dropped) */
+uint32_t zcu_note_tracker_consume(zcu_note_tracker* nt, float sample_rate, uint32_t start, uint32_t end,
+                                  zcu_impulse* out_impulses, uint32_t* out_params, uint32_t max_out);
+
+/* PolyphonyDispatcher(n) (notes.zig:209-349), n <= ZCU_MAX_POLYPHONY */
+#define ZCU_MAX_POLYPHONY 32
+typedef struct zcu_poly_slot { int32_t used; uint32_t note_id; uint32_t event_id; int32_t note_on; } zcu_poly_slot;
+typedef struct zcu_poly_dispatcher { uint32_t polyphony; zcu_poly_slot slots[ZCU_MAX_POLYPHONY]; } zcu_poly_dispatcher;
+int zcu_poly_dispatcher_init(zcu_poly_dispatcher* pd, uint32_t polyphony);
+void zcu_poly_dispatcher_reset(zcu_poly_dispatcher* pd);
+/* note_on[i] is the note_on field of the params of impulse i.  out_* are [polyphony][32] arrays;
+ * out_counts[polyphony]. */
+int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* impulses, const uint32_t* params,
+                                 const int32_t* note_on, uint32_t n, zcu_impulse* out_impulses,
+                                 uint32_t* out_params, uint32_t* out_counts);
+
+/* ---- fused instrument banks (B200-first path for the benchmark configs) ----------------------- */
+/* A note event of one voice with an ABSOLUTE frame position in the whole render.  Voice v owns
+ * events[event_off[v] .. event_off[v+1]), chronological.  The device replays Trigger semantics
+ * per mix buffer (trigger.zig:80-196) itself, so no span table crosses PCIe. */
+typedef struct zcu_note_event {
+    uint32_t frame;   /* absolute frame in the render */
+    uint32_t note_id;
+    float freq;
+    int32_t note_on;
+} zcu_note_event;
+
+typedef struct zcu_render zcu_render;
+
+enum {
+    ZCU_INSTR_NICE = 0,          /* examples/modules.zig:189-248 NiceInstrument */
+    ZCU_INSTR_COUNT = 1
+};
+
+typedef struct zcu_render_config {
+    int32_t instrument;       /* ZCU_INSTR_* */
+    uint32_t voices;
+    uint32_t buffer_frames;   /* the reference's AUDIO_BUFFER_SIZE, 1024 */
+    uint32_t total_frames;    /* length of the whole render */
+    uint32_t block_buffers;   /* mix buffers rendered per kernel launch (0 = default) */
+    uint32_t channels;        /* 1 or 2: channels of the mix */
+    float sample_rate;
+    uint32_t first_seed;      /* Noise seed of voice 0 */
+    int32_t mode;             /* ZCU_RENDER_EXACT or ZCU_RENDER_SCAN */
+} zcu_render_config;
+enum { ZCU_RENDER_EXACT = 0, ZCU_RENDER_SCAN = 1 };
+
+/* per-voice constants: NiceInstrument.color (modules.zig:198) and the mix gains [voices][channels] */
+int zcu_render_create(zcu_ctx*, const zcu_render_config* cfg, const float* voice_color_host,
+                      const float* gains_host, zcu_render** out);
+void zcu_render_free(zcu_render*);
+/* host events -> device (H2D), resets all voice state */
+int zcu_render_set_events(zcu_ctx*, zcu_render*, const uint32_t* event_off_host, const zcu_note_event* events_host);
+/* renders the whole job into mix ([total_frames][channels], accumulating, like every zang paint) */
+int zcu_render_run(zcu_ctx*, zcu_render*, zcu_buf* mix);
+/* optional: per-voice output (before mixing) of frames [first_frame, first_frame+out->frames) for parity tests */
+int zcu_render_run_voices(zcu_ctx*, zcu_render*, uint32_t first_frame, zcu_buf* out_voices);
+uint64_t zcu_render_launches_per_run(const zcu_render*);
+
+/* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
+/* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */
+int zcu_nccl_unique_id(uint8_t id_out[128]);
+int zcu_nccl_init(zcu_ctx*, int nranks, int rank, const uint8_t id[128]);
+int zcu_nccl_reduce_mix(zcu_ctx*, zcu_buf* mix, int root); /* ncclReduce(sum, f32) in place on root */
+int zcu_nccl_finalize(zcu_ctx*);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZANGCU_H */

@@ -1,0 +1,96 @@
+"""Test-side loader of the CPU oracle (oracle/_build/libzang_oracle.so).  TEST INFRASTRUCTURE ONLY."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from zang_b200 import _lib as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ODIR = os.path.join(ROOT, "oracle")
+OPATH = os.path.join(ODIR, "_build", "libzang_oracle.so")
+
+
+def _build():
+    subprocess.run(["make", "-C", ODIR], check=True, stdout=subprocess.DEVNULL)
+
+
+if not os.path.exists(OPATH):
+    _build()
+orc = C.CDLL(OPATH)
+
+_P, _I, _U, _F, _U64 = C.c_void_p, C.c_int, C.c_uint32, C.c_float, C.c_uint64
+orc.orc_basic.argtypes = [_I, _U, _U, _P, _P, _P, _P, _P, _F]
+orc.orc_paint.argtypes = [_I, _U, _U, _P, _P, _P, _U, _P, _P, _P, _P, _P, _P, _U64, _P]
+orc.orc_state_init.argtypes = [_I, _U, _U, _P]
+orc.orc_cutoff_from_frequency.argtypes = [_F, _F]
+orc.orc_cutoff_from_frequency.restype = _F
+orc.orc_xoshiro_seed.argtypes = [_U64, _P]
+orc.orc_xoshiro_next.argtypes = [_P, _P, _U]
+orc.orc_xoshiro_floats.argtypes = [_P, _P, _U]
+orc.orc_trigger_run.argtypes = [_P, _U, _U, _P, _P, _U, _U, _P, _U]
+orc.orc_trigger_run.restype = _U
+orc.orc_poly_dispatch.argtypes = [_U, _P, _P, _P, _P, _U, _P, _P, _P]
+orc.orc_note_tracker_consume.argtypes = [_P, _P, _U, _F, _U, _U, _P, _P]
+orc.orc_note_tracker_consume.restype = _U
+orc.orc_impulse_queue_push.argtypes = [_P, _U, _U, _U]
+orc.orc_mix_down.argtypes = [_P, _U, _U, _I, _F, _P]
+orc.orc_mix_reduce.argtypes = [_P, _U, _U, _P, _U, _P]
+orc.orc_render_nice.argtypes = [_U, _U, _U, _F, _P, _P, _P, _P, _U, _P, _P, _U, _U, _U]
+orc.orc_render_nice.restype = C.c_double
+orc.orc_hardware_threads.restype = _U
+
+ptr = L.ptr
+
+
+def state_init(kind, V, first_seed=0):
+    dt = L.state_dtypes[kind]
+    if dt is None:
+        return None
+    st = np.zeros(V, dtype=dt)
+    assert orc.orc_state_init(kind, V, first_seed, ptr(st)) == 0
+    return st
+
+
+def paint(kind, off, spans, params, state, out, in0=None, in1=None, in2=None, aux=None, aux_meta=None):
+    """In-place on `out` ([frames][V] f32) and `state`."""
+    frames, V = out.shape
+    params = np.ascontiguousarray(params, dtype=L.param_dtypes[kind]).reshape(-1)
+    for a in (in0, in1, in2):
+        assert a is None or (a.dtype == np.float32 and a.flags.c_contiguous and a.shape == out.shape)
+    aux_len = 0
+    meta = None
+    if kind == L.MOD_CURVE:
+        aux = np.ascontiguousarray(aux, dtype=L.curve_node_dtype).reshape(-1)
+        aux_len = aux.size
+    elif kind == L.MOD_SAMPLER:
+        aux = np.ascontiguousarray(aux, dtype=np.uint8)
+        aux_len = aux.size
+        meta = np.array(aux_meta, dtype=np.int64)
+    rc = orc.orc_paint(kind, V, frames, ptr(off), ptr(spans), ptr(params), params.size, ptr(state), ptr(out), ptr(in0), ptr(in1),
+                       ptr(in2), ptr(aux), aux_len, ptr(meta))
+    assert rc == 0, rc
+
+
+def basic(op, off, spans, dest, a=None, b=None, scalar=0.0):
+    frames, V = dest.shape
+    rc = orc.orc_basic(op, V, frames, ptr(off), ptr(spans), ptr(dest), ptr(a), ptr(b), float(scalar))
+    assert rc == 0
+
+
+def render_nice(wl, total_frames, sample_rate=48000.0, buffer_frames=1024, channels=2, want_mix=True, window=None, nthreads=1):
+    """Oracle render of a polyphony-bank workload.  Returns (mix or None, voices window or None, seconds)."""
+    V = wl["color"].size
+    mix = np.zeros((total_frames, channels), dtype=np.float32) if want_mix else None
+    vo, first, n = None, 0, 0
+    if window is not None:
+        first, n = window
+        vo = np.zeros((n, V), dtype=np.float32)
+    ev = np.ascontiguousarray(wl["events"], dtype=L.note_event_dtype)
+    off = np.ascontiguousarray(wl["event_off"], dtype=np.uint32)
+    color = np.ascontiguousarray(wl["color"], dtype=np.float32)
+    gains = np.ascontiguousarray(wl["gains"], dtype=np.float32)
+    secs = orc.orc_render_nice(V, total_frames, buffer_frames, sample_rate, ptr(off), ptr(ev), ptr(color), ptr(gains), channels, ptr(mix),
+                               ptr(vo), first, n, nthreads)
+    return mix, vo, secs

@@ -1,0 +1,320 @@
+// zcu_basics.cu — zang's buffer primitives (src/zang/basics.zig:12-78), the voice mix, zang.mixDown
+// (src/zang/mixdown.zig), bank initialisation and the no-FMA self test.
+#include "zcu_internal.h"
+#include "zcu_paint_kernel.cuh"
+
+using namespace zcu;
+
+namespace {
+
+// ---- whole-buffer elementwise kernels: float4 over the flattened [frame][voice] array ----------
+template <int OP>
+__device__ __forceinline__ float basic_op(float d, float a, float b, float s) {
+    switch (OP) {
+        case 0: return 0.0f;
+        case 1: return s;
+        case 2: return a;
+        case 3: return d + (a + b);
+        case 4: return d + a;
+        case 5: return d + (a + s);
+        case 6: return d + s;
+        case 7: return d + a * b;
+        case 8: return d * a;
+        case 9: return d + a * s;
+        default: return d * s;
+    }
+}
+template <int OP>
+struct OpTraits {
+    static constexpr bool reads_dest = !(OP == 0 || OP == 1 || OP == 2);
+    static constexpr bool reads_a = (OP == 2 || OP == 3 || OP == 4 || OP == 5 || OP == 7 || OP == 8 || OP == 9);
+    static constexpr bool reads_b = (OP == 3 || OP == 7);
+};
+
+template <int OP>
+__global__ void __launch_bounds__(256) k_basic_full(float* __restrict__ dest, const float* __restrict__ a,
+                                                    const float* __restrict__ b, float s, size_t n4, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 d = make_float4(0, 0, 0, 0), x = d, y = d;
+        if (OpTraits<OP>::reads_dest) d = reinterpret_cast<const float4*>(dest)[i];
+        if (OpTraits<OP>::reads_a) x = reinterpret_cast<const float4*>(a)[i];
+        if (OpTraits<OP>::reads_b) y = reinterpret_cast<const float4*>(b)[i];
+        float4 r;
+        r.x = basic_op<OP>(d.x, x.x, y.x, s);
+        r.y = basic_op<OP>(d.y, x.y, y.y, s);
+        r.z = basic_op<OP>(d.z, x.z, y.z, s);
+        r.w = basic_op<OP>(d.w, x.w, y.w, s);
+        reinterpret_cast<float4*>(dest)[i] = r;
+    }
+    // tail (n not a multiple of 4)
+    for (size_t i = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float d = OpTraits<OP>::reads_dest ? dest[i] : 0.0f;
+        const float x = OpTraits<OP>::reads_a ? a[i] : 0.0f;
+        const float y = OpTraits<OP>::reads_b ? b[i] : 0.0f;
+        dest[i] = basic_op<OP>(d, x, y, s);
+    }
+}
+
+template <int OP>
+int launch_full(zcu_ctx* ctx, float* dest, const float* a, const float* b, float s, size_t n) {
+    const bool aligned = (((uintptr_t)dest | (uintptr_t)a | (uintptr_t)b) & 15u) == 0;
+    const size_t n4 = aligned ? n / 4 : 0;
+    size_t blocks = (n4 + 255) / 256;
+    const size_t cap = (size_t)ctx->sm_count * 8;  // 8 resident CTAs of 256 threads per SM, grid-stride beyond
+    if (blocks > cap) blocks = cap;
+    if (blocks == 0) blocks = 1;
+    k_basic_full<OP><<<(unsigned)blocks, 256, 0, ctx->stream>>>(dest, a, b, s, n4, n);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    return ZCU_OK;
+}
+
+template <int OP>
+int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a, const float* b, float s) {
+    void* dscalar = nullptr;
+    int rc = zcu_arena_upload(ctx, 0, &s, sizeof(float), &dscalar);
+    if (rc) return rc;
+    PaintArgs pa{};
+    pa.V = sp->voices;
+    pa.frames = sp->frames;
+    pa.off = sp->d_off;
+    pa.spans = sp->d_spans;
+    pa.params = dscalar;
+    pa.out = dest;
+    pa.in0 = OpTraits<OP>::reads_a ? a : nullptr;
+    pa.in1 = OpTraits<OP>::reads_b ? b : nullptr;
+    if (pa.V == 0 || pa.frames == 0) return ZCU_OK;
+    const uint32_t warps = (pa.V + 31) / 32;
+    const uint32_t T = warps <= 4 * 148 ? 64u : 32u;
+    int nb = 1 + (pa.in0 ? 1 : 0) + (pa.in1 ? 1 : 0);
+    const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP>>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
+        attr_set = true;
+    }
+    k_paint_lockstep<BasicMod<OP>><<<warps, 32, smem, ctx->stream>>>(pa, T);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    return ZCU_OK;
+}
+
+template <int OP>
+int launch_op(zcu_ctx* ctx, const zcu_spans* sp, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b, float s) {
+    const float* pa = a ? a->d : nullptr;
+    const float* pb = b ? b->d : nullptr;
+    if (sp) return launch_spans<OP>(ctx, sp, dest->d, pa, pb, s);
+    return launch_full<OP>(ctx, dest->d, pa, pb, s, (size_t)dest->frames * dest->voices);
+}
+
+// ---- voice mix: dst[f][c] += sum_v gains[v][c] * src[f][v] -------------------------------------
+// One CTA per frame; each thread strides over voices with coalesced float loads, then a fixed-order
+// tree (warp shuffles, then one warp over the per-warp partials) so the result is deterministic.
+template <int C>
+__global__ void __launch_bounds__(256) k_mix_reduce(const float* __restrict__ src, const float* __restrict__ gains,
+                                                    float* __restrict__ dst, uint32_t V) {
+    const uint32_t f = blockIdx.x;
+    const float* row = src + (size_t)f * V;
+    float acc[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) acc[c] = 0.0f;
+    for (uint32_t v = threadIdx.x; v < V; v += blockDim.x) {
+        const float x = row[v];
+#pragma unroll
+        for (int c = 0; c < C; c++) acc[c] += (gains ? gains[(size_t)v * C + c] : 1.0f) * x;
+    }
+    __shared__ float part[8][C];
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        float s = acc[c];
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5][c] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < C) {
+        float s = 0.0f;
+        for (int w = 0; w < 8; w++) s += part[w][threadIdx.x];
+        dst[(size_t)f * C + threadIdx.x] += s;
+    }
+}
+
+// ---- zang.mixDown (mixdown.zig:28-86) ---------------------------------------------------------------
+__global__ void k_mix_down_s16(const float* __restrict__ mix, uint8_t* __restrict__ dst, size_t n, float mul) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float value = mix[i] * mul;
+    int cv;
+    if (value <= -32767.0f)
+        cv = -32767;
+    else if (value >= 32766.0f)
+        cv = 32766;
+    else if (value != value)
+        cv = 0;
+    else
+        cv = (int)value;  // @intFromFloat: truncation
+    dst[i * 2 + 0] = (uint8_t)(cv & 0xFF);
+    dst[i * 2 + 1] = (uint8_t)((cv >> 8) & 0xFF);
+}
+__global__ void k_mix_down_s8(const float* __restrict__ mix, uint8_t* __restrict__ dst, size_t n, float mul) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float value = mix[i] * mul;
+    int cv;
+    if (value <= -127.0f)
+        cv = -127;
+    else if (value >= 126.0f)
+        cv = 126;
+    else if (value != value)
+        cv = 0;
+    else
+        cv = (int)value;
+    dst[i] = (uint8_t)(int8_t)cv;
+}
+
+// ---- bank init: <Module>.init() for every voice ------------------------------------------------------
+__global__ void k_bank_init(int kind, void* state, uint32_t V, uint32_t first_seed) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    switch (kind) {
+        case ZCU_MOD_SINE_OSC: ((zcu_sine_state*)state)[v].t = 0.0f; break;
+        case ZCU_MOD_PULSE_OSC: ((zcu_pulse_state*)state)[v].cnt = 0; break;
+        case ZCU_MOD_TRISAW_OSC: {
+            zcu_trisaw_state s;
+            s.cnt = 0;
+            s.t = 0.0f;
+            ((zcu_trisaw_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_NOISE: {  // Noise.zig:25-32, seed = counter value
+            XoshiroDev r;
+            r.seed((uint64_t)(first_seed + v));
+            zcu_noise_state s;
+            s.s[0] = r.s0;
+            s.s[1] = r.s1;
+            s.s[2] = r.s2;
+            s.s[3] = r.s3;
+            ((zcu_noise_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_ENVELOPE: {
+            zcu_envelope_state s;
+            s.state = ZCU_ENV_IDLE;
+            s.painter.t = s.painter.last_value = s.painter.start = 0.0f;
+            ((zcu_envelope_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_FILTER: {
+            zcu_filter_state s;
+            s.l = s.b = 0.0f;
+            ((zcu_filter_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_PORTAMENTO: {
+            zcu_portamento_state s;
+            s.painter.t = s.painter.last_value = s.painter.start = 0.0f;
+            ((zcu_portamento_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_CURVE: {
+            zcu_curve_state s;
+            s.t = 0.0f;
+            s.current_song_note = 0;
+            s.current_song_note_offset = 0;
+            s.next_song_note = 0;
+            ((zcu_curve_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_SAMPLER: ((zcu_sampler_state*)state)[v].t = 0.0f; break;
+        case ZCU_MOD_DECIMATOR: {
+            zcu_decimator_state s;
+            s.dval = 0.0f;
+            s.dcount = 1.0f;
+            ((zcu_decimator_state*)state)[v] = s;
+        } break;
+        case ZCU_MOD_CYCLE: ((zcu_cycle_state*)state)[v].t = 0.0f; break;
+        default: break;
+    }
+}
+
+// a*b+c with operands chosen so that a fused multiply-add gives a different f32 than mul-then-add
+__global__ void k_fma_probe(float a, float b, float c, float* out) { out[0] = a * b + c; }
+
+}  // namespace
+
+int zcu_launch_basic(zcu_ctx* ctx, int op, const zcu_spans* sp, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b, float s) {
+    switch (op) {
+        case 0: return launch_op<0>(ctx, sp, dest, a, b, s);
+        case 1: return launch_op<1>(ctx, sp, dest, a, b, s);
+        case 2: return launch_op<2>(ctx, sp, dest, a, b, s);
+        case 3: return launch_op<3>(ctx, sp, dest, a, b, s);
+        case 4: return launch_op<4>(ctx, sp, dest, a, b, s);
+        case 5: return launch_op<5>(ctx, sp, dest, a, b, s);
+        case 6: return launch_op<6>(ctx, sp, dest, a, b, s);
+        case 7: return launch_op<7>(ctx, sp, dest, a, b, s);
+        case 8: return launch_op<8>(ctx, sp, dest, a, b, s);
+        case 9: return launch_op<9>(ctx, sp, dest, a, b, s);
+        case 10: return launch_op<10>(ctx, sp, dest, a, b, s);
+        default: return zcu_fail(ctx, ZCU_ERR_INVALID, "unknown basic op %d", op);
+    }
+}
+
+int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed) {
+    if (bank->voices == 0 || bank->stride == 0) return ZCU_OK;
+    k_bank_init<<<(bank->voices + 127) / 128, 128, 0, ctx->stream>>>(bank->kind, bank->d, bank->voices, first_seed);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    return ZCU_OK;
+}
+
+int zcu_selftest_no_fma(zcu_ctx* ctx) {
+    // a = 1 + 2^-12, b = 1 - 2^-12: a*b = 1 - 2^-24 exactly, which rounds to 1.0f;  c = -1:
+    // unfused -> 0, fused -> -2^-24.
+    float* d = nullptr;
+    int rc = zcu_arena_reserve(ctx, 0, sizeof(float), (void**)&d);
+    if (rc) return rc;
+    k_fma_probe<<<1, 1, 0, ctx->stream>>>(1.0f + 0x1p-12f, 1.0f - 0x1p-12f, -1.0f, d);
+    ctx->launches++;
+    float h = 1.0f;
+    ZCU_CUDA(ctx, cudaMemcpyAsync(&h, d, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h != 0.0f) return zcu_fail(ctx, ZCU_ERR_UNSUPPORTED, "library was built with FMA contraction (need -fmad=false)");
+    return ZCU_OK;
+}
+
+extern "C" int zcu_mix_reduce(zcu_ctx* ctx, const zcu_buf* src, const float* gains_host, uint32_t channels, zcu_buf* dst) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, src && dst, "null buffer");
+    ZCU_REQUIRE(ctx, channels == 1 || channels == 2, "channels must be 1 or 2");
+    ZCU_REQUIRE(ctx, dst->voices == channels && dst->frames == src->frames, "dst must be [frames][channels]");
+    float* dg = nullptr;
+    if (gains_host) {
+        int rc = zcu_arena_upload(ctx, 1, gains_host, (size_t)src->voices * channels * sizeof(float), (void**)&dg);
+        if (rc) return rc;
+    }
+    if (src->frames == 0) return ZCU_OK;
+    if (channels == 1)
+        k_mix_reduce<1><<<src->frames, 256, 0, ctx->stream>>>(src->d, dg, dst->d, src->voices);
+    else
+        k_mix_reduce<2><<<src->frames, 256, 0, ctx->stream>>>(src->d, dg, dst->d, src->voices);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    return ZCU_OK;
+}
+
+extern "C" int zcu_mix_down(zcu_ctx* ctx, const zcu_buf* mix, int audio_format, float vol, uint8_t* dst_host, size_t dst_len) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, mix && dst_host, "null argument");
+    const size_t n = (size_t)mix->frames * mix->voices;
+    const size_t bytes = audio_format == ZCU_AUDIO_SIGNED16_LSB ? n * 2 : n;
+    ZCU_REQUIRE(ctx, audio_format == ZCU_AUDIO_SIGNED16_LSB || audio_format == ZCU_AUDIO_SIGNED8, "unknown audio format");
+    ZCU_REQUIRE(ctx, dst_len == bytes, "dst_len must be frames*channels*bytes_per_sample (mixdown.zig:35,66)");
+    if (n == 0) return ZCU_OK;
+    uint8_t* d = nullptr;
+    int rc = zcu_arena_reserve(ctx, 2, bytes, (void**)&d);
+    if (rc) return rc;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    if (audio_format == ZCU_AUDIO_SIGNED16_LSB)
+        k_mix_down_s16<<<blocks, 256, 0, ctx->stream>>>(mix->d, d, n, vol * 32767.0f);
+    else
+        k_mix_down_s8<<<blocks, 256, 0, ctx->stream>>>(mix->d, d, n, vol * 127.0f);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    ZCU_CUDA(ctx, cudaMemcpyAsync(dst_host, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ZCU_OK;
+}

@@ -1,0 +1,204 @@
+// zcu_events.cpp — host-side event layer: the index logic of src/zang/notes.zig and src/zang/trigger.zig
+// on the PODs of zangcu.h.  Pure integer / f32 host code, no CUDA.  Results are bit-exact with the
+// reference (pinned by its own tests, transcribed in tests/test_event_kat.py).
+//
+// A params value P of the reference is represented by a `param` row index that travels with the
+// impulse; the caller keeps the table of rows.
+#include <algorithm>
+#include <cstring>
+
+#include "../../include/zangcu.h"
+
+extern "C" {
+
+// ---- Trigger (trigger.zig:26-198) ---------------------------------------------------------------------
+void zcu_trigger_init(zcu_trigger* t) {
+    t->has_note = 0;
+    t->note_id = 0;
+    t->param = 0;
+}
+void zcu_trigger_reset(zcu_trigger* t) { zcu_trigger_init(t); }
+
+// What Trigger.next() produces over one buffer, stated directly:
+//   * while a note is current and the next unconsumed impulse lies later, the current note plays up to
+//     that impulse (carryOver, :107-137);
+//   * at an impulse's frame the impulse is consumed; if another impulse has the same frame the earlier
+//     one is dropped (:173-178), otherwise it becomes the current note and plays to the next impulse or
+//     the end of the buffer;
+//   * before the first note ever, the gap up to the first impulse is skipped (:152-158);
+//   * an impulse at or past the end of the buffer ends the scan (:144-150) — the rest of the buffer is
+//     a gap when nothing has played yet, and belongs to the current note otherwise.
+// note_id_changed compares with the note of the previously RETURNED span (:96-100).
+uint32_t zcu_trigger_run(zcu_trigger* t, uint32_t start, uint32_t end, const zcu_impulse* impulses, const uint32_t* impulse_params,
+                         uint32_t n, uint32_t frame_base, zcu_span* out, uint32_t max_out) {
+    uint32_t produced = 0;
+    uint32_t idx = 0;   // Counter.impulse_index
+    uint32_t pos = start;
+    while (pos < end) {
+        uint32_t span_end;
+        bool has = false;
+        uint32_t id = 0, param = 0;
+        bool carried = false;
+        if (t->has_note) {
+            if (idx < n) {
+                const uint32_t nf = impulses[idx].frame;
+                if (nf > pos) {
+                    carried = true;
+                    span_end = std::min(end, nf);
+                }
+            } else {
+                carried = true;
+                span_end = end;
+            }
+            if (carried) {
+                has = true;
+                id = t->note_id;
+                param = t->param;
+            }
+        }
+        if (!carried) {
+            // getNextNoteSpan: scan from idx
+            span_end = end;  // "no more impulses" gap
+            uint32_t i = idx;
+            for (; i < n; i++) {
+                const uint32_t fr = impulses[i].frame;
+                if (fr >= end) break;         // gap to the end of the buffer
+                if (fr > pos) {               // gap before the note begins
+                    span_end = fr;
+                    break;
+                }
+                idx++;                        // consumed (frame == pos; earlier frames are a caller bug, trigger.zig:161)
+                const uint32_t note_end = (i + 1 < n) ? std::min(end, impulses[i + 1].frame) : end;
+                if (note_end <= pos) continue;  // superseded by the next impulse at the same frame
+                has = true;
+                id = impulses[i].note_id;
+                param = impulse_params[i];
+                span_end = note_end;
+                break;
+            }
+        }
+        if (has) {
+            const bool changed = t->has_note ? (id != t->note_id) : true;
+            if (produced < max_out) out[produced] = zcu_span{pos + frame_base, span_end + frame_base, changed ? ZCU_SPAN_NOTE_ID_CHANGED : 0u, param};
+            produced++;
+            t->has_note = 1;
+            t->note_id = id;
+            t->param = param;
+        }
+        pos = span_end;
+    }
+    return produced;
+}
+
+// ---- ImpulseQueue (notes.zig:72-128) ------------------------------------------------------------------
+void zcu_impulse_queue_init(zcu_impulse_queue* q) {
+    q->length = 0;
+    q->next_event_id = 1;
+}
+void zcu_impulse_queue_push(zcu_impulse_queue* q, uint32_t impulse_frame, uint32_t note_id, uint32_t param) {
+    if (q->length >= 32) return;                                                      // full: dropped (:108-111)
+    if (q->length > 0 && impulse_frame < q->impulses[q->length - 1].frame) return;   // out of order: dropped (:112-118)
+    q->impulses[q->length] = zcu_impulse{impulse_frame, note_id, q->next_event_id};
+    q->params[q->length] = param;
+    q->length++;
+    q->next_event_id++;
+}
+uint32_t zcu_impulse_queue_consume(zcu_impulse_queue* q, zcu_impulse* out_impulses, uint32_t* out_params) {
+    const uint32_t n = q->length;
+    if (out_impulses) std::memcpy(out_impulses, q->impulses, n * sizeof(zcu_impulse));
+    if (out_params) std::memcpy(out_params, q->params, n * sizeof(uint32_t));
+    q->length = 0;
+    return n;
+}
+
+// ---- IdGenerator (notes.zig:43-56) ---------------------------------------------------------------------
+void zcu_id_generator_init(zcu_id_generator* g) { g->next_id = 1; }
+uint32_t zcu_id_generator_next(zcu_id_generator* g) { return g->next_id++; }
+
+// ---- NoteTracker (notes.zig:138-207) -------------------------------------------------------------------
+void zcu_note_tracker_init(zcu_note_tracker* nt, const zcu_song_event* song, uint32_t song_len) {
+    nt->song = song;
+    nt->song_len = song_len;
+    nt->next_song_event = 0;
+    nt->t = 0.0f;
+}
+void zcu_note_tracker_reset(zcu_note_tracker* nt) {
+    nt->next_song_event = 0;
+    nt->t = 0.0f;
+}
+uint32_t zcu_note_tracker_consume(zcu_note_tracker* nt, float sample_rate, uint32_t start, uint32_t end, zcu_impulse* out_impulses,
+                                  uint32_t* out_params, uint32_t max_out) {
+    uint32_t count = 0;
+    const uint32_t out_len = end - start;
+    const float flen = (float)out_len;
+    const float buf_time = flen / sample_rate;
+    const float end_t = nt->t + buf_time;  // f32 accumulation, as the reference
+    while (nt->next_song_event < nt->song_len) {
+        const zcu_song_event& ev = nt->song[nt->next_song_event];
+        if (!(ev.t < end_t)) break;
+        const float f = (ev.t - nt->t) / buf_time;
+        uint32_t rel = (uint32_t)(f * flen);
+        if (rel > out_len - 1) rel = out_len - 1;
+        nt->next_song_event++;
+        if (count < max_out) {
+            out_impulses[count] = zcu_impulse{start + rel, ev.note_id, nt->next_song_event};  // event_id is 1-based (:186-190)
+            out_params[count] = ev.param;
+            count++;
+        }
+    }
+    nt->t = end_t;
+    return count;
+}
+
+// ---- PolyphonyDispatcher (notes.zig:209-349) -----------------------------------------------------------
+int zcu_poly_dispatcher_init(zcu_poly_dispatcher* pd, uint32_t polyphony) {
+    if (!pd || polyphony == 0 || polyphony > ZCU_MAX_POLYPHONY) return ZCU_ERR_INVALID;
+    pd->polyphony = polyphony;
+    zcu_poly_dispatcher_reset(pd);
+    return ZCU_OK;
+}
+void zcu_poly_dispatcher_reset(zcu_poly_dispatcher* pd) {
+    for (uint32_t i = 0; i < ZCU_MAX_POLYPHONY; i++) pd->slots[i] = zcu_poly_slot{0, 0, 0, 0};
+}
+
+// slot policy (:246-306): note-off -> the slot still sounding that note id, else dropped; note-on -> the
+// first never-used slot, else the released slot with the oldest event, else the sounding slot with the
+// oldest event.
+static int choose_slot(const zcu_poly_dispatcher* pd, uint32_t note_id, bool note_on) {
+    const uint32_t n = pd->polyphony;
+    if (!note_on) {
+        for (uint32_t i = 0; i < n; i++)
+            if (pd->slots[i].used && pd->slots[i].note_id == note_id && pd->slots[i].note_on) return (int)i;
+        return -1;
+    }
+    int best_released = -1;
+    for (uint32_t i = 0; i < n; i++) {
+        if (!pd->slots[i].used) return (int)i;
+        if (!pd->slots[i].note_on && (best_released < 0 || pd->slots[i].event_id < pd->slots[best_released].event_id)) best_released = (int)i;
+    }
+    if (best_released >= 0) return best_released;
+    int best = 0;
+    for (uint32_t i = 1; i < n; i++)
+        if (pd->slots[i].event_id < pd->slots[best].event_id) best = (int)i;
+    return best;
+}
+
+int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* impulses, const uint32_t* params, const int32_t* note_on,
+                                 uint32_t n, zcu_impulse* out_impulses, uint32_t* out_params, uint32_t* out_counts) {
+    if (!pd || pd->polyphony == 0 || pd->polyphony > ZCU_MAX_POLYPHONY) return ZCU_ERR_INVALID;
+    for (uint32_t i = 0; i < pd->polyphony; i++) out_counts[i] = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const int slot = choose_slot(pd, impulses[i].note_id, note_on[i] != 0);
+        if (slot < 0) continue;
+        pd->slots[slot] = zcu_poly_slot{1, impulses[i].note_id, impulses[i].event_id, note_on[i] != 0 ? 1 : 0};
+        const uint32_t c = out_counts[slot];
+        if (c < 32) {
+            out_impulses[(size_t)slot * 32 + c] = impulses[i];
+            out_params[(size_t)slot * 32 + c] = params[i];
+            out_counts[slot] = c + 1;
+        }
+    }
+    return ZCU_OK;
+}
+
+}  // extern "C"

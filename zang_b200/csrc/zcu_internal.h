@@ -1,0 +1,98 @@
+// zcu_internal.h — handle definitions and helpers shared by the translation units of libzangcu.so.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/zangcu.h"
+
+struct zcu_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err = "";
+    uint64_t launches = 0;
+    // stream-ordered arena for per-call parameter tables (params rows, curve nodes, gains)
+    void* arena[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t arena_bytes[4] = {0, 0, 0, 0};
+    int sm_count = 148;
+    // NCCL (loaded lazily with dlopen)
+    void* nccl_comm = nullptr;
+    int nccl_rank = 0, nccl_nranks = 1;
+};
+
+struct zcu_buf {
+    zcu_ctx* ctx;
+    float* d;
+    uint32_t frames, voices;
+    bool owned;
+};
+
+struct zcu_bank {
+    zcu_ctx* ctx;
+    int kind;
+    uint32_t voices;
+    void* d;        // voices * stride bytes
+    size_t stride;  // sizeof the state POD
+};
+
+struct zcu_spans {
+    zcu_ctx* ctx;
+    uint32_t voices, frames, nspans;
+    uint32_t* d_off;    // voices+1
+    zcu_span* d_spans;  // nspans
+    uint32_t max_param; // largest param row referenced
+};
+
+struct zcu_sample {
+    zcu_ctx* ctx;
+    uint8_t* d;
+    size_t len;
+    uint32_t num_channels, sample_rate;
+    int format;
+};
+
+// -- error plumbing -----------------------------------------------------------------------------
+int zcu_fail(zcu_ctx* ctx, int code, const char* fmt, ...);
+
+#define ZCU_CUDA(ctx, expr)                                                                          \
+    do {                                                                                             \
+        cudaError_t _e = (expr);                                                                     \
+        if (_e != cudaSuccess)                                                                       \
+            return zcu_fail((ctx), _e == cudaErrorMemoryAllocation ? ZCU_ERR_OOM : ZCU_ERR_CUDA,     \
+                            "%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));    \
+    } while (0)
+
+#define ZCU_REQUIRE(ctx, cond, msg)                                                         \
+    do {                                                                                    \
+        if (!(cond)) return zcu_fail((ctx), ZCU_ERR_INVALID, "%s: %s", __func__, (msg));    \
+    } while (0)
+
+// copies `bytes` of host memory into arena slot `slot` (stream ordered) and returns the device ptr
+int zcu_arena_upload(zcu_ctx* ctx, int slot, const void* host, size_t bytes, void** dev_out);
+int zcu_arena_reserve(zcu_ctx* ctx, int slot, size_t bytes, void** dev_out);
+
+// implemented in zcu_paint.cu / zcu_basics.cu / zcu_render.cu
+struct PaintLaunch {
+    int kind;
+    uint32_t V, frames;
+    const uint32_t* off;
+    const zcu_span* spans;
+    const void* params;
+    void* state;
+    float* out;
+    const float* in0;
+    const float* in1;
+    const float* in2;
+    const void* aux;      // curve nodes / PCM bytes
+    uint64_t aux_len;
+    uint32_t smp_channels, smp_rate;
+    int smp_format;
+};
+int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl);
+int zcu_launch_basic(zcu_ctx* ctx, int op, const zcu_spans* spans, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b, float scalar);
+int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed);
+int zcu_selftest_no_fma(zcu_ctx* ctx);

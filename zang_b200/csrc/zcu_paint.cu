@@ -1,0 +1,83 @@
+// zcu_paint.cu — instantiation and launch of the lockstep paint kernel for every module variant.
+#include "zcu_internal.h"
+#include "zcu_paint_kernel.cuh"
+
+using namespace zcu;
+
+namespace {
+
+uint32_t pick_tile(uint32_t V) {
+    // few voices -> few warps on the chip -> deeper prefetch per warp; many voices -> more warps per SM
+    const uint32_t warps = (V + 31) / 32;
+    return warps <= 4 * 148 ? 64u : 32u;
+}
+
+template <class M>
+int launch(zcu_ctx* ctx, const PaintArgs& a) {
+    const uint32_t T = pick_tile(a.V);
+    int nb = 1;
+    if (M::NIN >= 1 && a.in0) nb++;
+    if (M::NIN >= 2 && a.in1) nb++;
+    if (M::NIN >= 3 && a.in2) nb++;
+    const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
+        attr_set = true;
+    }
+    const uint32_t grid = (a.V + 31) / 32;
+    k_paint_lockstep<M><<<grid, 32, smem, ctx->stream>>>(a, T);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    return ZCU_OK;
+}
+
+}  // namespace
+
+int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
+    PaintArgs a;
+    a.V = pl.V;
+    a.frames = pl.frames;
+    a.off = pl.off;
+    a.spans = pl.spans;
+    a.params = pl.params;
+    a.state = pl.state;
+    a.out = pl.out;
+    a.in0 = pl.in0;
+    a.in1 = pl.in1;
+    a.in2 = pl.in2;
+    a.nodes = (const zcu_curve_node*)pl.aux;
+    a.smp.data = (const uint8_t*)pl.aux;
+    a.smp.len = pl.aux_len;
+    a.smp.num_channels = pl.smp_channels;
+    a.smp.sample_rate = pl.smp_rate;
+    a.smp.format = pl.smp_format;
+    if (a.V == 0 || a.frames == 0) return ZCU_OK;
+    const bool b0 = pl.in0 != nullptr, b1 = pl.in1 != nullptr, b2 = pl.in2 != nullptr;
+    switch (pl.kind) {
+        case ZCU_MOD_SINE_OSC:
+            if (b0 && b1) return launch<SineMod<true, true>>(ctx, a);
+            if (b0) return launch<SineMod<true, false>>(ctx, a);
+            if (b1) return launch<SineMod<false, true>>(ctx, a);
+            return launch<SineMod<false, false>>(ctx, a);
+        case ZCU_MOD_PULSE_OSC:
+            return b0 ? launch<PulseMod<true>>(ctx, a) : launch<PulseMod<false>>(ctx, a);
+        case ZCU_MOD_TRISAW_OSC:
+            return b0 ? launch<TriSawMod<true>>(ctx, a) : launch<TriSawMod<false>>(ctx, a);
+        case ZCU_MOD_NOISE: return launch<NoiseMod>(ctx, a);
+        case ZCU_MOD_ENVELOPE: return launch<EnvelopeMod>(ctx, a);
+        case ZCU_MOD_GATE: return launch<GateMod>(ctx, a);
+        case ZCU_MOD_FILTER:
+            if (b1 && b2) return launch<FilterMod<true, true>>(ctx, a);
+            if (b1) return launch<FilterMod<true, false>>(ctx, a);
+            if (b2) return launch<FilterMod<false, true>>(ctx, a);
+            return launch<FilterMod<false, false>>(ctx, a);
+        case ZCU_MOD_PORTAMENTO: return launch<PortamentoMod>(ctx, a);
+        case ZCU_MOD_CURVE: return launch<CurveMod>(ctx, a);
+        case ZCU_MOD_SAMPLER: return launch<SamplerMod>(ctx, a);
+        case ZCU_MOD_DECIMATOR: return launch<DecimatorMod>(ctx, a);
+        case ZCU_MOD_DISTORTION: return launch<DistortionMod>(ctx, a);
+        case ZCU_MOD_CYCLE: return b0 ? launch<CycleMod<true>>(ctx, a) : launch<CycleMod<false>>(ctx, a);
+        default: return zcu_fail(ctx, ZCU_ERR_INVALID, "unknown module kind %d", pl.kind);
+    }
+}

@@ -1,0 +1,109 @@
+// zcu_paint_kernel.cuh — the generic "lockstep" paint kernel.
+//
+// One thread per voice, 32 adjacent voices per warp, every warp walks the frame axis of the
+// [frame][voice] buffers in lockstep, so each access is one coalesced 128-byte row.  A voice's
+// spans (= the reference's paint() calls) are entered and left at the voice's own frames; module
+// state lives in registers for the whole block of buffers (Filter l/b, oscillator phase, PRNG ...).
+//
+// Memory pipeline: the strictly sequential recurrences give each warp only one sample of work at a
+// time, so HBM latency is hidden by staging tiles of T frames x 32 voices through shared memory with
+// cp.async (LDGSTS), two stages deep: while tile i is consumed, tile i+1 of the output buffer and of
+// every input buffer is in flight.  Each thread only ever reads the shared-memory words it copied
+// itself, so no block-level barrier is needed, only cp.async.wait_group.
+#pragma once
+
+#include <cuda_pipeline.h>
+
+#include "zcu_modules.cuh"
+
+namespace zcu {
+
+template <class M>
+__global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T) {
+    extern __shared__ float smem[];
+    const uint32_t tid = threadIdx.x, nt = blockDim.x;
+    const uint32_t v = blockIdx.x * nt + tid;
+    if (v >= a.V) return;  // whole-lane exit is safe: no block or warp level synchronisation below
+
+    const float* bufs[4];
+    int nb = 0;
+    const int i_out = nb;
+    bufs[nb++] = a.out;
+    int i_in0 = -1, i_in1 = -1, i_in2 = -1;
+    if (M::NIN >= 1 && a.in0) { i_in0 = nb; bufs[nb++] = a.in0; }
+    if (M::NIN >= 2 && a.in1) { i_in1 = nb; bufs[nb++] = a.in1; }
+    if (M::NIN >= 3 && a.in2) { i_in2 = nb; bufs[nb++] = a.in2; }
+
+    const size_t V = a.V;
+    // smem layout [stage][buf][T][nt]
+    auto sm = [&](uint32_t stage, int buf, uint32_t j) -> float* { return smem + ((size_t)(stage * nb + buf) * T + j) * nt + tid; };
+
+    auto issue = [&](uint32_t tile) {
+        const uint32_t f0 = tile * T;
+        const uint32_t n = min(T, a.frames - f0);
+        const uint32_t stage = tile & 1u;
+        for (int b = 0; b < nb; b++) {
+            const float* src = bufs[b] + (size_t)f0 * V + v;
+            for (uint32_t j = 0; j < n; j++) __pipeline_memcpy_async(sm(stage, b, j), src + (size_t)j * V, 4);
+        }
+        __pipeline_commit();
+    };
+
+    M m;
+    m.load(a, v);
+    uint32_t k = a.off[v];
+    const uint32_t ke = a.off[v + 1];
+    uint32_t s_start = 0xFFFFFFFFu, s_end = 0xFFFFFFFFu, s_flags = 0, s_param = 0;
+    if (k < ke) {
+        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+        s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+    }
+    bool active = false;
+
+    const uint32_t ntiles = (a.frames + T - 1) / T;
+    if (ntiles > 0) issue(0);
+    for (uint32_t tile = 0; tile < ntiles; tile++) {
+        if (tile + 1 < ntiles) {
+            issue(tile + 1);
+            __pipeline_wait_prior(1);
+        } else {
+            __pipeline_wait_prior(0);
+        }
+        const uint32_t f0 = tile * T;
+        const uint32_t n = min(T, a.frames - f0);
+        const uint32_t stage = tile & 1u;
+        if (!active && s_start >= f0 + n) continue;  // nothing of this voice in the tile
+        float* optr = a.out + (size_t)f0 * V + v;
+#pragma unroll 1
+        for (uint32_t j = 0; j < n; j++) {
+            const uint32_t f = f0 + j;
+            if (active && f == s_end) {
+                m.end_span(a);
+                active = false;
+                k++;
+                if (k < ke) {
+                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                    s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+                } else {
+                    s_start = s_end = 0xFFFFFFFFu;
+                }
+            }
+            if (!active && f == s_start) {
+                m.begin_span(a, s_param, s_flags, s_end - s_start);
+                active = true;
+            }
+            if (active) {
+                float acc = *sm(stage, i_out, j);
+                const float x0 = i_in0 >= 0 ? *sm(stage, i_in0, j) : 0.0f;
+                const float x1 = i_in1 >= 0 ? *sm(stage, i_in1, j) : 0.0f;
+                const float x2 = i_in2 >= 0 ? *sm(stage, i_in2, j) : 0.0f;
+                m.sample(acc, x0, x1, x2);
+                optr[(size_t)j * V] = acc;
+            }
+        }
+    }
+    if (active) m.end_span(a);
+    m.store(a, v);
+}
+
+}  // namespace zcu

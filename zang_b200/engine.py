@@ -1,0 +1,448 @@
+"""Host-side mirror of zang's module contract on top of the C ABI (include/zangcu.h).
+
+The reference paints ONE voice:  Module.paint(span, outputs, temps, note_id_changed, params).
+A bank paints EVERY voice of a block:  bank.paint(spans, outputs, temps, params) where `spans` is the
+table of all (span, note_id_changed, params-row) records and outputs/temps are [frame][voice] device
+buffers.  Names, argument meaning and accumulate (+=) semantics follow src/modules/*.zig.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+from ._lib import lib, ptr
+
+
+class ZangCuError(RuntimeError):
+    pass
+
+
+def _check(ctx, rc):
+    if rc != L.OK:
+        msg = lib.zcu_last_error(ctx._h if ctx is not None else None)
+        names = {1: "INVALID", 2: "NO_DEVICE", 3: "CUDA", 4: "OOM", 5: "UNSUPPORTED", 6: "NCCL"}
+        raise ZangCuError(f"zangcu error {rc} ({names.get(rc, '?')}): {msg.decode() if msg else ''}")
+
+
+class Context:
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        rc = lib.zcu_ctx_create(int(device), C.byref(h))
+        if rc == L.ERR_NO_DEVICE:
+            raise ZangCuError("no CUDA device: libzangcu has no CPU fallback")
+        if rc != L.OK:
+            raise ZangCuError(f"zcu_ctx_create failed with code {rc}")
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib.zcu_ctx_destroy(self._h)
+            self._h = None
+
+    def sync(self):
+        _check(self, lib.zcu_ctx_sync(self._h))
+
+    @property
+    def stream(self):
+        return lib.zcu_ctx_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(lib.zcu_ctx_launch_count(self._h))
+
+    def timer_start(self):
+        _check(self, lib.zcu_timer_start(self._h))
+
+    def timer_stop_ms(self):
+        ms = C.c_float()
+        _check(self, lib.zcu_timer_stop_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    # ---- buffers -------------------------------------------------------------------------------
+    def buf(self, frames, voices, data=None):
+        b = Buffer(self, frames, voices)
+        if data is not None:
+            b.upload(data)
+        return b
+
+    def wrap(self, device_ptr, frames, voices):
+        return Buffer(self, frames, voices, device_ptr=device_ptr)
+
+    def bank(self, kind, voices, first_seed=0):
+        return Bank(self, kind, voices, first_seed)
+
+    def spans(self, voices, frames, voice_off, spans):
+        return Spans(self, voices, frames, voice_off, spans)
+
+    def spans_full(self, voices, num_buffers, buffer_frames):
+        h = C.c_void_p()
+        _check(self, lib.zcu_spans_full(self._h, voices, num_buffers, buffer_frames, C.byref(h)))
+        s = Spans.__new__(Spans)
+        s.ctx, s._h, s.voices, s.frames = self, h, voices, num_buffers * buffer_frames
+        return s
+
+    def sample(self, data, num_channels, sample_rate, fmt):
+        return Sample(self, data, num_channels, sample_rate, fmt)
+
+    # ---- zang basics (src/zang/basics.zig) --------------------------------------------------------
+    def zero(self, spans, dest):
+        _check(self, lib.zcu_zero(self._h, _h(spans), dest._h))
+
+    def set(self, spans, dest, a):
+        _check(self, lib.zcu_set(self._h, _h(spans), dest._h, float(a)))
+
+    def copy(self, spans, dest, src):
+        _check(self, lib.zcu_copy(self._h, _h(spans), dest._h, src._h))
+
+    def add(self, spans, dest, a, b):
+        _check(self, lib.zcu_add(self._h, _h(spans), dest._h, a._h, b._h))
+
+    def addInto(self, spans, dest, src):
+        _check(self, lib.zcu_add_into(self._h, _h(spans), dest._h, src._h))
+
+    def addScalar(self, spans, dest, a, b):
+        _check(self, lib.zcu_add_scalar(self._h, _h(spans), dest._h, a._h, float(b)))
+
+    def addScalarInto(self, spans, dest, a):
+        _check(self, lib.zcu_add_scalar_into(self._h, _h(spans), dest._h, float(a)))
+
+    def multiply(self, spans, dest, a, b):
+        _check(self, lib.zcu_multiply(self._h, _h(spans), dest._h, a._h, b._h))
+
+    def multiplyWith(self, spans, dest, a):
+        _check(self, lib.zcu_multiply_with(self._h, _h(spans), dest._h, a._h))
+
+    def multiplyScalar(self, spans, dest, a, b):
+        _check(self, lib.zcu_multiply_scalar(self._h, _h(spans), dest._h, a._h, float(b)))
+
+    def multiplyWithScalar(self, spans, dest, a):
+        _check(self, lib.zcu_multiply_with_scalar(self._h, _h(spans), dest._h, float(a)))
+
+    # ---- mix ------------------------------------------------------------------------------------
+    def mix_reduce(self, src, gains, channels, dst):
+        g = None if gains is None else np.ascontiguousarray(gains, dtype=np.float32)
+        _check(self, lib.zcu_mix_reduce(self._h, src._h, ptr(g), channels, dst._h))
+
+    def mixDown(self, mix, audio_format, vol):
+        n = mix.frames * mix.voices * (2 if audio_format == L.AUDIO_SIGNED16_LSB else 1)
+        out = np.zeros(n, dtype=np.uint8)
+        _check(self, lib.zcu_mix_down(self._h, mix._h, audio_format, float(vol), ptr(out), n))
+        return out
+
+
+def _h(x):
+    return None if x is None else x._h
+
+
+class Buffer:
+    def __init__(self, ctx, frames, voices, device_ptr=None):
+        self.ctx, self.frames, self.voices = ctx, int(frames), int(voices)
+        h = C.c_void_p()
+        if device_ptr is None:
+            _check(ctx, lib.zcu_buf_alloc(ctx._h, self.frames, self.voices, C.byref(h)))
+        else:
+            _check(ctx, lib.zcu_buf_wrap(ctx._h, C.c_void_p(device_ptr), self.frames, self.voices, C.byref(h)))
+        self._h = h
+
+    def upload(self, data):
+        a = np.ascontiguousarray(data, dtype=np.float32)
+        assert a.shape == (self.frames, self.voices), (a.shape, self.frames, self.voices)
+        _check(self.ctx, lib.zcu_buf_upload(self.ctx._h, self._h, ptr(a)))
+        self.ctx.sync()  # `a` may be a temporary
+
+    def download(self):
+        out = np.empty((self.frames, self.voices), dtype=np.float32)
+        _check(self.ctx, lib.zcu_buf_download(self.ctx._h, self._h, ptr(out)))
+        return out
+
+    @property
+    def device_ptr(self):
+        return lib.zcu_buf_device_ptr(self._h)
+
+    def free(self):
+        if self._h:
+            lib.zcu_buf_free(self._h)
+            self._h = None
+
+
+class Bank:
+    """<Module>.init() for every voice; row v is the `self` of voice v."""
+
+    def __init__(self, ctx, kind, voices, first_seed=0):
+        self.ctx, self.kind, self.voices = ctx, kind, int(voices)
+        h = C.c_void_p()
+        _check(ctx, lib.zcu_bank_create(ctx._h, kind, self.voices, first_seed, C.byref(h)))
+        self._h = h
+
+    def get_state(self):
+        dt = L.state_dtypes[self.kind]
+        if dt is None:
+            return None
+        out = np.zeros(self.voices, dtype=dt)
+        _check(self.ctx, lib.zcu_bank_get_state(self.ctx._h, self._h, ptr(out), out.nbytes))
+        return out
+
+    def set_state(self, st):
+        st = np.ascontiguousarray(st, dtype=L.state_dtypes[self.kind])
+        _check(self.ctx, lib.zcu_bank_set_state(self.ctx._h, self._h, ptr(st), st.nbytes))
+        self.ctx.sync()
+
+    def reset(self, first_seed=0):
+        _check(self.ctx, lib.zcu_bank_reset(self.ctx._h, self._h, first_seed))
+
+    def free(self):
+        if self._h:
+            lib.zcu_bank_free(self._h)
+            self._h = None
+
+
+class Spans:
+    def __init__(self, ctx, voices, frames, voice_off, spans):
+        self.ctx, self.voices, self.frames = ctx, int(voices), int(frames)
+        off = np.ascontiguousarray(voice_off, dtype=np.uint32)
+        sp = np.ascontiguousarray(spans, dtype=L.span_dtype)
+        assert off.shape == (voices + 1,)
+        h = C.c_void_p()
+        _check(ctx, lib.zcu_spans_upload(ctx._h, self.voices, self.frames, ptr(off), ptr(sp), C.byref(h)))
+        ctx.sync()
+        self._h = h
+
+    def free(self):
+        if self._h:
+            lib.zcu_spans_free(self._h)
+            self._h = None
+
+
+class Sample:
+    """Sampler.Sample (Sampler.zig:16-21)"""
+
+    def __init__(self, ctx, data, num_channels, sample_rate, fmt):
+        self.ctx = ctx
+        d = np.ascontiguousarray(np.frombuffer(bytes(data), dtype=np.uint8))
+        h = C.c_void_p()
+        _check(ctx, lib.zcu_sample_create(ctx._h, ptr(d), d.size, num_channels, sample_rate, fmt, C.byref(h)))
+        ctx.sync()
+        self._h = h
+        self.data, self.num_channels, self.sample_rate, self.format = d, num_channels, sample_rate, fmt
+
+    def free(self):
+        if self._h:
+            lib.zcu_sample_free(self._h)
+            self._h = None
+
+
+def _params(kind, params):
+    p = np.ascontiguousarray(params, dtype=L.param_dtypes[kind])
+    return p.reshape(-1)
+
+
+class _Module:
+    """Shared shape of the module contract: num_outputs / num_temps / Params / paint."""
+    kind = None
+    num_outputs = 1
+    num_temps = 0
+
+    def __init__(self, ctx, voices, first_seed=0):
+        self.ctx = ctx
+        self.voices = voices
+        self.Params = L.param_dtypes[self.kind]
+        self.bank = Bank(ctx, self.kind, voices, first_seed) if L.state_dtypes[self.kind] is not None else None
+
+    def _bh(self):
+        return self.bank._h if self.bank is not None else None
+
+
+class SineOsc(_Module):
+    kind = L.MOD_SINE_OSC
+
+    def paint(self, spans, outputs, temps, params, freq=None, phase=None):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_sine_osc(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(freq), _h(phase)))
+
+
+class PulseOsc(_Module):
+    kind = L.MOD_PULSE_OSC
+
+    def paint(self, spans, outputs, temps, params, freq=None):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_pulse_osc(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(freq)))
+
+
+class TriSawOsc(_Module):
+    kind = L.MOD_TRISAW_OSC
+
+    def paint(self, spans, outputs, temps, params, freq=None):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_trisaw_osc(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(freq)))
+
+
+class Noise(_Module):
+    kind = L.MOD_NOISE
+
+    def paint(self, spans, outputs, temps, params):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_noise(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h))
+
+
+class Envelope(_Module):
+    kind = L.MOD_ENVELOPE
+
+    def paint(self, spans, outputs, temps, params):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_envelope(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h))
+
+
+class Gate(_Module):
+    kind = L.MOD_GATE
+
+    def paint(self, spans, outputs, temps, params):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_gate(self.ctx._h, spans._h, ptr(p), p.size, outputs[0]._h))
+
+
+class Filter(_Module):
+    kind = L.MOD_FILTER
+
+    @staticmethod
+    def cutoffFromFrequency(frequency, sample_rate):
+        return float(lib.zcu_filter_cutoff_from_frequency(float(frequency), float(sample_rate)))
+
+    def paint(self, spans, outputs, temps, params, input, cutoff=None, res=None):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_filter(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(input), _h(cutoff), _h(res)))
+
+
+class Portamento(_Module):
+    kind = L.MOD_PORTAMENTO
+
+    def paint(self, spans, outputs, temps, params):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_portamento(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h))
+
+
+class Curve(_Module):
+    kind = L.MOD_CURVE
+
+    def paint(self, spans, outputs, temps, params, nodes):
+        p = _params(self.kind, params)
+        n = np.ascontiguousarray(nodes, dtype=L.curve_node_dtype).reshape(-1)
+        _check(self.ctx, lib.zcu_paint_curve(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, ptr(n), n.size, outputs[0]._h))
+
+
+class Sampler(_Module):
+    kind = L.MOD_SAMPLER
+
+    def paint(self, spans, outputs, temps, params, sample):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_sampler(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, sample._h, outputs[0]._h))
+
+
+class Decimator(_Module):
+    kind = L.MOD_DECIMATOR
+
+    def paint(self, spans, outputs, temps, params, input):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_decimator(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(input)))
+
+
+class Distortion(_Module):
+    kind = L.MOD_DISTORTION
+
+    def paint(self, spans, outputs, temps, params, input):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_distortion(self.ctx._h, spans._h, ptr(p), p.size, outputs[0]._h, _h(input)))
+
+
+class Cycle(_Module):
+    kind = L.MOD_CYCLE
+
+    def paint(self, spans, outputs, temps, params, speed=None):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_cycle(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(speed)))
+
+
+MODULE_CLASSES = {c.kind: c for c in (SineOsc, PulseOsc, TriSawOsc, Noise, Envelope, Gate, Filter, Portamento, Curve, Sampler,
+                                      Decimator, Distortion, Cycle)}
+
+
+class NiceInstrumentBank:
+    """examples/modules.zig:189-248 composed from the module paints (the un-fused, drop-in path).
+
+    instrument params rows: (sample_rate, freq, note_on); `color` is per bank as in NiceInstrument.init.
+    """
+    num_outputs = 1
+    num_temps = 2
+    Params = np.dtype([("sample_rate", "<f4"), ("freq", "<f4"), ("note_on", "<i4")])
+
+    def __init__(self, ctx, voices, color):
+        self.ctx, self.color = ctx, float(color)
+        self.osc = PulseOsc(ctx, voices)
+        self.flt = Filter(ctx, voices)
+        self.env = Envelope(ctx, voices)
+
+    def paint(self, spans, outputs, temps, params):
+        ctx = self.ctx
+        params = np.ascontiguousarray(params, dtype=self.Params).reshape(-1)
+        n = params.size
+        pp = np.zeros(n, dtype=L.param_dtypes[L.MOD_PULSE_OSC])
+        pp["sample_rate"], pp["freq"], pp["color"] = params["sample_rate"], params["freq"], self.color
+        fp = np.zeros(n, dtype=L.param_dtypes[L.MOD_FILTER])
+        fp["type"] = L.FILTER_LOW_PASS
+        fp["cutoff"] = [Filter.cutoffFromFrequency(np.float32(f) * np.float32(8.0), sr) for f, sr in zip(params["freq"], params["sample_rate"])]
+        fp["res"] = 0.7
+        ep = np.zeros(n, dtype=L.param_dtypes[L.MOD_ENVELOPE])
+        ep["sample_rate"] = params["sample_rate"]
+        ep["attack"] = (L.CURVE_CUBED, 0.01)
+        ep["decay"] = (L.CURVE_CUBED, 0.1)
+        ep["release"] = (L.CURVE_CUBED, 0.5)
+        ep["sustain_volume"] = 0.8
+        ep["note_on"] = params["note_on"]
+        ctx.zero(spans, temps[0])
+        self.osc.paint(spans, [temps[0]], [], pp)
+        ctx.multiplyWithScalar(spans, temps[0], 0.5)
+        ctx.zero(spans, temps[1])
+        self.flt.paint(spans, [temps[1]], [], fp, input=temps[0])
+        ctx.zero(spans, temps[0])
+        self.env.paint(spans, [temps[0]], [], ep)
+        ctx.multiply(spans, outputs[0], temps[0], temps[1])
+
+
+class Render:
+    """Fused instrument bank (zcu_render_*): whole-job render of V voices into a [frames][channels] mix."""
+
+    def __init__(self, ctx, voices, total_frames, color, gains, channels=2, sample_rate=48000.0, buffer_frames=1024, block_buffers=0,
+                 instrument=L.INSTR_NICE, mode=L.RENDER_EXACT):
+        self.ctx = ctx
+        cfg = L.RenderConfig(instrument, voices, buffer_frames, total_frames, block_buffers, channels, sample_rate, 0, mode)
+        self.cfg = cfg
+        color = np.ascontiguousarray(color, dtype=np.float32)
+        gains = np.ascontiguousarray(gains, dtype=np.float32)
+        assert color.shape == (voices,) and gains.shape == (voices, channels)
+        h = C.c_void_p()
+        _check(ctx, lib.zcu_render_create(ctx._h, C.byref(cfg), ptr(color), ptr(gains), C.byref(h)))
+        ctx.sync()
+        self._h = h
+        self.voices, self.total_frames, self.channels = voices, total_frames, channels
+
+    def set_events(self, event_off, events):
+        off = np.ascontiguousarray(event_off, dtype=np.uint32)
+        ev = np.ascontiguousarray(events, dtype=L.note_event_dtype)
+        _check(self.ctx, lib.zcu_render_set_events(self.ctx._h, self._h, ptr(off), ptr(ev)))
+        # the host arrays may be temporaries: the copies are stream ordered, wait for them
+        self.ctx.sync()
+
+    def run(self, mix):
+        _check(self.ctx, lib.zcu_render_run(self.ctx._h, self._h, mix._h))
+
+    def run_voices(self, first_frame, out_voices):
+        _check(self.ctx, lib.zcu_render_run_voices(self.ctx._h, self._h, first_frame, out_voices._h))
+
+    @property
+    def launches_per_run(self):
+        return int(lib.zcu_render_launches_per_run(self._h))
+
+    def free(self):
+        if self._h:
+            lib.zcu_render_free(self._h)
+            self._h = None

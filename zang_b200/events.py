@@ -1,0 +1,120 @@
+"""Python face of the host-side event layer exported by libzangcu.so (src/zang/notes.zig, src/zang/trigger.zig).
+
+All logic lives in zang_b200/csrc/zcu_events.cpp; these classes only marshal arguments so the tests can
+be written like the reference's own (src/zang/trigger_test.zig, src/zang/notes_test.zig).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+from ._lib import lib, ptr
+
+
+class IdGenerator:
+    def __init__(self):
+        self._g = L.IdGeneratorPOD()
+        lib.zcu_id_generator_init(C.byref(self._g))
+
+    def nextId(self):
+        return int(lib.zcu_id_generator_next(C.byref(self._g)))
+
+
+class ImpulseQueue:
+    """Notes(P).ImpulseQueue: push(impulse_frame, note_id, params) / consume()."""
+
+    def __init__(self):
+        self._q = L.ImpulseQueuePOD()
+        lib.zcu_impulse_queue_init(C.byref(self._q))
+        self._rows = []  # params values by row
+
+    def push(self, impulse_frame, note_id, params):
+        before = self._q.length
+        lib.zcu_impulse_queue_push(C.byref(self._q), int(impulse_frame), int(note_id), len(self._rows))
+        if self._q.length != before:
+            self._rows.append(params)
+
+    def consume(self):
+        imp = np.zeros(32, dtype=L.impulse_dtype)
+        rows = np.zeros(32, dtype=np.uint32)
+        n = lib.zcu_impulse_queue_consume(C.byref(self._q), ptr(imp), ptr(rows))
+        params = [self._rows[r] for r in rows[:n]]
+        self._rows = []
+        return imp[:n].copy(), params
+
+
+class Trigger:
+    """Trigger(P): `run(span, impulses, params)` returns the list the reference's
+    `while (trigger.next(&ctr))` loop would yield: (start, end, params, note_id_changed)."""
+
+    def __init__(self):
+        self._t = L.TriggerPOD()
+        lib.zcu_trigger_init(C.byref(self._t))
+        self._cur = None  # params value of the carried note
+
+    def reset(self):
+        lib.zcu_trigger_reset(C.byref(self._t))
+        self._cur = None
+
+    def run(self, span, impulses, params, frame_base=0):
+        start, end = span
+        imp = np.ascontiguousarray(impulses, dtype=L.impulse_dtype).reshape(-1)
+        n = imp.size
+        # row 0 = the carried note's params, rows 1.. = this call's impulses
+        table = [self._cur] + list(params)
+        self._t.param = 0
+        rows = np.arange(1, n + 1, dtype=np.uint32)
+        out = np.zeros(n + 2, dtype=L.span_dtype)
+        cnt = lib.zcu_trigger_run(C.byref(self._t), start, end, ptr(imp), ptr(rows), n, frame_base, ptr(out), out.size)
+        assert cnt <= out.size
+        res = [(int(s["start"]), int(s["end"]), table[int(s["param"])], bool(s["flags"] & L.SPAN_NOTE_ID_CHANGED)) for s in out[:cnt]]
+        if self._t.has_note:
+            self._cur = table[self._t.param]
+        return res
+
+
+class NoteTracker:
+    """Notes(P).NoteTracker over a song = list of (t, note_id, params)."""
+
+    def __init__(self, song):
+        self._params = [e[2] for e in song]
+        self._song = np.zeros(len(song), dtype=L.song_event_dtype)
+        for i, (t, nid, _) in enumerate(song):
+            self._song[i] = (t, nid, i)
+        self._nt = L.NoteTrackerPOD()
+        lib.zcu_note_tracker_init(C.byref(self._nt), ptr(self._song), len(song))
+
+    def reset(self):
+        lib.zcu_note_tracker_reset(C.byref(self._nt))
+
+    def consume(self, sample_rate, span):
+        imp = np.zeros(32, dtype=L.impulse_dtype)
+        rows = np.zeros(32, dtype=np.uint32)
+        n = lib.zcu_note_tracker_consume(C.byref(self._nt), float(sample_rate), span[0], span[1], ptr(imp), ptr(rows), 32)
+        return imp[:n].copy(), [self._params[r] for r in rows[:n]]
+
+
+class PolyphonyDispatcher:
+    """Notes(P).PolyphonyDispatcher(polyphony); params values must expose note_on (dict key or attribute)."""
+
+    def __init__(self, polyphony):
+        self.polyphony = polyphony
+        self._pd = L.PolyDispatcherPOD()
+        rc = lib.zcu_poly_dispatcher_init(C.byref(self._pd), polyphony)
+        if rc != L.OK:
+            raise ValueError("polyphony must be 1..32")
+
+    def reset(self):
+        lib.zcu_poly_dispatcher_reset(C.byref(self._pd))
+
+    def dispatch(self, impulses, params):
+        imp = np.ascontiguousarray(impulses, dtype=L.impulse_dtype).reshape(-1)
+        n = imp.size
+        rows = np.arange(n, dtype=np.uint32)
+        on = np.array([1 if (p["note_on"] if isinstance(p, dict) else p.note_on) else 0 for p in params], dtype=np.int32)
+        oi = np.zeros((self.polyphony, 32), dtype=L.impulse_dtype)
+        op = np.zeros((self.polyphony, 32), dtype=np.uint32)
+        oc = np.zeros(self.polyphony, dtype=np.uint32)
+        rc = lib.zcu_poly_dispatcher_dispatch(C.byref(self._pd), ptr(imp), ptr(rows), ptr(on), n, ptr(oi), ptr(op), ptr(oc))
+        assert rc == L.OK
+        return [(oi[s, :oc[s]].copy(), [params[r] for r in op[s, :oc[s]]]) for s in range(self.polyphony)]
