@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py — voice-samples/s of the polyphony-bank render (BASELINE.json configs[1]) on N B200s.
+
+Workload ("step" = one whole render job): 4096 voices per GPU of NiceInstrument
+(PulseOsc -> x0.5 -> Filter low-pass res 0.7 -> x Envelope; examples/modules.zig:189-248), each voice
+driven by its own synthetic note stream through Trigger span splitting, 60 s at 48 kHz in 1024-frame
+mix buffers, summed to a stereo mix with per-voice pan gains.  With N > 1 each rank renders its own
+4096 voices (weak scaling: voices are independent, no data-path exchange) and the per-GPU partial
+mixes are summed with ONE NCCL reduce to rank 0 inside the timed region.
+
+  value  : voice-samples/s, device timed (CUDA events on the launch stream), inputs resident in HBM
+  e2e    : same metric through the C ABI from HOST buffers: H2D of the note events (pinned), render,
+           (reduce,) D2H of the stereo mix (pinned) — all inside the timed region, every step
+  roofline: algorithmic bytes (64 B per voice-sample, SURVEY.md §8d: what the reference's module chain
+           moves through its buffers) of the dominant kernel / its event-timed duration, vs the measured
+           HBM copy peak.  The fused kernel keeps the chain in registers, so `traffic` (ncu DRAM bytes)
+           is far below the algorithmic bytes and frac may exceed 1; DESIGN.md explains.
+  cpu_baseline: the oracle (C++ restatement of the reference loops; no Zig toolchain exists here) on the
+           host cores, on a bounded sample of the same workload.  Reported, not the target.
+
+`--impl reference` times that CPU path alone (rank 0 only).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+VOICES_PER_GPU = 4096
+SECONDS = 60
+SAMPLE_RATE = 48000.0
+BUFFER_FRAMES = 1024
+ALGO_BYTES_PER_VOICE_SAMPLE = 64  # zero4+Pulse8+mulScalar8+zero4+Filter12+zero4+Env8+multiply16
+METRIC = "voice-samples/sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--voices", type=int, default=VOICES_PER_GPU, help="voices per GPU (default: the BASELINE config)")
+    ap.add_argument("--seconds", type=float, default=SECONDS)
+    ap.add_argument("--block-buffers", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json, torch copy)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic_bytes_per_launch():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, if there is one."""
+    p = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except Exception:
+                continue
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for name, val in zip(names, r[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_reference_run(steps, warmup, quiet=False):
+    """The reference's CPU path (oracle port) on all host threads, bounded sample per step."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle  # noqa: E402  (bench's cpu_baseline / reference legs are allowed to execute oracle/)
+    from zang_b200 import synth
+    threads = max(1, min(32, len(os.sched_getaffinity(0))))
+    voices = 32 * threads
+    total = int(SECONDS * SAMPLE_RATE)
+    wl = synth.polyphony_bank(voices, total, SAMPLE_RATE)
+    times = []
+    for i in range(warmup + steps):
+        _, _, secs = oracle.render_nice(wl, total, SAMPLE_RATE, BUFFER_FRAMES, channels=2, nthreads=threads)
+        if i >= warmup:
+            times.append(secs)
+    t = sum(times) / len(times)
+    value = voices * total / t
+    sample = f"{voices} voices x {SECONDS} s @48 kHz NiceInstrument bank (same generator as the GPU workload), {threads} threads"
+    return {"value": value, "unit": METRIC, "cores": threads, "kind": "port", "sample": sample, "ms_per_step": t * 1e3,
+            "note": "C++ restatement of the reference's Zig paint loops (oracle/); the Zig ReleaseFast build cannot be produced here"}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    total_frames = int(args.seconds * SAMPLE_RATE)
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        res = cpu_reference_run(max(1, args.steps), max(0, args.warmup))
+        line = {"impl": "reference", "metric": METRIC, "value": res["value"], "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "polyphony bank: NiceInstrument (PulseOsc+Envelope+Filter lowpass res 0.7), 60 s @48 kHz, stereo mix",
+                           "voices_per_gpu": VOICES_PER_GPU, "note": "CPU reference arm renders a bounded sample of the same workload"},
+                "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": res["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import numpy as np
+    import torch
+    from zang_b200 import _lib as L
+    from zang_b200 import synth
+    from zang_b200.engine import Context, Render
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libzangcu has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    stream = torch.cuda.current_stream()
+    ctx = Context(local_rank, stream=stream.cuda_stream)  # every kernel, copy, event and the NCCL reduce share one stream
+
+    # ---- workload: the global bank has voices*world voices; this rank owns a contiguous shard ----
+    V = args.voices
+    wl_all = synth.polyphony_bank(V * world, total_frames, SAMPLE_RATE)
+    wl = synth.shard_voices(wl_all, rank, world)
+    n_events = int(wl["event_off"][-1])
+    # pinned host buffers for the end-to-end leg
+    ev_pinned = torch.empty(n_events * L.note_event_dtype.itemsize, dtype=torch.uint8).pin_memory()
+    ev_host = ev_pinned.numpy().view(L.note_event_dtype)
+    ev_host[:] = wl["events"]
+    off_pinned = torch.empty(V + 1, dtype=torch.int32).pin_memory()
+    off_host = off_pinned.numpy().view(np.uint32)
+    off_host[:] = wl["event_off"]
+    mix_host = torch.empty((total_frames, 2), dtype=torch.float32).pin_memory()
+
+    mix_t = torch.zeros((total_frames, 2), dtype=torch.float32, device="cuda")
+    mix = ctx.wrap(mix_t.data_ptr(), total_frames, 2)
+    r = Render(ctx, V, total_frames, wl["color"], wl["gains"], channels=2, sample_rate=SAMPLE_RATE, buffer_frames=BUFFER_FRAMES,
+               block_buffers=args.block_buffers)
+    r.set_events(off_host, ev_host)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        mix_t.zero_()
+        r.run(mix)
+        if dist is not None:
+            dist.reduce(mix_t, dst=0)
+
+    def step_e2e():
+        r.set_events(off_host, ev_host, sync=False)  # H2D from pinned memory (+ host scalars per event)
+        mix_t.zero_()
+        r.run(mix)
+        if dist is not None:
+            dist.reduce(mix_t, dst=0)
+        if rank == 0:
+            mix_host.copy_(mix_t, non_blocking=True)  # D2H of the step's result
+
+    def timed(fn, steps, profile=False):
+        """K steps between barrier+synchronize; per-step device time from CUDA events on the launch stream;
+        L2 flushed (untimed) between steps."""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        for a, b in evs:
+            flush.zero_()
+            a.record(stream)
+            fn()
+            b.record(stream)
+        barrier()
+        ms = [a.elapsed_time(b) for a, b in evs]
+        return ms
+
+    for _ in range(max(args.warmup, 0)):
+        step_resident()
+    barrier()
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launch_count
+    r.set_profiling(True)
+    ms_steps = timed(step_resident, args.steps)
+    kern_ms, kern_launches = r.kernel_ms()
+    r.set_profiling(False)
+    launches = ctx.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    for _ in range(min(2, max(args.warmup, 0))):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    # max over ranks of the mean step time
+    t_res = torch.tensor([sum(ms_steps) / len(ms_steps), sum(ms_e2e) / len(ms_e2e)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
+    ms_per_step, ms_e2e_step = float(t_res[0]), float(t_res[1])
+
+    if rank == 0:
+        voice_samples = float(V) * world * total_frames
+        value = voice_samples / (ms_per_step * 1e-3)
+        e2e_value = voice_samples / (ms_e2e_step * 1e-3)
+        peak, peak_src = measured_peak()
+        block_frames = (args.block_buffers or 64) * BUFFER_FRAMES
+        avg_launch_ms = kern_ms / max(kern_launches, 1)
+        frames_per_launch = total_frames * args.steps / max(kern_launches, 1)
+        algo_bytes_per_launch = ALGO_BYTES_PER_VOICE_SAMPLE * V * frames_per_launch
+        achieved = algo_bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9
+        traffic = ncu_traffic_bytes_per_launch()
+        h2d = n_events * L.note_event_dtype.itemsize + (V + 1) * 4 + n_events * 4  # events + offsets + per-event cutoff
+        d2h = total_frames * 2 * 4
+        line = {
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "polyphony bank: NiceInstrument (PulseOsc+Envelope+Filter lowpass res 0.7) x Trigger note streams, "
+                                   f"{args.seconds:g} s @48 kHz in 1024-frame buffers, stereo mix (BASELINE.json configs[1])",
+                       "voices_per_gpu": V, "voices_total": V * world, "frames": total_frames, "block_frames": block_frames,
+                       "parallelism": f"voices sharded over {world} GPU(s); one NCCL reduce of the stereo mix per job" if world > 1 else "1 GPU",
+                       "render_mode": "exact (bit-exact per voice vs oracle)",
+                       "l2": "flushed between timed steps (256 MiB memset, untimed)"},
+            "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": ms_e2e_step},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": "k_render_nice (fused PulseOsc+Filter+Envelope+mix, Trigger replay on device)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
+                         "algorithmic_bytes_per_launch": algo_bytes_per_launch, "avg_launch_ms": avg_launch_ms,
+                         "launches_timed": int(kern_launches), "kernel_share_of_step": kern_ms / sum(ms_steps), "peak_source": peak_src,
+                         "note": "algorithmic bytes = 64 B/voice-sample of the un-fused module chain; the fused kernel keeps them in registers"},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cb = cpu_reference_run(1, 0)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -145,6 +145,9 @@ typedef struct { float sample_rate, speed; } zcu_cycle_params;                  
 int zcu_abi_version(void);
 int zcu_device_count(void); /* 0 when no CUDA device is usable */
 int zcu_ctx_create(int device, zcu_ctx** out);
+/* same, but every call is enqueued on the caller's stream (a cudaStream_t of `device`, e.g. the host
+ * application's audio/render stream); the stream is borrowed, not owned */
+int zcu_ctx_create_on_stream(int device, void* cuda_stream, zcu_ctx** out);
 void zcu_ctx_destroy(zcu_ctx* ctx);
 int zcu_ctx_sync(zcu_ctx* ctx);
 const char* zcu_last_error(zcu_ctx* ctx); /* never NULL */
@@ -345,6 +348,11 @@ int zcu_render_run(zcu_ctx*, zcu_render*, zcu_buf* mix);
 /* optional: per-voice output (before mixing) of frames [first_frame, first_frame+out->frames) for parity tests */
 int zcu_render_run_voices(zcu_ctx*, zcu_render*, uint32_t first_frame, zcu_buf* out_voices);
 uint64_t zcu_render_launches_per_run(const zcu_render*);
+/* per-launch CUDA-event timing of the render kernel (the dominant kernel): after enabling, every
+ * zcu_render_run records an event pair around each render-kernel launch; zcu_render_kernel_ms
+ * synchronises and returns the summed duration and the number of launches since the last call. */
+int zcu_render_set_profiling(zcu_render*, int enabled);
+int zcu_render_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* launches);
 
 /* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
 /* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */

@@ -1,0 +1,110 @@
+"""The polyphony-bank workload (BASELINE.json configs[1], scaled to what the oracle renders in seconds):
+NiceInstrument (examples/modules.zig:189-248) driven by per-voice note streams through the Trigger.
+
+Three implementations must agree:
+  oracle     — per voice: ImpulseQueue -> Trigger -> NiceInstrument.paint, as example_polyphony.zig:61-92
+  un-fused   — the drop-in module path: host Trigger -> span table -> zcu_zero / zcu_paint_pulse_osc / ...
+  fused      — zcu_render_* (device-side Trigger replay, all module state in registers)
+Per-voice output is BIT-EXACT in both device paths (no transcendental is evaluated per sample; the one
+per-note cos/sqrt of Filter.cutoffFromFrequency is a host scalar in all three).  The stereo mix is held
+to 1e-5 x sum|gain| because the reference's voice summation order is not reproduced.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from helpers import assert_bit_exact, assert_close
+from zang_b200 import _lib as L
+from zang_b200 import engine as E
+from zang_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+SR = 48000.0
+
+
+def small_workload(voices, total_frames, seed=123):
+    # short notes so that attack/decay/sustain/release, retriggers and same-buffer events all occur
+    wl = synth.polyphony_bank(voices, total_frames, SR, seed=seed, mean_on=0.05, mean_off=0.03)
+    return wl
+
+
+@pytest.mark.parametrize("voices,total", [(70, 8 * 1024), (33, 5 * 1024 + 300)])
+def test_fused_voices_bit_exact(ctx, voices, total):
+    wl = small_workload(voices, total)
+    _, want, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(0, total))
+    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=3)
+    r.set_events(wl["event_off"], wl["events"])
+    vo = ctx.buf(total, voices)
+    r.run_voices(0, vo)
+    assert_bit_exact(vo.download(), want, "fused NiceInstrument voices")
+    # a window that starts mid-render (state carried through blocks that are not returned)
+    first, n = 2 * 1024 + 17, 1500
+    _, want_w, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(first, n))
+    vw = ctx.buf(n, voices)
+    r.run_voices(first, vw)
+    assert_bit_exact(vw.download(), want_w, "fused voices window")
+    r.free()
+
+
+@pytest.mark.parametrize("channels", [1, 2])
+def test_fused_mix(ctx, channels):
+    voices, total = 200, 6 * 1024 + 100
+    wl = small_workload(voices, total, seed=7)
+    gains = wl["gains"][:, :channels].copy()
+    wl2 = dict(wl, gains=gains)
+    want, _, _ = oracle.render_nice(wl2, total, SR, channels=channels)
+    r = E.Render(ctx, voices, total, wl["color"], gains, channels=channels, sample_rate=SR, block_buffers=2)
+    r.set_events(wl["event_off"], wl["events"])
+    mix = ctx.buf(total, channels)
+    r.run(mix)
+    got = mix.download()
+    assert np.abs(want).max() > 0.05
+    assert_close(got, want, 1e-5 * float(np.abs(gains).sum(axis=0).max()), "fused mix")
+    # accumulate semantics + determinism: a second run adds the identical render on top
+    r.run(mix)
+    assert_bit_exact(mix.download(), got + got, "second run must add the same bits")
+    r.free()
+
+
+def test_unfused_module_path_bit_exact(ctx):
+    """The drop-in path: every module called through its own C-ABI entry point on device buffers."""
+    voices, nbuf = 40, 6
+    total = nbuf * 1024
+    wl = small_workload(voices, total, seed=99)
+    _, want, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(0, total))
+    instr_params = np.zeros(wl["events"].size, dtype=E.NiceInstrumentBank.Params)
+    instr_params["sample_rate"] = SR
+    instr_params["freq"] = wl["events"]["freq"]
+    instr_params["note_on"] = wl["events"]["note_on"]
+    # NiceInstrument.color is per instance; the un-fused bank takes one colour, so paint voice groups by colour
+    color = np.float32(0.3)
+    wl_c = dict(wl, color=np.full(voices, color, dtype=np.float32))
+    _, want, _ = oracle.render_nice(wl_c, total, SR, want_mix=False, window=(0, total))
+    bank = E.NiceInstrumentBank(ctx, voices, color)
+    out, t0, t1 = ctx.buf(total, voices), ctx.buf(total, voices), ctx.buf(total, voices)
+    # two blocks of 3 buffers: module state and Trigger state carried across the block boundary
+    half = 3 * 1024
+    for blk in range(2):
+        off, spans = synth.spans_from_events(wl["event_off"], wl["events"], total, 1024, first_frame=blk * half, num_frames=half)
+        sp = ctx.spans(voices, half, off, spans)
+        o, a, b = ctx.buf(half, voices), ctx.buf(half, voices), ctx.buf(half, voices)
+        bank.paint(sp, [o], [a, b], instr_params)
+        got = o.download()
+        assert_bit_exact(got, want[blk * half:(blk + 1) * half], f"un-fused NiceInstrument block {blk}")
+        for x in (sp, o, a, b):
+            x.free()
+
+
+def test_render_config_errors(ctx):
+    import ctypes as C
+    from zang_b200._lib import lib, ptr
+    cfg = L.RenderConfig(L.INSTR_NICE, 8, 1024, 4096, 0, 3, SR, 0, L.RENDER_EXACT)
+    col, g = np.zeros(8, np.float32), np.zeros((8, 3), np.float32)
+    h = C.c_void_p()
+    assert lib.zcu_render_create(ctx._h, C.byref(cfg), ptr(col), ptr(g), C.byref(h)) == L.ERR_INVALID
+    cfg.channels = 2
+    assert lib.zcu_render_create(ctx._h, C.byref(cfg), ptr(col), ptr(g), C.byref(h)) == L.OK
+    mix = ctx.buf(4096, 2)
+    assert lib.zcu_render_run(ctx._h, h, mix._h) == L.ERR_INVALID  # no events yet
+    lib.zcu_render_free(h)

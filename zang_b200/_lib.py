@@ -112,6 +112,7 @@ PROTOTYPES = {
     "zcu_abi_version": (_I, []),
     "zcu_device_count": (_I, []),
     "zcu_ctx_create": (_I, [_I, _P]),
+    "zcu_ctx_create_on_stream": (_I, [_I, _P, _P]),
     "zcu_ctx_destroy": (None, [_P]),
     "zcu_ctx_sync": (_I, [_P]),
     "zcu_last_error": (C.c_char_p, [_P]),
@@ -185,6 +186,8 @@ PROTOTYPES = {
     "zcu_render_run": (_I, [_P, _P, _P]),
     "zcu_render_run_voices": (_I, [_P, _P, _U, _P]),
     "zcu_render_launches_per_run": (_U64, [_P]),
+    "zcu_render_set_profiling": (_I, [_P, _I]),
+    "zcu_render_kernel_ms": (_I, [_P, _P, _P, _P]),
     "zcu_nccl_unique_id": (_I, [_P]),
     "zcu_nccl_init": (_I, [_P, _I, _I, _P]),
     "zcu_nccl_reduce_mix": (_I, [_P, _P, _I]),

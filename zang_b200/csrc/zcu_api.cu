@@ -53,7 +53,10 @@ int zcu_device_count(void) {
     return n;
 }
 
-int zcu_ctx_create(int device, zcu_ctx** out) {
+static int ctx_create(int device, bool borrow, cudaStream_t borrowed, zcu_ctx** out);
+int zcu_ctx_create(int device, zcu_ctx** out) { return ctx_create(device, false, nullptr, out); }
+int zcu_ctx_create_on_stream(int device, void* cuda_stream, zcu_ctx** out) { return ctx_create(device, true, (cudaStream_t)cuda_stream, out); }
+static int ctx_create(int device, bool borrow, cudaStream_t borrowed, zcu_ctx** out) {
     if (!out) return ZCU_ERR_INVALID;
     *out = nullptr;
     int n = zcu_device_count();
@@ -62,7 +65,9 @@ int zcu_ctx_create(int device, zcu_ctx** out) {
     zcu_ctx* ctx = new (std::nothrow) zcu_ctx();
     if (!ctx) return ZCU_ERR_OOM;
     ctx->device = device;
-    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    ctx->own_stream = !borrow;
+    if (borrow) ctx->stream = borrowed;
+    if (cudaSetDevice(device) != cudaSuccess || (!borrow && cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
         cudaGetLastError();
         delete ctx;
@@ -81,12 +86,12 @@ int zcu_ctx_create(int device, zcu_ctx** out) {
 void zcu_ctx_destroy(zcu_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 4; i++)
         if (ctx->arena[i]) cudaFree(ctx->arena[i]);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->stream && ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 

@@ -12,6 +12,7 @@
 struct zcu_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    bool own_stream = true;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::string err = "";
     uint64_t launches = 0;

@@ -44,6 +44,9 @@ struct zcu_render {
     float* d_cutoff;       // per event: Filter.cutoffFromFrequency(freq*8, sr) evaluated on the host
     uint32_t nevents;
     float* d_partial;      // [nwarps][block_frames][C]
+    bool profiling;
+    std::vector<cudaEvent_t> ev;   // pairs around every render-kernel launch since the last query
+    size_t ev_used;
 };
 
 namespace {
@@ -285,10 +288,22 @@ int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t
                 k_render_nice<1, true><<<r->nwarps, 32, 0, ctx->stream>>>(a);
             ctx->launches++;
         } else {
+            if (r->profiling) {
+                if (r->ev_used + 2 > r->ev.size()) {
+                    r->ev.resize(r->ev_used + 2, nullptr);
+                    ZCU_CUDA(ctx, cudaEventCreate(&r->ev[r->ev_used]));
+                    ZCU_CUDA(ctx, cudaEventCreate(&r->ev[r->ev_used + 1]));
+                }
+                ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used], ctx->stream));
+            }
             if (c.channels == 2)
                 k_render_nice<2, false><<<r->nwarps, 32, 0, ctx->stream>>>(a);
             else
                 k_render_nice<1, false><<<r->nwarps, 32, 0, ctx->stream>>>(a);
+            if (r->profiling) {
+                ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used + 1], ctx->stream));
+                r->ev_used += 2;
+            }
             const size_t n = (size_t)(a.F1 - a.F0) * c.channels;
             k_partial_reduce<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(r->d_partial, mix + (size_t)F0 * c.channels, r->nwarps, n);
             ctx->launches += 2;
@@ -312,7 +327,13 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     ZCU_REQUIRE(ctx, cfg->mode == ZCU_RENDER_EXACT, "only ZCU_RENDER_EXACT is implemented");
     zcu_render* r = new (std::nothrow) zcu_render();
     if (!r) return ZCU_ERR_OOM;
-    *r = zcu_render{};
+    r->d_color = r->d_gains = r->d_cutoff = r->d_partial = nullptr;
+    r->d_state = nullptr;
+    r->d_event_off = nullptr;
+    r->d_events = nullptr;
+    r->nevents = 0;
+    r->profiling = false;
+    r->ev_used = 0;
     r->ctx = ctx;
     r->cfg = *cfg;
     const uint32_t bb = cfg->block_buffers ? cfg->block_buffers : 64;
@@ -345,6 +366,8 @@ void zcu_render_free(zcu_render* r) {
     cudaFree(r->d_events);
     cudaFree(r->d_cutoff);
     cudaFree(r->d_partial);
+    for (cudaEvent_t e : r->ev)
+        if (e) cudaEventDestroy(e);
     delete r;
 }
 
@@ -390,6 +413,29 @@ int zcu_render_run_voices(zcu_ctx* ctx, zcu_render* r, uint32_t first_frame, zcu
     ZCU_REQUIRE(ctx, out_voices->voices == r->cfg.voices, "out_voices must be [frames][voices]");
     ZCU_REQUIRE(ctx, (uint64_t)first_frame + out_voices->frames <= r->cfg.total_frames, "window beyond the render");
     return render_blocks(ctx, r, nullptr, out_voices->d, first_frame, out_voices->frames, first_frame + out_voices->frames);
+}
+
+int zcu_render_set_profiling(zcu_render* r, int enabled) {
+    if (!r) return ZCU_ERR_INVALID;
+    r->profiling = enabled != 0;
+    r->ev_used = 0;
+    return ZCU_OK;
+}
+
+int zcu_render_kernel_ms(zcu_ctx* ctx, zcu_render* r, float* total_ms, uint32_t* launches) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, r && total_ms && launches, "null argument");
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    double sum = 0.0;
+    for (size_t i = 0; i + 1 < r->ev_used; i += 2) {
+        float ms = 0.0f;
+        ZCU_CUDA(ctx, cudaEventElapsedTime(&ms, r->ev[i], r->ev[i + 1]));
+        sum += ms;
+    }
+    *total_ms = (float)sum;
+    *launches = (uint32_t)(r->ev_used / 2);
+    r->ev_used = 0;
+    return ZCU_OK;
 }
 
 uint64_t zcu_render_launches_per_run(const zcu_render* r) {

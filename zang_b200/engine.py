@@ -25,9 +25,12 @@ def _check(ctx, rc):
 
 
 class Context:
-    def __init__(self, device=0):
+    def __init__(self, device=0, stream=None):
         h = C.c_void_p()
-        rc = lib.zcu_ctx_create(int(device), C.byref(h))
+        if stream is None:
+            rc = lib.zcu_ctx_create(int(device), C.byref(h))
+        else:
+            rc = lib.zcu_ctx_create_on_stream(int(device), C.c_void_p(stream), C.byref(h))
         if rc == L.ERR_NO_DEVICE:
             raise ZangCuError("no CUDA device: libzangcu has no CPU fallback")
         if rc != L.OK:
@@ -425,18 +428,27 @@ class Render:
         self._h = h
         self.voices, self.total_frames, self.channels = voices, total_frames, channels
 
-    def set_events(self, event_off, events):
+    def set_events(self, event_off, events, sync=True):
         off = np.ascontiguousarray(event_off, dtype=np.uint32)
         ev = np.ascontiguousarray(events, dtype=L.note_event_dtype)
         _check(self.ctx, lib.zcu_render_set_events(self.ctx._h, self._h, ptr(off), ptr(ev)))
-        # the host arrays may be temporaries: the copies are stream ordered, wait for them
-        self.ctx.sync()
+        if sync:  # the host arrays may be temporaries: the copies are stream ordered, wait for them
+            self.ctx.sync()
 
     def run(self, mix):
         _check(self.ctx, lib.zcu_render_run(self.ctx._h, self._h, mix._h))
 
     def run_voices(self, first_frame, out_voices):
         _check(self.ctx, lib.zcu_render_run_voices(self.ctx._h, self._h, first_frame, out_voices._h))
+
+    def set_profiling(self, enabled=True):
+        _check(self.ctx, lib.zcu_render_set_profiling(self._h, 1 if enabled else 0))
+
+    def kernel_ms(self):
+        """(summed render-kernel milliseconds, launches) since the last call; synchronises."""
+        ms, n = C.c_float(), C.c_uint32()
+        _check(self.ctx, lib.zcu_render_kernel_ms(self.ctx._h, self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     @property
     def launches_per_run(self):
