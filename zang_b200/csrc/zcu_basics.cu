@@ -262,12 +262,12 @@ int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed) {
 }
 
 int zcu_selftest_no_fma(zcu_ctx* ctx) {
-    // a = 1 + 2^-12, b = 1 - 2^-12: a*b = 1 - 2^-24 exactly, which rounds to 1.0f;  c = -1:
-    // unfused -> 0, fused -> -2^-24.
+    // a = b = 1 + 2^-12: a*b = 1 + 2^-11 + 2^-24, a tie that rounds to 1 + 2^-11 in f32;
+    // c = -(1 + 2^-11): unfused -> 0, fused -> 2^-24.
     float* d = nullptr;
     int rc = zcu_arena_reserve(ctx, 0, sizeof(float), (void**)&d);
     if (rc) return rc;
-    k_fma_probe<<<1, 1, 0, ctx->stream>>>(1.0f + 0x1p-12f, 1.0f - 0x1p-12f, -1.0f, d);
+    k_fma_probe<<<1, 1, 0, ctx->stream>>>(1.0f + 0x1p-12f, 1.0f + 0x1p-12f, -(1.0f + 0x1p-11f), d);
     ctx->launches++;
     float h = 1.0f;
     ZCU_CUDA(ctx, cudaMemcpyAsync(&h, d, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
