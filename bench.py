@@ -270,7 +270,7 @@ def main():
         algo_bytes_per_launch = ALGO_BYTES_PER_VOICE_SAMPLE * V * frames_per_launch
         achieved = algo_bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9
         traffic = ncu_traffic_bytes_per_launch()
-        h2d = n_events * L.note_event_dtype.itemsize + (V + 1) * 4 + n_events * 4  # events + offsets + per-event cutoff
+        h2d = n_events * 32 + (V + 1) * 4  # device event records (note event + host-evaluated cutoff, 32 B) + offsets
         d2h = total_frames * 2 * 4
         line = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

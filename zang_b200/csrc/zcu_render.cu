@@ -12,24 +12,14 @@
 // row of partial mix per 32 frames.  A second kernel adds the per-warp partials in fixed order
 // (deterministic) into the mix.
 #include <cmath>
+#include <cstdlib>
 #include <new>
 #include <vector>
 
 #include "zcu_internal.h"
-#include "zcu_modules.cuh"
+#include "zcu_render_kernel.cuh"
 
 using namespace zcu;
-
-struct NiceVoiceState {
-    uint32_t cnt;                                // PulseOsc.cnt
-    float l, b;                                  // Filter.l/.b
-    int32_t env_state;                           // Envelope.state
-    float env_t, env_last, env_start;            // Envelope.painter
-    int32_t has_note;                            // Trigger.note != null
-    uint32_t note_id;                            // Trigger.note.id
-    uint32_t cur_event;                          // Trigger.note.params (row = event index)
-    uint32_t next_event;                         // ImpulseQueue read cursor
-};
 
 struct zcu_render {
     zcu_ctx* ctx;
@@ -40,203 +30,18 @@ struct zcu_render {
     float* d_gains;        // [V][C]
     NiceVoiceState* d_state;
     uint32_t* d_event_off; // [V+1]
-    zcu_note_event* d_events;
-    float* d_cutoff;       // per event: Filter.cutoffFromFrequency(freq*8, sr) evaluated on the host
+    DevEvent* d_events;    // per event, with Filter.cutoffFromFrequency(freq*8, sr) evaluated on the host
+    DevEvent* h_events;    // pinned staging for the H2D copy
     uint32_t nevents;
     float* d_partial;      // [nwarps][block_frames][C]
+    uint32_t debug_skip_mask;
+    unsigned long long* d_debug_cycles;  // [nwarps][4][2], only with ZCU_RENDER_DEBUG_CYCLES=1
     bool profiling;
     std::vector<cudaEvent_t> ev;   // pairs around every render-kernel launch since the last query
     size_t ev_used;
 };
 
 namespace {
-
-struct RenderArgs {
-    uint32_t V, C;
-    uint32_t buffer_frames, total_frames;
-    uint32_t F0, F1;  // frames of this launch
-    float sample_rate;
-    const float* color;
-    const float* gains;
-    NiceVoiceState* state;
-    const uint32_t* event_off;
-    const zcu_note_event* events;
-    const float* cutoff;
-    float* partial;   // [nwarps][F1-F0][C] or null
-    float* vout;      // [vout_frames][V] window or null
-    uint32_t vout_first, vout_frames;
-};
-
-// NiceInstrument (examples/modules.zig:189-248) for one voice
-struct NiceVoice {
-    // PulseOsc (constant frequency path, PulseOsc.zig:75-114)
-    uint32_t cnt, ifreq, brpt, pstate;
-    float gdf2, col, cc121, cc212;
-    bool pskip;
-    FilterCore flt;
-    EnvelopeCore env;
-
-    __device__ void begin_span(float sample_rate, float freq, float cutoff, bool note_on, bool note_id_changed) {
-        const float gain = 0.7f;
-        pskip = (freq < 0.0f || freq > sample_rate / 8.0f);
-        if (!pskip) {
-            const float basefrq = 4294967296.0f / sample_rate;
-            ifreq = (uint32_t)(basefrq * freq);
-            const float gdf = gain / utof23(ifreq);
-            gdf2 = gdf * 2.0f;
-            cc121 = gdf2 * (col - 1.0f) + gain;
-            cc212 = gdf2 * col - gain;
-            pstate = ((uint32_t)(cnt - ifreq) < brpt) ? 3u : 0u;
-        }
-        flt.set_type(ZCU_FILTER_LOW_PASS);             // modules.zig:230
-        flt.cut = zclamp(cutoff, 0.0f, 1.0f);          // Filter.zig:114
-        flt.res = 1.0f - zclamp(0.7f, 0.0f, 1.0f);     // modules.zig:235, Filter.zig:118
-        zcu_envelope_params ep;                        // modules.zig:238-245
-        ep.sample_rate = sample_rate;
-        ep.attack.kind = ZCU_CURVE_CUBED;  ep.attack.duration = 0.01f;
-        ep.decay.kind = ZCU_CURVE_CUBED;   ep.decay.duration = 0.1f;
-        ep.release.kind = ZCU_CURVE_CUBED; ep.release.duration = 0.5f;
-        ep.sustain_volume = 0.8f;
-        ep.note_on = note_on ? 1 : 0;
-        env.begin(ep, note_id_changed);
-    }
-    __device__ __forceinline__ float sample() {
-        const float gain = 0.7f;
-        // zero(temps[0]); osc.paint -> temps[0]
-        float t0 = 0.0f;
-        if (!pskip) {
-            pstate = ((pstate << 1) | (cnt < brpt ? 1u : 0u)) & 3u;
-            const uint32_t transition = pstate | ((cnt < ifreq ? 1u : 0u) << 2);
-            const float p = utof23(cnt);
-            float v;
-            switch (transition) {
-                case 3: v = gain; break;
-                case 0: v = -gain; break;
-                case 2: v = gdf2 * (col - p) + gain; break;
-                case 5: v = gdf2 * p - gain; break;
-                case 7: v = cc121; break;
-                case 4: v = cc212; break;
-                default: v = 0.0f; break;
-            }
-            t0 += v;
-            cnt += ifreq;
-        }
-        t0 *= 0.5f;                        // multiplyWithScalar(temps[0], 0.5)
-        float t1 = 0.0f;                   // zero(temps[1])
-        t1 += flt.step(t0);                // flt.paint -> temps[1]
-        float e = 0.0f;                    // zero(temps[0])
-        env.sample(e);                     // env.paint -> temps[0]
-        return e * t1;                     // multiply(outputs[0], temps[0], temps[1]) adds this product
-    }
-};
-
-template <int C, bool VOUT>
-__global__ void __launch_bounds__(32) k_render_nice(RenderArgs a) {
-    __shared__ float tile[32 * 33];
-    __shared__ float g[2][32];
-    const uint32_t lane = threadIdx.x;
-    const uint32_t v = blockIdx.x * 32 + lane;
-    const bool valid = v < a.V;
-
-    NiceVoice nv;
-    NiceVoiceState st;
-    uint32_t ev_end = 0;
-    if (valid) {
-        st = a.state[v];
-        ev_end = a.event_off[v + 1];
-        const float color = a.color[v];
-        nv.brpt = ftou32(clamp01(color));
-        nv.col = utof23(nv.brpt);
-        nv.cnt = st.cnt;
-        nv.flt.l = st.l;
-        nv.flt.b = st.b;
-        nv.env.state = st.env_state;
-        nv.env.painter.t = st.env_t;
-        nv.env.painter.last_value = st.env_last;
-        nv.env.painter.start = st.env_start;
-        nv.env.mode = EnvelopeCore::M_NONE;
-        for (int c = 0; c < C; c++) g[c][lane] = a.gains[(size_t)v * C + c];
-    } else {
-        st = NiceVoiceState{};
-        for (int c = 0; c < C; c++) g[c][lane] = 0.0f;
-    }
-    __syncwarp();
-
-    bool active = false;
-    uint32_t boundary = valid ? a.F0 : 0xFFFFFFFFu;
-    uint32_t buf_end = a.F0;
-
-    for (uint32_t tf = a.F0; tf < a.F1; tf += 32) {
-        const uint32_t n = min(32u, a.F1 - tf);
-#pragma unroll 1
-        for (uint32_t j = 0; j < n; j++) {
-            const uint32_t f = tf + j;
-            if (f == boundary) {
-                // ---- Trigger replay (trigger.zig:80-196) at a span boundary ----
-                active = false;
-                if (f == buf_end) buf_end = min(f + a.buffer_frames, a.total_frames);  // next mix buffer
-                bool got = false;
-                uint32_t cand = 0;
-                while (st.next_event < ev_end && a.events[st.next_event].frame <= f) {  // same frame: the last one wins
-                    cand = st.next_event++;
-                    got = true;
-                }
-                bool changed = false;
-                if (got) {
-                    const uint32_t id = a.events[cand].note_id;
-                    changed = st.has_note ? (id != st.note_id) : true;
-                    st.has_note = 1;
-                    st.note_id = id;
-                    st.cur_event = cand;
-                }
-                if (st.has_note) {
-                    const zcu_note_event ev = a.events[st.cur_event];
-                    nv.begin_span(a.sample_rate, ev.freq, a.cutoff[st.cur_event], ev.note_on != 0, changed);
-                    active = true;
-                }
-                uint32_t nb = buf_end;
-                if (st.next_event < ev_end) nb = min(nb, a.events[st.next_event].frame);
-                boundary = nb;
-            }
-            float o = 0.0f;
-            if (active) o = nv.sample();
-            tile[j * 33 + lane] = o;
-            if (VOUT) {
-                if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames) a.vout[(size_t)(f - a.vout_first) * a.V + v] = o;
-            }
-        }
-        if (!VOUT) {
-            __syncwarp();
-            if (lane < n) {
-                float acc[C];
-#pragma unroll
-                for (int c = 0; c < C; c++) acc[c] = 0.0f;
-#pragma unroll 8
-                for (int vv = 0; vv < 32; vv++) {
-                    const float x = tile[lane * 33 + vv];
-#pragma unroll
-                    for (int c = 0; c < C; c++) acc[c] = fmaf(g[c][vv], x, acc[c]);  // mix order is not pinned by the reference
-                }
-                float* dst = a.partial + ((size_t)blockIdx.x * (a.F1 - a.F0) + (tf - a.F0 + lane)) * C;
-                if (C == 2)
-                    *reinterpret_cast<float2*>(dst) = make_float2(acc[0], acc[1]);
-                else
-                    dst[0] = acc[0];
-            }
-            __syncwarp();
-        }
-    }
-    if (valid) {
-        st.cnt = nv.cnt;
-        st.l = nv.flt.l;
-        st.b = nv.flt.b;
-        st.env_state = nv.env.state;
-        st.env_t = nv.env.painter.t;
-        st.env_last = nv.env.painter.last_value;
-        st.env_start = nv.env.painter.start;
-        a.state[v] = st;
-    }
-}
 
 // mix[F0+f][c] += sum over warps (fixed order) of partial[w][f][c]
 __global__ void __launch_bounds__(256) k_partial_reduce(const float* __restrict__ partial, float* __restrict__ mix, uint32_t nwarps,
@@ -276,16 +81,27 @@ int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t
         a.state = r->d_state;
         a.event_off = r->d_event_off;
         a.events = r->d_events;
-        a.cutoff = r->d_cutoff;
         a.partial = r->d_partial;
         a.vout = vout;
         a.vout_first = vout_first;
         a.vout_frames = vout_frames;
+        a.debug_skip_mask = r->debug_skip_mask;
+        a.debug_cycles = r->d_debug_cycles;
+        constexpr int RT = 128;
+        const size_t smem = render_smem_bytes<RT>();
+        static bool attr_set = false;
+        if (!attr_set) {
+            ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<1, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<2, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set = true;
+        }
         if (vout) {
             if (c.channels == 2)
-                k_render_nice<2, true><<<r->nwarps, 32, 0, ctx->stream>>>(a);
+                k_render_nice<2, true, RT><<<r->nwarps, 128, smem, ctx->stream>>>(a);
             else
-                k_render_nice<1, true><<<r->nwarps, 32, 0, ctx->stream>>>(a);
+                k_render_nice<1, true, RT><<<r->nwarps, 128, smem, ctx->stream>>>(a);
             ctx->launches++;
         } else {
             if (r->profiling) {
@@ -297,9 +113,9 @@ int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t
                 ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used], ctx->stream));
             }
             if (c.channels == 2)
-                k_render_nice<2, false><<<r->nwarps, 32, 0, ctx->stream>>>(a);
+                k_render_nice<2, false, RT><<<r->nwarps, 128, smem, ctx->stream>>>(a);
             else
-                k_render_nice<1, false><<<r->nwarps, 32, 0, ctx->stream>>>(a);
+                k_render_nice<1, false, RT><<<r->nwarps, 128, smem, ctx->stream>>>(a);
             if (r->profiling) {
                 ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used + 1], ctx->stream));
                 r->ev_used += 2;
@@ -327,13 +143,17 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     ZCU_REQUIRE(ctx, cfg->mode == ZCU_RENDER_EXACT, "only ZCU_RENDER_EXACT is implemented");
     zcu_render* r = new (std::nothrow) zcu_render();
     if (!r) return ZCU_ERR_OOM;
-    r->d_color = r->d_gains = r->d_cutoff = r->d_partial = nullptr;
+    r->d_color = r->d_gains = r->d_partial = nullptr;
+    r->h_events = nullptr;
     r->d_state = nullptr;
     r->d_event_off = nullptr;
     r->d_events = nullptr;
     r->nevents = 0;
     r->profiling = false;
     r->ev_used = 0;
+    r->debug_skip_mask = 0;
+    r->d_debug_cycles = nullptr;
+    if (const char* m = getenv("ZCU_RENDER_DEBUG_SKIP_MASK")) r->debug_skip_mask = (uint32_t)atoi(m);  // profiling aid, wrong results
     r->ctx = ctx;
     r->cfg = *cfg;
     const uint32_t bb = cfg->block_buffers ? cfg->block_buffers : 64;
@@ -352,6 +172,10 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_color, voice_color_host, (size_t)V * 4, cudaMemcpyHostToDevice, ctx->stream));
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_gains, gains_host, (size_t)V * C * 4, cudaMemcpyHostToDevice, ctx->stream));
     ZCU_CUDA(ctx, cudaMemsetAsync(r->d_event_off, 0, (size_t)(V + 1) * 4, ctx->stream));
+    if (getenv("ZCU_RENDER_DEBUG_CYCLES")) {  // profiling aid: per-stage busy/total cycles, printed at zcu_render_free
+        ZCU_CUDA(ctx, cudaMalloc(&r->d_debug_cycles, (size_t)r->nwarps * 8 * sizeof(unsigned long long)));
+        ZCU_CUDA(ctx, cudaMemsetAsync(r->d_debug_cycles, 0, (size_t)r->nwarps * 8 * sizeof(unsigned long long), ctx->stream));
+    }
     *out = r;
     return ZCU_OK;
 }
@@ -359,12 +183,25 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
 void zcu_render_free(zcu_render* r) {
     if (!r) return;
     if (r->ctx) cudaStreamSynchronize(r->ctx->stream);
+    if (r->d_debug_cycles) {
+        std::vector<unsigned long long> h((size_t)r->nwarps * 8);
+        cudaMemcpy(h.data(), r->d_debug_cycles, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+        double busy[4] = {0, 0, 0, 0}, tot[4] = {0, 0, 0, 0};
+        for (uint32_t c = 0; c < r->nwarps; c++)
+            for (int w = 0; w < 4; w++) {
+                busy[w] += (double)h[((size_t)c * 4 + w) * 2];
+                tot[w] += (double)h[((size_t)c * 4 + w) * 2 + 1];
+            }
+        fprintf(stderr, "[zcu_render debug] stage busy fraction of kernel time: pulse %.3f filter %.3f env %.3f mix %.3f (cycles total/CTA %.3g)\n",
+                busy[0] / tot[0], busy[1] / tot[1], busy[2] / tot[2], busy[3] / tot[3], tot[0] / r->nwarps);
+        cudaFree(r->d_debug_cycles);
+    }
     cudaFree(r->d_color);
     cudaFree(r->d_gains);
     cudaFree(r->d_state);
     cudaFree(r->d_event_off);
     cudaFree(r->d_events);
-    cudaFree(r->d_cutoff);
+    cudaFreeHost(r->h_events);
     cudaFree(r->d_partial);
     for (cudaEvent_t e : r->ev)
         if (e) cudaEventDestroy(e);
@@ -380,21 +217,27 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     if (n > r->nevents || !r->d_events) {
         ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(r->d_events);
-        cudaFree(r->d_cutoff);
+        cudaFreeHost(r->h_events);
         r->d_events = nullptr;
-        r->d_cutoff = nullptr;
-        ZCU_CUDA(ctx, cudaMalloc(&r->d_events, (size_t)(n ? n : 1) * sizeof(zcu_note_event)));
-        ZCU_CUDA(ctx, cudaMalloc(&r->d_cutoff, (size_t)(n ? n : 1) * sizeof(float)));
+        r->h_events = nullptr;
+        ZCU_CUDA(ctx, cudaMalloc(&r->d_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
+        ZCU_CUDA(ctx, cudaMallocHost(&r->h_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
+    } else {
+        ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the staging buffer may still be in flight
     }
     r->nevents = n;
     // per-call host scalar of modules.zig:231-234 (cos, sqrt): once per event, on the host
-    std::vector<float> cutoff(n);
-    for (uint32_t i = 0; i < n; i++) cutoff[i] = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, r->cfg.sample_rate);
-    ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    if (n) {
-        ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, events_host, (size_t)n * sizeof(zcu_note_event), cudaMemcpyHostToDevice, ctx->stream));
-        ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_cutoff, cutoff.data(), (size_t)n * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    for (uint32_t i = 0; i < n; i++) {
+        DevEvent& d = r->h_events[i];
+        d.frame = events_host[i].frame;
+        d.note_id = events_host[i].note_id;
+        d.freq = events_host[i].freq;
+        d.note_on = events_host[i].note_on;
+        d.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, r->cfg.sample_rate);
+        d.pad[0] = d.pad[1] = d.pad[2] = 0;
     }
+    ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, r->h_events, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
     return ZCU_OK;
 }
 
