@@ -1,0 +1,85 @@
+"""Regenerates tests/golden/oracle_golden.json from the oracle (oracle/zang_oracle.hpp).
+
+The reference pins no paint() output, and it cannot be executed here (Zig, no toolchain), so
+these vectors do not pin the oracle to the reference; they pin the oracle to ITSELF across rounds (any edit
+that changes a single output bit of any module shows up) and record short literal excerpts a reader can check
+by hand against the Zig source.
+Run:  python tests/golden/make_golden.py
+"""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+import cases  # noqa: E402
+import oracle  # noqa: E402
+from zang_b200 import _lib as L  # noqa: E402
+from zang_b200 import synth  # noqa: E402
+
+
+def digest(*arrays):
+    h = hashlib.sha256()
+    for a in arrays:
+        if a is not None:
+            h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def module_cases():
+    out = {}
+    for case in cases.CASES:
+        name, kind = case[0], case[1]
+        rng = cases.case_rng(name)
+        st = oracle.state_init(kind, cases.V, 5)
+        for blk in range(2):
+            off, spans, params, out0, inputs = cases.gen_block(case, rng)
+            want = out0.copy()
+            oracle.paint(kind, off, spans, params, st, want, *inputs)
+            out[f"{name}/block{blk}"] = digest(want, st)
+    return out
+
+
+def excerpts():
+    """Short literal vectors: one voice, one full-buffer span, simple params."""
+    ex = {}
+    off = np.array([0, 1], dtype=np.uint32)
+    spans = np.array([(0, 16, 1, 0)], dtype=L.span_dtype)
+
+    def run(kind, params, **kw):
+        out = np.zeros((16, 1), dtype=np.float32)
+        st = oracle.state_init(kind, 1, 0)
+        oracle.paint(kind, off, spans, np.array([params], dtype=L.param_dtypes[kind]), st, out, **kw)
+        return [float(x) for x in out[:, 0]]
+
+    ex["pulse 440Hz color 0.3 @48k"] = run(L.MOD_PULSE_OSC, (48000.0, 440.0, 0.3))
+    ex["trisaw 440Hz color 0.5 @48k"] = run(L.MOD_TRISAW_OSC, (48000.0, 440.0, 0.5))
+    ex["noise white seed 0"] = run(L.MOD_NOISE, (L.NOISE_WHITE,))
+    ex["noise pink seed 0"] = run(L.MOD_NOISE, (L.NOISE_PINK,))
+    ex["envelope attack cubed 0.0002s"] = run(L.MOD_ENVELOPE, (48000.0, (3, 0.0002), (3, 0.0001), (3, 0.5), 0.8, 1))
+    ex["cycle speed 4800"] = run(L.MOD_CYCLE, (48000.0, 4800.0))
+    step = np.zeros((16, 1), dtype=np.float32)
+    step[4:] = 1.0
+    ex["filter lowpass cutoff 0.2 res 0.7 step"] = run(L.MOD_FILTER, (L.FILTER_LOW_PASS, 0.2, 0.7), in0=step)
+    return ex
+
+
+def render_case():
+    wl = synth.polyphony_bank(24, 6 * 1024, 48000.0, seed=42, mean_on=0.04, mean_off=0.02)
+    mix, vo, _ = oracle.render_nice(wl, 6 * 1024, window=(0, 6 * 1024))
+    return {"workload": digest(wl["event_off"], wl["events"], wl["color"], wl["gains"]), "voices": digest(vo), "mix": digest(mix)}
+
+
+def build():
+    return {"modules": module_cases(), "excerpts": excerpts(), "render_nice": render_case()}
+
+
+if __name__ == "__main__":
+    with open(os.path.join(HERE, "oracle_golden.json"), "w") as f:
+        json.dump(build(), f, indent=1, sort_keys=True)
+    print("written")

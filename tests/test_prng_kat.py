@@ -1,0 +1,76 @@
+"""Known-answer tests for the arithmetic that lives OUTSIDE /root/reference: Zig std's DefaultPrng
+(xoshiro256++ seeded through SplitMix64) and Random.float(f32), used by src/modules/Noise.zig:22-29,51,58.
+
+The reference pins none of this with a test of its own.  Anchors used here:
+  * xoshiro256++ seeded with SplitMix64(0): the Zig std test vector quoted in SURVEY.md §8(c)
+  * SplitMix64(seed = 1234567) first outputs: the reference vector of the public-domain splitmix64.c
+  * the float conversion: structural properties (range, mantissa = low 23 bits, exponent from the leading zeros)
+"""
+import numpy as np
+
+import oracle
+from zang_b200 import _lib as L
+
+ptr = L.ptr
+
+XOSHIRO_SEED0 = [0x53175d61490b23df, 0x61da6f3dc380d507, 0x5c0fdf91ec9a7bfc, 0x02eebf8c3bbe5e1a, 0x7eca04ebaf4a5eea, 0x0543c37757f08d9a]
+
+
+def splitmix(seed, n):
+    out, s, M = [], seed, (1 << 64) - 1
+    for _ in range(n):
+        s = (s + 0x9e3779b97f4a7c15) & M
+        z = s
+        z = ((z ^ (z >> 30)) * 0xbf58476d1ce4e5b9) & M
+        z = ((z ^ (z >> 27)) * 0x94d049bb133111eb) & M
+        out.append(z ^ (z >> 31))
+    return out
+
+
+def test_splitmix64_reference_vector():
+    # splitmix64.c (Vigna), seed 1234567
+    assert splitmix(1234567, 5) == [6457827717110365317, 3203168211198807973, 9817491932198370423, 4593380528125082431, 16408922859458223821]
+
+
+def test_xoshiro_seed_is_splitmix():
+    s = np.zeros(4, dtype=np.uint64)
+    for seed in (0, 1, 5, 4095, 2 ** 32 - 1):
+        oracle.orc.orc_xoshiro_seed(seed, ptr(s))
+        assert [int(x) for x in s] == splitmix(seed, 4)
+
+
+def test_xoshiro256pp_zig_std_vector():
+    s = np.zeros(4, dtype=np.uint64)
+    oracle.orc.orc_xoshiro_seed(0, ptr(s))
+    out = np.zeros(6, dtype=np.uint64)
+    oracle.orc.orc_xoshiro_next(ptr(s), ptr(out), 6)
+    assert [int(x) for x in out] == XOSHIRO_SEED0
+
+
+def py_float32(r):
+    lz = 64 - r.bit_length()
+    assert lz < 41  # the >= 41 branch has probability 2^-41 per draw
+    bits = ((126 - lz) << 23) | (r & 0x7FFFFF)
+    return np.array([bits], dtype=np.uint32).view(np.float32)[0]
+
+
+def test_float_conversion_structure():
+    s = np.zeros(4, dtype=np.uint64)
+    oracle.orc.orc_xoshiro_seed(7, ptr(s))
+    s2 = s.copy()
+    raw = np.zeros(4096, dtype=np.uint64)
+    oracle.orc.orc_xoshiro_next(ptr(s), ptr(raw), raw.size)
+    fl = np.zeros(4096, dtype=np.float32)
+    oracle.orc.orc_xoshiro_floats(ptr(s2), ptr(fl), fl.size)
+    assert np.array_equal(s, s2)  # one u64 per float
+    assert fl.min() >= 0.0 and fl.max() < 1.0
+    want = np.array([py_float32(int(r)) for r in raw], dtype=np.float32)
+    assert np.array_equal(fl.view(np.uint32), want.view(np.uint32))
+    assert 0.45 < fl.mean() < 0.55
+
+
+def test_noise_seed_counter():
+    # Noise.zig:26: the k-th Noise.init() in program order gets seed k; bank voice v gets first_seed + v
+    st = oracle.state_init(L.MOD_NOISE, 5, first_seed=10)
+    for v in range(5):
+        assert [int(x) for x in st["s"][v]] == splitmix(10 + v, 4)
