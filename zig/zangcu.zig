@@ -1,0 +1,223 @@
+// zangcu.zig — the Zig side of the boundary: module-contract-shaped wrappers over include/zangcu.h.
+//
+// SOURCE ONLY: there is no Zig toolchain in the build image or on the GPU box, so this file has never been
+// compiled.  It shows the binding a zang maintainer would add (build.zig: exe.addIncludePath("include");
+// exe.linkSystemLibrary("zangcu"); exe.linkLibC();).  The Python ctypes harness in zang_b200/ is the
+// binding that actually runs in this repository's tests.
+//
+// A zang module paints ONE voice:   paint(self, span, outputs, temps, note_id_changed, params)
+// A bank paints EVERY voice of a block of mix buffers: the per-voice (span, note_id_changed, params) triples
+// that Trigger.next() yields are collected into a span table, then one call paints them all on the GPU.
+const std = @import("std");
+pub const c = @cImport({
+    @cInclude("zangcu.h");
+});
+
+pub const Error = error{ Invalid, NoDevice, Cuda, OutOfMemory, Unsupported, Nccl };
+
+fn check(rc: c_int) Error!void {
+    return switch (rc) {
+        c.ZCU_OK => {},
+        c.ZCU_ERR_INVALID => Error.Invalid,
+        c.ZCU_ERR_NO_DEVICE => Error.NoDevice, // there is no CPU fallback
+        c.ZCU_ERR_CUDA => Error.Cuda,
+        c.ZCU_ERR_OOM => Error.OutOfMemory,
+        c.ZCU_ERR_UNSUPPORTED => Error.Unsupported,
+        else => Error.Nccl,
+    };
+}
+
+pub const Context = struct {
+    h: *c.zcu_ctx,
+
+    pub fn init(device: c_int) Error!Context {
+        var h: ?*c.zcu_ctx = null;
+        try check(c.zcu_ctx_create(device, &h));
+        return .{ .h = h.? };
+    }
+    pub fn deinit(self: Context) void {
+        c.zcu_ctx_destroy(self.h);
+    }
+    pub fn sync(self: Context) Error!void {
+        try check(c.zcu_ctx_sync(self.h));
+    }
+};
+
+/// [frames][voices] f32 device buffer: the batched form of the caller-owned []f32
+pub const Buffer = struct {
+    h: *c.zcu_buf,
+    pub fn init(ctx: Context, frames: u32, voices: u32) Error!Buffer {
+        var h: ?*c.zcu_buf = null;
+        try check(c.zcu_buf_alloc(ctx.h, frames, voices, &h));
+        return .{ .h = h.? };
+    }
+    pub fn deinit(self: Buffer) void {
+        c.zcu_buf_free(self.h);
+    }
+};
+
+/// Collects what `while (trigger.next(&ctr)) |result|` yields for every voice of a block.
+pub const SpanTableBuilder = struct {
+    voice_off: std.ArrayList(u32),
+    spans: std.ArrayList(c.zcu_span),
+
+    pub fn init(allocator: std.mem.Allocator) SpanTableBuilder {
+        return .{ .voice_off = std.ArrayList(u32).init(allocator), .spans = std.ArrayList(c.zcu_span).init(allocator) };
+    }
+    pub fn beginVoice(self: *SpanTableBuilder) !void {
+        try self.voice_off.append(@intCast(self.spans.items.len));
+    }
+    /// frame_base = index of the mix buffer inside the block times its length
+    pub fn add(self: *SpanTableBuilder, frame_base: u32, start: usize, end: usize, note_id_changed: bool, params_row: u32) !void {
+        try self.spans.append(.{
+            .start = frame_base + @as(u32, @intCast(start)),
+            .end = frame_base + @as(u32, @intCast(end)),
+            .flags = if (note_id_changed) c.ZCU_SPAN_NOTE_ID_CHANGED else 0,
+            .param = params_row,
+        });
+    }
+    pub fn upload(self: *SpanTableBuilder, ctx: Context, voices: u32, frames: u32) Error!*c.zcu_spans {
+        self.voice_off.append(@intCast(self.spans.items.len)) catch return Error.OutOfMemory;
+        var h: ?*c.zcu_spans = null;
+        try check(c.zcu_spans_upload(ctx.h, voices, frames, self.voice_off.items.ptr, self.spans.items.ptr, &h));
+        return h.?;
+    }
+};
+
+/// mod.PulseOsc for `voices` voices: same contract, one more axis.
+pub const PulseOscBank = struct {
+    pub const num_outputs = 1;
+    pub const num_temps = 0;
+    pub const Params = c.zcu_pulse_params; // { sample_rate, freq, color }
+
+    ctx: Context,
+    bank: *c.zcu_bank,
+
+    pub fn init(ctx: Context, voices: u32) Error!PulseOscBank {
+        var b: ?*c.zcu_bank = null;
+        try check(c.zcu_bank_create(ctx.h, c.ZCU_MOD_PULSE_OSC, voices, 0, &b));
+        return .{ .ctx = ctx, .bank = b.? };
+    }
+    /// `freq` null = zang.constant(params.freq), non-null = zang.buffer(freq)
+    pub fn paint(
+        self: *PulseOscBank,
+        spans: *const c.zcu_spans,
+        outputs: [num_outputs]Buffer,
+        temps: [num_temps]Buffer,
+        params: []const Params,
+        freq: ?Buffer,
+    ) Error!void {
+        _ = temps;
+        try check(c.zcu_paint_pulse_osc(self.ctx.h, self.bank, spans, params.ptr, @intCast(params.len), outputs[0].h, if (freq) |f| f.h else null));
+    }
+};
+
+/// mod.Filter
+pub const FilterBank = struct {
+    pub const num_outputs = 1;
+    pub const num_temps = 0;
+    pub const Params = c.zcu_filter_params; // { type, cutoff, res }; input/cutoff/res buffers are call arguments
+
+    ctx: Context,
+    bank: *c.zcu_bank,
+
+    pub fn init(ctx: Context, voices: u32) Error!FilterBank {
+        var b: ?*c.zcu_bank = null;
+        try check(c.zcu_bank_create(ctx.h, c.ZCU_MOD_FILTER, voices, 0, &b));
+        return .{ .ctx = ctx, .bank = b.? };
+    }
+    pub fn cutoffFromFrequency(frequency: f32, sample_rate: f32) f32 {
+        return c.zcu_filter_cutoff_from_frequency(frequency, sample_rate);
+    }
+    pub fn paint(self: *FilterBank, spans: *const c.zcu_spans, outputs: [1]Buffer, temps: [0]Buffer, params: []const Params, input: Buffer, cutoff: ?Buffer, res: ?Buffer) Error!void {
+        _ = temps;
+        try check(c.zcu_paint_filter(self.ctx.h, self.bank, spans, params.ptr, @intCast(params.len), outputs[0].h, input.h, if (cutoff) |b| b.h else null, if (res) |b| b.h else null));
+    }
+};
+
+/// mod.Envelope
+pub const EnvelopeBank = struct {
+    pub const num_outputs = 1;
+    pub const num_temps = 0;
+    pub const Params = c.zcu_envelope_params;
+
+    ctx: Context,
+    bank: *c.zcu_bank,
+
+    pub fn init(ctx: Context, voices: u32) Error!EnvelopeBank {
+        var b: ?*c.zcu_bank = null;
+        try check(c.zcu_bank_create(ctx.h, c.ZCU_MOD_ENVELOPE, voices, 0, &b));
+        return .{ .ctx = ctx, .bank = b.? };
+    }
+    pub fn paint(self: *EnvelopeBank, spans: *const c.zcu_spans, outputs: [1]Buffer, temps: [0]Buffer, params: []const Params) Error!void {
+        _ = temps;
+        try check(c.zcu_paint_envelope(self.ctx.h, self.bank, spans, params.ptr, @intCast(params.len), outputs[0].h));
+    }
+};
+
+/// examples/modules.zig NiceInstrument for a bank of voices, composed exactly like the original.
+pub const NiceInstrumentBank = struct {
+    pub const num_outputs = 1;
+    pub const num_temps = 2;
+    pub const Params = struct { sample_rate: f32, freq: f32, note_on: bool };
+
+    ctx: Context,
+    color: f32,
+    osc: PulseOscBank,
+    flt: FilterBank,
+    env: EnvelopeBank,
+
+    pub fn paint(
+        self: *NiceInstrumentBank,
+        allocator: std.mem.Allocator,
+        spans: *const c.zcu_spans,
+        outputs: [num_outputs]Buffer,
+        temps: [num_temps]Buffer,
+        params: []const Params, // one row per note event; spans refer to rows
+    ) !void {
+        const h = self.ctx.h;
+        var pp = try allocator.alloc(PulseOscBank.Params, params.len);
+        defer allocator.free(pp);
+        var fp = try allocator.alloc(FilterBank.Params, params.len);
+        defer allocator.free(fp);
+        var ep = try allocator.alloc(EnvelopeBank.Params, params.len);
+        defer allocator.free(ep);
+        for (params, 0..) |p, i| {
+            pp[i] = .{ .sample_rate = p.sample_rate, .freq = p.freq, .color = self.color };
+            fp[i] = .{ .type = c.ZCU_FILTER_LOW_PASS, .cutoff = FilterBank.cutoffFromFrequency(p.freq * 8.0, p.sample_rate), .res = 0.7 };
+            ep[i] = .{
+                .sample_rate = p.sample_rate,
+                .attack = .{ .kind = c.ZCU_CURVE_CUBED, .duration = 0.01 },
+                .decay = .{ .kind = c.ZCU_CURVE_CUBED, .duration = 0.1 },
+                .release = .{ .kind = c.ZCU_CURVE_CUBED, .duration = 0.5 },
+                .sustain_volume = 0.8,
+                .note_on = @intFromBool(p.note_on),
+            };
+        }
+        try check(c.zcu_zero(h, spans, temps[0].h));
+        try self.osc.paint(spans, .{temps[0]}, .{}, pp, null);
+        try check(c.zcu_multiply_with_scalar(h, spans, temps[0].h, 0.5));
+        try check(c.zcu_zero(h, spans, temps[1].h));
+        try self.flt.paint(spans, .{temps[1]}, .{}, fp, temps[0], null, null);
+        try check(c.zcu_zero(h, spans, temps[0].h));
+        try self.env.paint(spans, .{temps[0]}, .{}, ep);
+        try check(c.zcu_multiply(h, spans, outputs[0].h, temps[0].h, temps[1].h));
+    }
+};
+
+/// zang.Trigger(P) with P = a params-row index; the host keeps the rows.
+pub const Trigger = struct {
+    t: c.zcu_trigger,
+    pub fn init() Trigger {
+        var t: c.zcu_trigger = undefined;
+        c.zcu_trigger_init(&t);
+        return .{ .t = t };
+    }
+    pub fn reset(self: *Trigger) void {
+        c.zcu_trigger_reset(&self.t);
+    }
+    /// the whole `while (trigger.next(&ctr))` loop of one mix buffer, appended to `out`
+    pub fn run(self: *Trigger, start: u32, end: u32, impulses: []const c.zcu_impulse, rows: []const u32, frame_base: u32, out: []c.zcu_span) u32 {
+        return c.zcu_trigger_run(&self.t, start, end, impulses.ptr, rows.ptr, @intCast(impulses.len), frame_base, out.ptr, @intCast(out.len));
+    }
+};
