@@ -201,6 +201,14 @@ int zcu_multiply(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, co
 int zcu_multiply_with(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a);
 int zcu_multiply_scalar(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, float b);
 int zcu_multiply_with_scalar(zcu_ctx*, const zcu_spans*, zcu_buf* dest, float a);
+/* The same scalar ops when the reference passes a value derived from the span's params, e.g.
+ * zang.set(span, temps[0], params.freq * params.ratio.constant) (examples/modules.zig:39-47): the scalar of a
+ * span is scalars[span.param].  scalars is a host array of nscalars rows, copied by the call; spans != NULL. */
+int zcu_set_rows(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const float* scalars, uint32_t nscalars);
+int zcu_add_scalar_rows(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, const float* scalars, uint32_t nscalars);
+int zcu_add_scalar_into_rows(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const float* scalars, uint32_t nscalars);
+int zcu_multiply_scalar_rows(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const zcu_buf* a, const float* scalars, uint32_t nscalars);
+int zcu_multiply_with_scalar_rows(zcu_ctx*, const zcu_spans*, zcu_buf* dest, const float* scalars, uint32_t nscalars);
 
 /* ---- module paints (each replaces <Module>.paint of src/modules/<Module>.zig) ---------------- */
 /* params: host array of nparams rows, copied to the device by the call.  Buffer arguments that model
@@ -243,6 +251,12 @@ void zcu_sample_free(zcu_sample*);
 /* dst[f][c] += sum_v gains[v*channels + c] * src[f][v];  dst is a [frames][channels] buffer.
  * gains == NULL means 1.0 for every voice/channel. */
 int zcu_mix_reduce(zcu_ctx*, const zcu_buf* src, const float* gains_host, uint32_t channels, zcu_buf* dst);
+
+/* The reference's own accumulation order: voices paint one after the other into the shared outputs[0]
+ * (examples/example_song.zig:382-396), i.e. dst[f][c] = (((dst[f][c] + g0*src[f][0]) + g1*src[f][1]) + ...) in
+ * voice order, multiply and add rounded separately.  Bit-exact with the sequential host loop; use it where the
+ * summation order matters (PCM output), zcu_mix_reduce where it does not. */
+int zcu_mix_ordered(zcu_ctx*, const zcu_buf* src, const float* gains_host, uint32_t channels, zcu_buf* dst);
 
 /* ---- zang.mixDown (src/zang/mixdown.zig:8-86): f32 -> s16le / s8 with clamping ---------------- */
 enum { ZCU_AUDIO_SIGNED8 = 0, ZCU_AUDIO_SIGNED16_LSB = 1 };
@@ -305,6 +319,25 @@ void zcu_poly_dispatcher_reset(zcu_poly_dispatcher* pd);
 int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* impulses, const uint32_t* params,
                                  const int32_t* note_on, uint32_t n, zcu_impulse* out_impulses,
                                  uint32_t* out_params, uint32_t* out_counts);
+
+/* Voice(T) of examples/example_song.zig:287-350 without the module paint: a NoteTracker feeding a
+ * PolyphonyDispatcher feeding one Trigger per sub-voice. */
+typedef struct zcu_poly_voice {
+    zcu_note_tracker tracker;
+    zcu_poly_dispatcher dispatcher;
+    zcu_trigger triggers[ZCU_MAX_POLYPHONY];
+} zcu_poly_voice;
+int zcu_poly_voice_init(zcu_poly_voice* pv, const zcu_song_event* song, uint32_t song_len, uint32_t polyphony);
+void zcu_poly_voice_reset(zcu_poly_voice* pv); /* example_song.zig:316-322 */
+/* Runs Voice.paint's event logic (example_song.zig:331-347) for num_buffers consecutive mix buffers of buffer_frames
+ * frames (the last one last_buffer_frames long) and writes the block's span table in the CSR layout of
+ * zcu_spans_upload: sub-voice i is voice column i, frames are block relative, span.param is the song event's
+ * `param`.  param_note_on[param] is the note_on flag of that params row (the dispatcher reads params.note_on,
+ * notes.zig:318-323).  Returns the number of spans; if it exceeds max_spans nothing is written, *pv is left
+ * untouched and the required count is returned negated. */
+int64_t zcu_poly_voice_spans(zcu_poly_voice* pv, const int32_t* param_note_on, float sample_rate, uint32_t buffer_frames,
+                             uint32_t num_buffers, uint32_t last_buffer_frames, uint32_t* voice_off_out, zcu_span* spans_out,
+                             uint64_t max_spans);
 
 /* ---- fused instrument banks (B200-first path for the benchmark configs) ----------------------- */
 /* A note event of one voice with an ABSOLUTE frame position in the whole render.  Voice v owns

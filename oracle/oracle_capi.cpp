@@ -11,6 +11,7 @@
 
 #include "../include/zangcu.h"
 #include "zang_oracle.hpp"
+#include "song_oracle.hpp"
 
 using namespace zo;
 
@@ -479,6 +480,48 @@ double orc_render_nice(uint32_t V, uint32_t total_frames, uint32_t buffer_frames
             for (uint32_t t = 0; t < nthreads; t++)
                 for (size_t i = 0; i < (size_t)total_frames * channels; i++) mix[i] += partial[t][i];
     }
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+}
+
+// ---- the reference's own CPU workload: write_wav of the Toccata song (song_oracle.hpp) -------------
+// Parsed song events of one instrument (0 Pedal, 1 RegularOrgan, 2 WeirdOrgan).  Returns the number of
+// events (writes at most max_out), or -1 if the text does not parse.
+int orc_song_events(const char* text, size_t len, uint32_t instrument, float* t_out, uint32_t* id_out, float* freq_out,
+                    int32_t* note_on_out, uint32_t max_out) {
+    Song song;
+    song.parse(text, len);
+    if (!song.ok || instrument >= Song::NUM_INSTRUMENTS) return -1;
+    const auto& ev = song.all_notes[instrument];
+    for (size_t i = 0; i < ev.size() && i < max_out; i++) {
+        t_out[i] = ev[i].t;
+        id_out[i] = (uint32_t)ev[i].note_id;
+        freq_out[i] = ev[i].params.freq;
+        note_on_out[i] = ev[i].params.note_on ? 1 : 0;
+    }
+    return (int)ev.size();
+}
+
+// write_wav.zig:49-95 for the first total_frames frames: pcm = s16le mono after mixDown(0.25); mix = f32 before it.
+// Returns wall seconds, or a negative value if the song does not parse.
+double orc_song_render(const char* text, size_t len, uint64_t total_frames, float sample_rate, uint8_t* pcm, float* mix) {
+    Song song;
+    song.parse(text, len);
+    auto t_begin = std::chrono::steady_clock::now();
+    if (!song_render(song, (size_t)total_frames, sample_rate, pcm, mix)) return -1.0;
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+}
+
+// the same from already-parsed events (the GPU box has no /root/reference: tests ship the parsed score as a fixture).
+// counts[3]; the four arrays hold the events of instrument 0, then 1, then 2.
+double orc_song_render_events(const uint32_t* counts, const float* t, const uint32_t* id, const float* freq, const int32_t* note_on,
+                              uint64_t total_frames, float sample_rate, uint8_t* pcm, float* mix) {
+    Song song;
+    size_t k = 0;
+    for (size_t i = 0; i < Song::NUM_INSTRUMENTS; i++)
+        for (uint32_t j = 0; j < counts[i]; j++, k++) song.all_notes[i].push_back(SongEvent{MyNoteParams{freq[k], note_on[k] != 0}, t[k], id[k]});
+    song.ok = true;
+    auto t_begin = std::chrono::steady_clock::now();
+    if (!song_render(song, (size_t)total_frames, sample_rate, pcm, mix)) return -1.0;
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
 }
 

@@ -94,3 +94,42 @@ def render_nice(wl, total_frames, sample_rate=48000.0, buffer_frames=1024, chann
     secs = orc.orc_render_nice(V, total_frames, buffer_frames, sample_rate, ptr(off), ptr(ev), ptr(color), ptr(gains), channels, ptr(mix),
                                ptr(vo), first, n, nthreads)
     return mix, vo, secs
+
+
+# ---- the reference's own CPU workload: write_wav of the Toccata song (oracle/song_oracle.hpp) ------------
+orc.orc_song_events.argtypes = [C.c_char_p, C.c_size_t, _U, _P, _P, _P, _P, _U]
+orc.orc_song_render.argtypes = [C.c_char_p, C.c_size_t, _U64, _F, _P, _P]
+orc.orc_song_render.restype = C.c_double
+orc.orc_song_render_events.argtypes = [_P, _P, _P, _P, _P, _U64, _F, _P, _P]
+orc.orc_song_render_events.restype = C.c_double
+
+song_note_dtype = np.dtype([("t", "<f4"), ("note_id", "<u4"), ("freq", "<f4"), ("note_on", "<i4")])
+
+
+def song_parse(text):
+    """The oracle's doParse: one event array per instrument."""
+    if isinstance(text, str):
+        text = text.encode("latin-1")
+    out = []
+    for k in range(3):
+        cap = 20000  # example_song.zig:103
+        t, ids, fr, on = np.zeros(cap, np.float32), np.zeros(cap, np.uint32), np.zeros(cap, np.float32), np.zeros(cap, np.int32)
+        n = orc.orc_song_events(text, len(text), k, ptr(t), ptr(ids), ptr(fr), ptr(on), cap)
+        assert n >= 0, "song text does not parse"
+        ev = np.zeros(n, dtype=song_note_dtype)
+        ev["t"], ev["note_id"], ev["freq"], ev["note_on"] = t[:n], ids[:n], fr[:n], on[:n]
+        out.append(ev)
+    return out
+
+
+def song_render(notes, total_frames, sample_rate=48000.0, want_mix=True):
+    """write_wav.zig's loop over the parsed events.  Returns (pcm uint8[total*2], mix f32[total] or None, seconds)."""
+    counts = np.array([n.size for n in notes], dtype=np.uint32)
+    cat = np.concatenate(notes)
+    t, ids = np.ascontiguousarray(cat["t"]), np.ascontiguousarray(cat["note_id"])
+    fr, on = np.ascontiguousarray(cat["freq"]), np.ascontiguousarray(cat["note_on"])
+    pcm = np.zeros(total_frames * 2, dtype=np.uint8)
+    mix = np.zeros(total_frames, dtype=np.float32) if want_mix else None
+    secs = orc.orc_song_render_events(ptr(counts), ptr(t), ptr(ids), ptr(fr), ptr(on), total_frames, sample_rate, ptr(pcm), ptr(mix))
+    assert secs >= 0
+    return pcm, mix, secs

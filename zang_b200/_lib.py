@@ -100,6 +100,10 @@ class PolyDispatcherPOD(C.Structure):
     _fields_ = [("polyphony", C.c_uint32), ("slots", PolySlotPOD * MAX_POLYPHONY)]
 
 
+class PolyVoicePOD(C.Structure):
+    _fields_ = [("tracker", NoteTrackerPOD), ("dispatcher", PolyDispatcherPOD), ("triggers", TriggerPOD * MAX_POLYPHONY)]
+
+
 class RenderConfig(C.Structure):
     _fields_ = [("instrument", C.c_int32), ("voices", C.c_uint32), ("buffer_frames", C.c_uint32), ("total_frames", C.c_uint32),
                 ("block_buffers", C.c_uint32), ("channels", C.c_uint32), ("sample_rate", C.c_float), ("first_seed", C.c_uint32),
@@ -148,6 +152,11 @@ PROTOTYPES = {
     "zcu_multiply_with": (_I, [_P, _P, _P, _P]),
     "zcu_multiply_scalar": (_I, [_P, _P, _P, _P, _F]),
     "zcu_multiply_with_scalar": (_I, [_P, _P, _P, _F]),
+    "zcu_set_rows": (_I, [_P, _P, _P, _P, _U]),
+    "zcu_add_scalar_rows": (_I, [_P, _P, _P, _P, _P, _U]),
+    "zcu_add_scalar_into_rows": (_I, [_P, _P, _P, _P, _U]),
+    "zcu_multiply_scalar_rows": (_I, [_P, _P, _P, _P, _P, _U]),
+    "zcu_multiply_with_scalar_rows": (_I, [_P, _P, _P, _P, _U]),
     "zcu_paint_sine_osc": (_I, [_P, _P, _P, _P, _U, _P, _P, _P]),
     "zcu_paint_pulse_osc": (_I, [_P, _P, _P, _P, _U, _P, _P]),
     "zcu_paint_trisaw_osc": (_I, [_P, _P, _P, _P, _U, _P, _P]),
@@ -165,6 +174,7 @@ PROTOTYPES = {
     "zcu_sample_create": (_I, [_P, _P, _S, _U, _U, _I, _P]),
     "zcu_sample_free": (None, [_P]),
     "zcu_mix_reduce": (_I, [_P, _P, _P, _U, _P]),
+    "zcu_mix_ordered": (_I, [_P, _P, _P, _U, _P]),
     "zcu_mix_down": (_I, [_P, _P, _I, _F, _P, _S]),
     "zcu_trigger_init": (None, [_P]),
     "zcu_trigger_reset": (None, [_P]),
@@ -180,6 +190,9 @@ PROTOTYPES = {
     "zcu_poly_dispatcher_init": (_I, [_P, _U]),
     "zcu_poly_dispatcher_reset": (None, [_P]),
     "zcu_poly_dispatcher_dispatch": (_I, [_P, _P, _P, _P, _U, _P, _P, _P]),
+    "zcu_poly_voice_init": (_I, [_P, _P, _U, _U]),
+    "zcu_poly_voice_reset": (None, [_P]),
+    "zcu_poly_voice_spans": (C.c_int64, [_P, _P, _F, _U, _U, _U, _P, _P, _U64]),
     "zcu_render_create": (_I, [_P, _P, _P, _P, _P]),
     "zcu_render_free": (None, [_P]),
     "zcu_render_set_events": (_I, [_P, _P, _P, _P]),

@@ -300,6 +300,24 @@ int zcu_multiply_with(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const zcu_buf*
 int zcu_multiply_scalar(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const zcu_buf* a, float b) { return basic_call(c, 9, s, d, a, nullptr, b, true, false); }
 int zcu_multiply_with_scalar(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, float a) { return basic_call(c, 10, s, d, nullptr, nullptr, a, false, false); }
 
+// per-span scalars (scalars[span.param]); the span table is mandatory
+static int basic_rows_call(zcu_ctx* ctx, int op, const zcu_spans* sp, zcu_buf* dest, const zcu_buf* a, bool need_a, const float* rows, uint32_t nrows) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, dest != nullptr, "null dest");
+    ZCU_REQUIRE(ctx, sp != nullptr, "per-span scalars need a span table");
+    ZCU_REQUIRE(ctx, !need_a || a, "null source a");
+    ZCU_REQUIRE(ctx, !a || (a->frames == dest->frames && a->voices == dest->voices), "shape mismatch (a)");
+    ZCU_REQUIRE(ctx, sp->voices == dest->voices && sp->frames == dest->frames, "span table / buffer shape mismatch");
+    ZCU_REQUIRE(ctx, sp->nspans == 0 || (rows && sp->max_param < nrows), "a span refers to a scalar row beyond nscalars");
+    if (sp->nspans == 0) return ZCU_OK;
+    return zcu_launch_basic_rows(ctx, op, sp, dest, a, rows, nrows);
+}
+int zcu_set_rows(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const float* r, uint32_t n) { return basic_rows_call(c, 1, s, d, nullptr, false, r, n); }
+int zcu_add_scalar_rows(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const zcu_buf* a, const float* r, uint32_t n) { return basic_rows_call(c, 5, s, d, a, true, r, n); }
+int zcu_add_scalar_into_rows(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const float* r, uint32_t n) { return basic_rows_call(c, 6, s, d, nullptr, false, r, n); }
+int zcu_multiply_scalar_rows(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const zcu_buf* a, const float* r, uint32_t n) { return basic_rows_call(c, 9, s, d, a, true, r, n); }
+int zcu_multiply_with_scalar_rows(zcu_ctx* c, const zcu_spans* s, zcu_buf* d, const float* r, uint32_t n) { return basic_rows_call(c, 10, s, d, nullptr, false, r, n); }
+
 // ---- module paints ------------------------------------------------------------------------------------
 static int paint_call(zcu_ctx* ctx, int kind, zcu_bank* bank, const zcu_spans* sp, const void* params, size_t row_bytes, uint32_t nparams,
                       zcu_buf* out, const zcu_buf* in0, const zcu_buf* in1, const zcu_buf* in2, bool need_in0, const void* aux_dev,

@@ -70,10 +70,11 @@ int launch_full(zcu_ctx* ctx, float* dest, const float* a, const float* b, float
     return ZCU_OK;
 }
 
-template <int OP>
-int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a, const float* b, float s) {
+template <int OP, bool ROWS = false>
+int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a, const float* b, float s, const float* rows = nullptr,
+                 uint32_t nrows = 0) {
     void* dscalar = nullptr;
-    int rc = zcu_arena_upload(ctx, 0, &s, sizeof(float), &dscalar);
+    int rc = ROWS ? zcu_arena_upload(ctx, 0, rows, (size_t)nrows * sizeof(float), &dscalar) : zcu_arena_upload(ctx, 0, &s, sizeof(float), &dscalar);
     if (rc) return rc;
     PaintArgs pa{};
     pa.V = sp->voices;
@@ -91,10 +92,10 @@ int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a,
     const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP>>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
         attr_set = true;
     }
-    k_paint_lockstep<BasicMod<OP>><<<warps, 32, smem, ctx->stream>>>(pa, T);
+    k_paint_lockstep<BasicMod<OP, ROWS>><<<warps, 32, smem, ctx->stream>>>(pa, T);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;
@@ -136,6 +137,45 @@ __global__ void __launch_bounds__(256) k_mix_reduce(const float* __restrict__ sr
         float s = 0.0f;
         for (int w = 0; w < 8; w++) s += part[w][threadIdx.x];
         dst[(size_t)f * C + threadIdx.x] += s;
+    }
+}
+
+// ---- ordered voice mix: the reference's sequential accumulation into the shared output ----------------
+// One thread per frame walks the voices in order; a CTA stages its 128 frames x V tile through shared
+// memory so that the HBM reads are coalesced whatever V is.
+template <int C>
+__global__ void __launch_bounds__(128) k_mix_ordered(const float* __restrict__ src, const float* __restrict__ gains,
+                                                     float* __restrict__ dst, uint32_t frames, uint32_t V) {
+    extern __shared__ float tile[];  // [128][VT+1]
+    constexpr uint32_t VT = 32;
+    const uint32_t f0 = blockIdx.x * 128;
+    const uint32_t nf = min(128u, frames - f0);
+    const uint32_t f = f0 + threadIdx.x;
+    float acc[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) acc[c] = (threadIdx.x < nf) ? dst[(size_t)f * C + c] : 0.0f;
+    for (uint32_t v0 = 0; v0 < V; v0 += VT) {
+        const uint32_t nv = min(VT, V - v0);
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < nf * nv; i += 128) {
+            const uint32_t r = i / nv, c = i - r * nv;
+            tile[r * (VT + 1) + c] = src[(size_t)(f0 + r) * V + v0 + c];
+        }
+        __syncthreads();
+        if (threadIdx.x < nf) {
+            for (uint32_t c = 0; c < nv; c++) {
+                const float x = tile[threadIdx.x * (VT + 1) + c];
+#pragma unroll
+                for (int ch = 0; ch < C; ch++) {
+                    const float gx = gains ? gains[(size_t)(v0 + c) * C + ch] * x : x;  // rounded product, then rounded sum (-fmad=false)
+                    acc[ch] = acc[ch] + gx;
+                }
+            }
+        }
+    }
+    if (threadIdx.x < nf) {
+#pragma unroll
+        for (int c = 0; c < C; c++) dst[(size_t)f * C + c] = acc[c];
     }
 }
 
@@ -253,6 +293,18 @@ int zcu_launch_basic(zcu_ctx* ctx, int op, const zcu_spans* sp, zcu_buf* dest, c
     }
 }
 
+int zcu_launch_basic_rows(zcu_ctx* ctx, int op, const zcu_spans* sp, zcu_buf* dest, const zcu_buf* a, const float* rows, uint32_t nrows) {
+    const float* pa = a ? a->d : nullptr;
+    switch (op) {
+        case 1: return launch_spans<1, true>(ctx, sp, dest->d, pa, nullptr, 0.0f, rows, nrows);
+        case 5: return launch_spans<5, true>(ctx, sp, dest->d, pa, nullptr, 0.0f, rows, nrows);
+        case 6: return launch_spans<6, true>(ctx, sp, dest->d, pa, nullptr, 0.0f, rows, nrows);
+        case 9: return launch_spans<9, true>(ctx, sp, dest->d, pa, nullptr, 0.0f, rows, nrows);
+        case 10: return launch_spans<10, true>(ctx, sp, dest->d, pa, nullptr, 0.0f, rows, nrows);
+        default: return zcu_fail(ctx, ZCU_ERR_INVALID, "basic op %d takes no scalar", op);
+    }
+}
+
 int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed) {
     if (bank->voices == 0 || bank->stride == 0) return ZCU_OK;
     k_bank_init<<<(bank->voices + 127) / 128, 128, 0, ctx->stream>>>(bank->kind, bank->d, bank->voices, first_seed);
@@ -291,6 +343,28 @@ extern "C" int zcu_mix_reduce(zcu_ctx* ctx, const zcu_buf* src, const float* gai
         k_mix_reduce<1><<<src->frames, 256, 0, ctx->stream>>>(src->d, dg, dst->d, src->voices);
     else
         k_mix_reduce<2><<<src->frames, 256, 0, ctx->stream>>>(src->d, dg, dst->d, src->voices);
+    ctx->launches++;
+    ZCU_CUDA(ctx, cudaGetLastError());
+    return ZCU_OK;
+}
+
+extern "C" int zcu_mix_ordered(zcu_ctx* ctx, const zcu_buf* src, const float* gains_host, uint32_t channels, zcu_buf* dst) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, src && dst, "null buffer");
+    ZCU_REQUIRE(ctx, channels == 1 || channels == 2, "channels must be 1 or 2");
+    ZCU_REQUIRE(ctx, dst->voices == channels && dst->frames == src->frames, "dst must be [frames][channels]");
+    float* dg = nullptr;
+    if (gains_host) {
+        int rc = zcu_arena_upload(ctx, 1, gains_host, (size_t)src->voices * channels * sizeof(float), (void**)&dg);
+        if (rc) return rc;
+    }
+    if (src->frames == 0 || src->voices == 0) return ZCU_OK;
+    const unsigned blocks = (src->frames + 127) / 128;
+    const size_t smem = 128 * 33 * sizeof(float);
+    if (channels == 1)
+        k_mix_ordered<1><<<blocks, 128, smem, ctx->stream>>>(src->d, dg, dst->d, src->frames, src->voices);
+    else
+        k_mix_ordered<2><<<blocks, 128, smem, ctx->stream>>>(src->d, dg, dst->d, src->frames, src->voices);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;

@@ -6,6 +6,7 @@
 // impulse; the caller keeps the table of rows.
 #include <algorithm>
 #include <cstring>
+#include <vector>
 
 #include "../../include/zangcu.h"
 
@@ -199,6 +200,56 @@ int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* imp
         }
     }
     return ZCU_OK;
+}
+
+// ---- Voice(T) event logic (examples/example_song.zig:287-350) ------------------------------------------
+int zcu_poly_voice_init(zcu_poly_voice* pv, const zcu_song_event* song, uint32_t song_len, uint32_t polyphony) {
+    if (!pv) return ZCU_ERR_INVALID;
+    zcu_note_tracker_init(&pv->tracker, song, song_len);
+    const int rc = zcu_poly_dispatcher_init(&pv->dispatcher, polyphony);
+    for (uint32_t i = 0; i < ZCU_MAX_POLYPHONY; i++) zcu_trigger_init(&pv->triggers[i]);
+    return rc;
+}
+void zcu_poly_voice_reset(zcu_poly_voice* pv) {
+    zcu_note_tracker_reset(&pv->tracker);
+    zcu_poly_dispatcher_reset(&pv->dispatcher);
+    for (uint32_t i = 0; i < ZCU_MAX_POLYPHONY; i++) zcu_trigger_reset(&pv->triggers[i]);
+}
+
+int64_t zcu_poly_voice_spans(zcu_poly_voice* pv, const int32_t* param_note_on, float sample_rate, uint32_t buffer_frames,
+                             uint32_t num_buffers, uint32_t last_buffer_frames, uint32_t* voice_off_out, zcu_span* spans_out,
+                             uint64_t max_spans) {
+    if (!pv || !voice_off_out || pv->dispatcher.polyphony == 0 || pv->dispatcher.polyphony > ZCU_MAX_POLYPHONY) return 0;
+    const uint32_t P = pv->dispatcher.polyphony;
+    zcu_poly_voice w = *pv;  // work on a copy: commit only when the table fits
+    std::vector<std::vector<zcu_span>> per(P);
+    zcu_impulse imps[32], poly_imps[ZCU_MAX_POLYPHONY * 32];
+    uint32_t params[32], poly_params[ZCU_MAX_POLYPHONY * 32], counts[ZCU_MAX_POLYPHONY];
+    int32_t on[32];
+    zcu_span tmp[40];
+    for (uint32_t b = 0; b < num_buffers; b++) {
+        const uint32_t len = (b + 1 == num_buffers) ? last_buffer_frames : buffer_frames;
+        const uint32_t base = b * buffer_frames;
+        const uint32_t n = zcu_note_tracker_consume(&w.tracker, sample_rate, 0, len, imps, params, 32);
+        for (uint32_t i = 0; i < n; i++) on[i] = param_note_on ? param_note_on[params[i]] : 1;
+        zcu_poly_dispatcher_dispatch(&w.dispatcher, imps, params, on, n, poly_imps, poly_params, counts);
+        for (uint32_t i = 0; i < P; i++) {
+            const uint32_t k = zcu_trigger_run(&w.triggers[i], 0, len, poly_imps + (size_t)i * 32, poly_params + (size_t)i * 32, counts[i], base, tmp, 40);
+            per[i].insert(per[i].end(), tmp, tmp + (k < 40 ? k : 40));
+        }
+    }
+    uint64_t total = 0;
+    for (uint32_t i = 0; i < P; i++) total += per[i].size();
+    if (total > max_spans || (total > 0 && !spans_out)) return -(int64_t)total;
+    uint32_t off = 0;
+    for (uint32_t i = 0; i < P; i++) {
+        voice_off_out[i] = off;
+        if (!per[i].empty()) std::memcpy(spans_out + off, per[i].data(), per[i].size() * sizeof(zcu_span));
+        off += (uint32_t)per[i].size();
+    }
+    voice_off_out[P] = off;
+    *pv = w;
+    return (int64_t)total;
 }
 
 }  // extern "C"

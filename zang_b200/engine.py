@@ -122,10 +122,36 @@ class Context:
     def multiplyWithScalar(self, spans, dest, a):
         _check(self, lib.zcu_multiply_with_scalar(self._h, _h(spans), dest._h, float(a)))
 
+    # the same with a per-span scalar (scalars[span.param]), e.g. zang.set(span, t, params.freq * ratio)
+    def setRows(self, spans, dest, scalars):
+        r = np.ascontiguousarray(scalars, dtype=np.float32).reshape(-1)
+        _check(self, lib.zcu_set_rows(self._h, spans._h, dest._h, ptr(r), r.size))
+
+    def addScalarRows(self, spans, dest, a, scalars):
+        r = np.ascontiguousarray(scalars, dtype=np.float32).reshape(-1)
+        _check(self, lib.zcu_add_scalar_rows(self._h, spans._h, dest._h, a._h, ptr(r), r.size))
+
+    def addScalarIntoRows(self, spans, dest, scalars):
+        r = np.ascontiguousarray(scalars, dtype=np.float32).reshape(-1)
+        _check(self, lib.zcu_add_scalar_into_rows(self._h, spans._h, dest._h, ptr(r), r.size))
+
+    def multiplyScalarRows(self, spans, dest, a, scalars):
+        r = np.ascontiguousarray(scalars, dtype=np.float32).reshape(-1)
+        _check(self, lib.zcu_multiply_scalar_rows(self._h, spans._h, dest._h, a._h, ptr(r), r.size))
+
+    def multiplyWithScalarRows(self, spans, dest, scalars):
+        r = np.ascontiguousarray(scalars, dtype=np.float32).reshape(-1)
+        _check(self, lib.zcu_multiply_with_scalar_rows(self._h, spans._h, dest._h, ptr(r), r.size))
+
     # ---- mix ------------------------------------------------------------------------------------
     def mix_reduce(self, src, gains, channels, dst):
         g = None if gains is None else np.ascontiguousarray(gains, dtype=np.float32)
         _check(self, lib.zcu_mix_reduce(self._h, src._h, ptr(g), channels, dst._h))
+
+    def mix_ordered(self, src, gains, channels, dst):
+        """the reference's sequential voice accumulation order (bit-exact)"""
+        g = None if gains is None else np.ascontiguousarray(gains, dtype=np.float32)
+        _check(self, lib.zcu_mix_ordered(self._h, src._h, ptr(g), channels, dst._h))
 
     def mixDown(self, mix, audio_format, vol):
         n = mix.frames * mix.voices * (2 if audio_format == L.AUDIO_SIGNED16_LSB else 1)
@@ -383,9 +409,14 @@ class NiceInstrumentBank:
         self.osc = PulseOsc(ctx, voices)
         self.flt = Filter(ctx, voices)
         self.env = Envelope(ctx, voices)
+        self._derived = None
 
-    def paint(self, spans, outputs, temps, params):
-        ctx = self.ctx
+    def derive(self, params):
+        """Module params rows of every instrument params row (the per-call scalars of modules.zig:221-245).
+        Cached for the params array last seen: a song passes the same table block after block."""
+        if self._derived is not None and self._derived[0] is params:
+            return self._derived[1]
+        src = params
         params = np.ascontiguousarray(params, dtype=self.Params).reshape(-1)
         n = params.size
         pp = np.zeros(n, dtype=L.param_dtypes[L.MOD_PULSE_OSC])
@@ -401,6 +432,12 @@ class NiceInstrumentBank:
         ep["release"] = (L.CURVE_CUBED, 0.5)
         ep["sustain_volume"] = 0.8
         ep["note_on"] = params["note_on"]
+        self._derived = (src, (pp, fp, ep))
+        return pp, fp, ep
+
+    def paint(self, spans, outputs, temps, params):
+        ctx = self.ctx
+        pp, fp, ep = self.derive(params)
         ctx.zero(spans, temps[0])
         self.osc.paint(spans, [temps[0]], [], pp)
         ctx.multiplyWithScalar(spans, temps[0], 0.5)
@@ -408,6 +445,79 @@ class NiceInstrumentBank:
         self.flt.paint(spans, [temps[1]], [], fp, input=temps[0])
         ctx.zero(spans, temps[0])
         self.env.paint(spans, [temps[0]], [], ep)
+        ctx.multiply(spans, outputs[0], temps[0], temps[1])
+
+
+class PhaseModOscillatorBank:
+    """examples/modules.zig:6-77 PhaseModOscillator with constant ratio and multiplier (the variants the
+    example instruments use), composed from the module paints.  params rows: (sample_rate, freq)."""
+    num_outputs = 1
+    num_temps = 2
+
+    def __init__(self, ctx, voices, relative=True, ratio=1.0, multiplier=1.0):
+        self.ctx, self.relative, self.ratio, self.multiplier = ctx, bool(relative), np.float32(ratio), np.float32(multiplier)
+        self.carrier = SineOsc(ctx, voices)
+        self.modulator = SineOsc(ctx, voices)
+
+    def derive(self, sample_rate, freq):
+        n = freq.size
+        mod_freq = (freq.astype(np.float32) * self.ratio) if self.relative else np.full(n, self.ratio, dtype=np.float32)  # :41-47
+        mp = np.zeros(n, dtype=L.param_dtypes[L.MOD_SINE_OSC])
+        mp["sample_rate"], mp["phase"] = sample_rate, 0.0  # freq comes from the buffer (:56-60)
+        cp = np.zeros(n, dtype=L.param_dtypes[L.MOD_SINE_OSC])
+        cp["sample_rate"], cp["freq"] = sample_rate, freq  # phase comes from the buffer (:69-73)
+        return mod_freq, mp, cp
+
+    def paint(self, spans, outputs, temps, derived):
+        ctx = self.ctx
+        mod_freq, mp, cp = derived
+        ctx.setRows(spans, temps[0], mod_freq)
+        ctx.zero(spans, temps[1])
+        self.modulator.paint(spans, [temps[1]], [], mp, freq=temps[0])
+        ctx.zero(spans, temps[0])
+        ctx.multiplyScalar(spans, temps[0], temps[1], float(self.multiplier))
+        ctx.zero(spans, temps[1])
+        self.carrier.paint(spans, [temps[1]], [], cp, phase=temps[0])
+        ctx.addInto(spans, outputs[0], temps[1])
+
+
+class PMOscInstrumentBank:
+    """examples/modules.zig:80-128 PMOscInstrument composed from the module paints.
+    instrument params rows: (sample_rate, freq, note_on); release_duration is per bank as in init()."""
+    num_outputs = 1
+    num_temps = 3
+    Params = NiceInstrumentBank.Params
+
+    def __init__(self, ctx, voices, release_duration):
+        self.ctx, self.release_duration = ctx, float(release_duration)
+        self.osc = PhaseModOscillatorBank(ctx, voices, relative=True, ratio=1.0, multiplier=1.0)
+        self.env = Envelope(ctx, voices)
+        self._derived = None
+
+    def derive(self, params):
+        if self._derived is not None and self._derived[0] is params:
+            return self._derived[1]
+        src = params
+        params = np.ascontiguousarray(params, dtype=self.Params).reshape(-1)
+        n = params.size
+        od = self.osc.derive(params["sample_rate"], params["freq"])
+        ep = np.zeros(n, dtype=L.param_dtypes[L.MOD_ENVELOPE])
+        ep["sample_rate"] = params["sample_rate"]
+        ep["attack"] = (L.CURVE_CUBED, 0.025)
+        ep["decay"] = (L.CURVE_CUBED, 0.1)
+        ep["release"] = (L.CURVE_CUBED, self.release_duration)
+        ep["sustain_volume"] = 0.5
+        ep["note_on"] = params["note_on"]
+        self._derived = (src, (od, ep))
+        return od, ep
+
+    def paint(self, spans, outputs, temps, params):
+        ctx = self.ctx
+        od, ep = self.derive(params)
+        ctx.zero(spans, temps[0])
+        self.osc.paint(spans, [temps[0]], [temps[1], temps[2]], od)
+        ctx.zero(spans, temps[1])
+        self.env.paint(spans, [temps[1]], [], ep)
         ctx.multiply(spans, outputs[0], temps[0], temps[1])
 
 
