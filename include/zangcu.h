@@ -320,6 +320,11 @@ int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* imp
                                  const int32_t* note_on, uint32_t n, zcu_impulse* out_impulses,
                                  uint32_t* out_params, uint32_t* out_counts);
 
+/* Painter's ramp clock in closed form (painter.zig:102-106): applies `t += t_step; if (t >= 1) { t = 1; finished }`
+ * up to n times with the reference's exact f32 rounding, in O(binades) instead of O(n).
+ * Returns the number of adds performed (< n only when the ramp finished). */
+uint32_t zcu_ramp_advance(float* t, float t_step, uint32_t n, int32_t* finished);
+
 /* Voice(T) of examples/example_song.zig:287-350 without the module paint: a NoteTracker feeding a
  * PolyphonyDispatcher feeding one Trigger per sub-voice. */
 typedef struct zcu_poly_voice {

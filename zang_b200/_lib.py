@@ -190,6 +190,7 @@ PROTOTYPES = {
     "zcu_poly_dispatcher_init": (_I, [_P, _U]),
     "zcu_poly_dispatcher_reset": (None, [_P]),
     "zcu_poly_dispatcher_dispatch": (_I, [_P, _P, _P, _P, _U, _P, _P, _P]),
+    "zcu_ramp_advance": (_U, [_P, _F, _U, _P]),
     "zcu_poly_voice_init": (_I, [_P, _P, _U, _U]),
     "zcu_poly_voice_reset": (None, [_P]),
     "zcu_poly_voice_spans": (C.c_int64, [_P, _P, _F, _U, _U, _U, _P, _P, _U64]),

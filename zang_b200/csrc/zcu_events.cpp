@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../include/zangcu.h"
+#include "zcu_exact_accum.cuh"
 
 extern "C" {
 
@@ -200,6 +201,13 @@ int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* imp
         }
     }
     return ZCU_OK;
+}
+
+uint32_t zcu_ramp_advance(float* t, float t_step, uint32_t n, int32_t* finished) {
+    bool fin = false;
+    const uint32_t done = zcu::ramp_advance(*t, t_step, n, fin);
+    if (finished) *finished = fin ? 1 : 0;
+    return done;
 }
 
 // ---- Voice(T) event logic (examples/example_song.zig:287-350) ------------------------------------------

@@ -1,0 +1,110 @@
+// zcu_exact_accum.cuh — exact closed form of the reference's f32 accumulators.
+//
+// painter.zig:102-106 runs `t += t_step; if (t >= 1) { t = 1; finished }` once per sample in f32.  A
+// closed form `n * t_step` drifts from that by up to ~1e-4, but repeated f32 addition of
+// a constant IS piecewise closed-form: while t stays in one binade [2^e, 2^(e+1)) with U = ulp(t), every add
+// moves the 24-bit significand by the same integer d = round-to-nearest-even(t_step / U).  So a ramp is
+// at most ~25 (binade, d) segments; inside a segment n adds are one integer multiply-add.  The add that
+// leaves a binade (and everything unusual: zero, subnormals, ties on an odd significand, non-positive or
+// non-finite steps) is done as one real f32 add, so the result is the reference's bit pattern by construction.
+//
+// Host + device: the same code is unit-tested on the CPU against the plain loop (tests/test_exact_accum.py).
+#pragma once
+
+#include <cstdint>
+#include <cstring>
+
+#if defined(__CUDACC__)
+#define ZCU_HD __host__ __device__ __forceinline__
+#else
+#define ZCU_HD inline
+#endif
+
+namespace zcu {
+
+ZCU_HD uint32_t ea_bits(float x) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(x);
+#else
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    return u;
+#endif
+}
+ZCU_HD float ea_float(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float x;
+    memcpy(&x, &u, 4);
+    return x;
+#endif
+}
+// one real f32 add that the compiler may not contract or reassociate
+ZCU_HD float ea_add(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return __fadd_rn(a, b);
+#else
+    volatile float r = a + b;
+    return r;
+#endif
+}
+
+// Painter's ramp clock: applies `t += step; if (t >= 1) { t = 1; finished }` up to n times, stopping after
+// the add that finishes.  Returns the number of adds performed; *finished tells whether the last one hit 1.
+ZCU_HD uint32_t ramp_advance(float& t, float step, uint32_t n, bool& finished) {
+    finished = false;
+    uint32_t done = 0;
+    const uint32_t sb = ea_bits(step);
+    const uint32_t es = (sb >> 23) & 0xFFu;
+    const bool fast_ok = (sb >> 31) == 0 && es != 0 && es != 0xFFu;  // positive, normal, finite step
+    const uint32_t ms = (sb & 0x7FFFFFu) | 0x800000u;
+    while (done < n) {
+        const uint32_t tb = ea_bits(t);
+        const uint32_t et = (tb >> 23) & 0xFFu;
+        uint32_t d = 0, k = 0;
+        bool jump = false;
+        if (fast_ok && (tb >> 31) == 0 && et != 0 && et < 127u && es < et) {  // t normal and below 1
+            const uint32_t shift = et - es;  // >= 1
+            const uint32_t m = (tb & 0x7FFFFFu) | 0x800000u;
+            bool settled = true;
+            if (shift > 24) {
+                d = 0;
+            } else {
+                const uint32_t q = ms >> shift;
+                const uint32_t rem = ms & ((1u << shift) - 1u);
+                const uint32_t half = 1u << (shift - 1);
+                if (rem > half)
+                    d = q + 1;
+                else if (rem < half)
+                    d = q;
+                else if (m & 1u)
+                    settled = false;  // tie on an odd significand: one real add makes it even
+                else
+                    d = (q & 1u) ? q + 1 : q;
+            }
+            if (settled) {
+                if (d == 0) return n;  // step is below half an ulp: t never moves again
+                k = (0xFFFFFFu - m) / d;  // adds that stay inside the binade
+                if (k > n - done) k = n - done;
+                if (k > 0) {
+                    t = ea_float((et << 23) | ((m + k * d) & 0x7FFFFFu));
+                    done += k;
+                    jump = true;
+                }
+            }
+        }
+        if (!jump) {
+            t = ea_add(t, step);
+            done++;
+            if (t >= 1.0f) {
+                t = 1.0f;
+                finished = true;
+                return done;
+            }
+        }
+    }
+    return done;
+}
+
+}  // namespace zcu
