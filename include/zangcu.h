@@ -391,6 +391,8 @@ uint64_t zcu_render_launches_per_run(const zcu_render*);
  * synchronises and returns the summed duration and the number of launches since the last call. */
 int zcu_render_set_profiling(zcu_render*, int enabled);
 int zcu_render_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* launches);
+/* ZCU_RENDER_SCAN only: the same for the zero-state filter pass that precedes each render-kernel launch */
+int zcu_render_aux_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* launches);
 
 /* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
 /* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */

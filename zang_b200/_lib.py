@@ -202,6 +202,7 @@ PROTOTYPES = {
     "zcu_render_launches_per_run": (_U64, [_P]),
     "zcu_render_set_profiling": (_I, [_P, _I]),
     "zcu_render_kernel_ms": (_I, [_P, _P, _P, _P]),
+    "zcu_render_aux_kernel_ms": (_I, [_P, _P, _P, _P]),
     "zcu_nccl_unique_id": (_I, [_P]),
     "zcu_nccl_init": (_I, [_P, _I, _I, _P]),
     "zcu_nccl_reduce_mix": (_I, [_P, _P, _I]),

@@ -18,6 +18,7 @@
 
 #include "zcu_internal.h"
 #include "zcu_render_kernel.cuh"
+#include "zcu_render_scan.cuh"
 
 using namespace zcu;
 
@@ -39,6 +40,16 @@ struct zcu_render {
     bool profiling;
     std::vector<cudaEvent_t> ev;   // pairs around every render-kernel launch since the last query
     size_t ev_used;
+    std::vector<cudaEvent_t> ev_aux;  // ZCU_RENDER_SCAN: pairs around every k_nice_scan_zs launch
+    size_t ev_aux_used;
+    // ZCU_RENDER_SCAN (zcu_render_scan.cuh)
+    uint32_t nchunks_total;
+    EnvSnap* d_snaps;      // per event
+    uint32_t* d_cursor;    // [nchunks_total][V]
+    float2* d_zs;          // [block chunks][V]
+    Mat2* d_M;             // [block chunks][V]
+    float2* d_sstart;      // [block chunks][V]
+    double2* d_fstate;     // [V]
 };
 
 namespace {
@@ -62,7 +73,98 @@ __global__ void k_state_reset(NiceVoiceState* st, const uint32_t* event_off, uin
     st[v] = s;
 }
 
+int record_pair_begin(zcu_ctx* ctx, std::vector<cudaEvent_t>& ev, size_t used) {
+    if (used + 2 > ev.size()) {
+        ev.resize(used + 2, nullptr);
+        ZCU_CUDA(ctx, cudaEventCreate(&ev[used]));
+        ZCU_CUDA(ctx, cudaEventCreate(&ev[used + 1]));
+    }
+    ZCU_CUDA(ctx, cudaEventRecord(ev[used], ctx->stream));
+    return ZCU_OK;
+}
+
+// ZCU_RENDER_SCAN: per block of chunks  zero-state pass -> per-voice chain -> render -> ordered partial sum
+int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+    const zcu_render_config& c = r->cfg;
+    ZCU_CUDA(ctx, cudaMemsetAsync(r->d_fstate, 0, (size_t)c.voices * sizeof(double2), ctx->stream));
+    constexpr int RT = 64;
+    const size_t smem = scan_render_smem_bytes<RT>();
+    static bool attr_set = false;
+    if (!attr_set) {
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_scan_render<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_scan_render<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_scan_render<1, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_scan_render<2, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    for (uint32_t F0 = 0; F0 < end_frame; F0 += r->block_frames) {
+        ScanArgs a;
+        a.V = c.voices;
+        a.C = c.channels;
+        a.L = c.buffer_frames;
+        a.total_frames = c.total_frames;
+        a.F0 = F0;
+        a.F1 = std::min(F0 + r->block_frames, end_frame);
+        a.nchunks = (a.F1 - a.F0 + a.L - 1) / a.L;
+        a.nvgroups = r->nwarps;
+        a.sample_rate = c.sample_rate;
+        a.color = r->d_color;
+        a.gains = r->d_gains;
+        a.event_off = r->d_event_off;
+        a.events = r->d_events;
+        a.snaps = r->d_snaps;
+        a.cursor = r->d_cursor;
+        a.zs = r->d_zs;
+        a.M = r->d_M;
+        a.sstart = r->d_sstart;
+        a.fstate = r->d_fstate;
+        a.partial = r->d_partial;
+        a.vout = vout;
+        a.vout_first = vout_first;
+        a.vout_frames = vout_frames;
+        const uint32_t tasks = a.nvgroups * a.nchunks;
+        const uint32_t grid = (tasks + 3) / 4;
+        const bool prof = r->profiling && !vout;
+        if (prof) {
+            int rc = record_pair_begin(ctx, r->ev_aux, r->ev_aux_used);
+            if (rc != ZCU_OK) return rc;
+        }
+        k_nice_scan_zs<<<grid, 128, 0, ctx->stream>>>(a);
+        if (prof) {
+            ZCU_CUDA(ctx, cudaEventRecord(r->ev_aux[r->ev_aux_used + 1], ctx->stream));
+            r->ev_aux_used += 2;
+        }
+        k_nice_scan_prefix<<<(c.voices + 127) / 128, 128, 0, ctx->stream>>>(a);
+        if (prof) {
+            int rc = record_pair_begin(ctx, r->ev, r->ev_used);
+            if (rc != ZCU_OK) return rc;
+        }
+        if (vout) {
+            if (c.channels == 2)
+                k_nice_scan_render<2, true, RT><<<grid, 128, smem, ctx->stream>>>(a);
+            else
+                k_nice_scan_render<1, true, RT><<<grid, 128, smem, ctx->stream>>>(a);
+            ctx->launches += 3;
+        } else {
+            if (c.channels == 2)
+                k_nice_scan_render<2, false, RT><<<grid, 128, smem, ctx->stream>>>(a);
+            else
+                k_nice_scan_render<1, false, RT><<<grid, 128, smem, ctx->stream>>>(a);
+            if (prof) {
+                ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used + 1], ctx->stream));
+                r->ev_used += 2;
+            }
+            const size_t n = (size_t)(a.F1 - a.F0) * c.channels;
+            k_partial_reduce<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(r->d_partial, mix + (size_t)F0 * c.channels, r->nwarps, n);
+            ctx->launches += 4;
+        }
+        ZCU_CUDA(ctx, cudaGetLastError());
+    }
+    return ZCU_OK;
+}
+
 int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+    if (r->cfg.mode == ZCU_RENDER_SCAN) return render_blocks_scan(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
     const zcu_render_config& c = r->cfg;
     k_state_reset<<<(c.voices + 127) / 128, 128, 0, ctx->stream>>>(r->d_state, r->d_event_off, c.voices);
     ctx->launches++;
@@ -140,7 +242,7 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     ZCU_REQUIRE(ctx, cfg->instrument == ZCU_INSTR_NICE, "unknown instrument");
     ZCU_REQUIRE(ctx, cfg->channels == 1 || cfg->channels == 2, "channels must be 1 or 2");
     ZCU_REQUIRE(ctx, cfg->voices > 0 && cfg->buffer_frames > 0 && cfg->total_frames > 0, "empty render");
-    ZCU_REQUIRE(ctx, cfg->mode == ZCU_RENDER_EXACT, "only ZCU_RENDER_EXACT is implemented");
+    ZCU_REQUIRE(ctx, cfg->mode == ZCU_RENDER_EXACT || cfg->mode == ZCU_RENDER_SCAN, "unknown render mode");
     zcu_render* r = new (std::nothrow) zcu_render();
     if (!r) return ZCU_ERR_OOM;
     r->d_color = r->d_gains = r->d_partial = nullptr;
@@ -151,12 +253,20 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     r->nevents = 0;
     r->profiling = false;
     r->ev_used = 0;
+    r->ev_aux_used = 0;
+    r->nchunks_total = 0;
+    r->d_snaps = nullptr;
+    r->d_cursor = nullptr;
+    r->d_zs = r->d_sstart = nullptr;
+    r->d_M = nullptr;
+    r->d_fstate = nullptr;
     r->debug_skip_mask = 0;
     r->d_debug_cycles = nullptr;
     if (const char* m = getenv("ZCU_RENDER_DEBUG_SKIP_MASK")) r->debug_skip_mask = (uint32_t)atoi(m);  // profiling aid, wrong results
     r->ctx = ctx;
     r->cfg = *cfg;
-    const uint32_t bb = cfg->block_buffers ? cfg->block_buffers : 64;
+    const bool scan = cfg->mode == ZCU_RENDER_SCAN;
+    const uint32_t bb = cfg->block_buffers ? cfg->block_buffers : (scan ? 256 : 64);
     r->block_frames = bb * cfg->buffer_frames;
     r->nwarps = (cfg->voices + 31) / 32;
     const uint32_t V = cfg->voices, C = cfg->channels;
@@ -165,6 +275,15 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     if (e == cudaSuccess) e = cudaMalloc(&r->d_state, (size_t)V * sizeof(NiceVoiceState));
     if (e == cudaSuccess) e = cudaMalloc(&r->d_event_off, (size_t)(V + 1) * 4);
     if (e == cudaSuccess) e = cudaMalloc(&r->d_partial, (size_t)r->nwarps * r->block_frames * C * 4);
+    if (scan) {
+        r->nchunks_total = (cfg->total_frames + cfg->buffer_frames - 1) / cfg->buffer_frames;
+        const size_t bc = (size_t)bb * V;
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_cursor, (size_t)r->nchunks_total * V * 4);
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_zs, bc * sizeof(float2));
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_M, bc * sizeof(Mat2));
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_sstart, bc * sizeof(float2));
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_fstate, (size_t)V * sizeof(double2));
+    }
     if (e != cudaSuccess) {
         zcu_render_free(r);
         return zcu_fail(ctx, ZCU_ERR_OOM, "render allocation failed: %s", cudaGetErrorString(e));
@@ -203,7 +322,15 @@ void zcu_render_free(zcu_render* r) {
     cudaFree(r->d_events);
     cudaFreeHost(r->h_events);
     cudaFree(r->d_partial);
+    cudaFree(r->d_snaps);
+    cudaFree(r->d_cursor);
+    cudaFree(r->d_zs);
+    cudaFree(r->d_M);
+    cudaFree(r->d_sstart);
+    cudaFree(r->d_fstate);
     for (cudaEvent_t e : r->ev)
+        if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : r->ev_aux)
         if (e) cudaEventDestroy(e);
     delete r;
 }
@@ -218,8 +345,11 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
         ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(r->d_events);
         cudaFreeHost(r->h_events);
+        cudaFree(r->d_snaps);
         r->d_events = nullptr;
         r->h_events = nullptr;
+        r->d_snaps = nullptr;
+        if (r->cfg.mode == ZCU_RENDER_SCAN) ZCU_CUDA(ctx, cudaMalloc(&r->d_snaps, (size_t)(n ? n : 1) * sizeof(EnvSnap)));
         ZCU_CUDA(ctx, cudaMalloc(&r->d_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
         ZCU_CUDA(ctx, cudaMallocHost(&r->h_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
     } else {
@@ -234,10 +364,24 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
         d.freq = events_host[i].freq;
         d.note_on = events_host[i].note_on;
         d.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, r->cfg.sample_rate);
-        d.pad[0] = d.pad[1] = d.pad[2] = 0;
+        d.cnt0 = d.flags = d.pad = 0;
     }
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, r->h_events, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
+    if (r->cfg.mode == ZCU_RENDER_SCAN) {
+        PrepassArgs p;
+        p.V = V;
+        p.L = r->cfg.buffer_frames;
+        p.nchunks_total = r->nchunks_total;
+        p.sample_rate = r->cfg.sample_rate;
+        p.event_off = r->d_event_off;
+        p.events = r->d_events;
+        p.snaps = r->d_snaps;
+        p.cursor = r->d_cursor;
+        k_nice_prepass<<<(V + 63) / 64, 64, 0, ctx->stream>>>(p);
+        ctx->launches++;
+        ZCU_CUDA(ctx, cudaGetLastError());
+    }
     return ZCU_OK;
 }
 
@@ -262,6 +406,7 @@ int zcu_render_set_profiling(zcu_render* r, int enabled) {
     if (!r) return ZCU_ERR_INVALID;
     r->profiling = enabled != 0;
     r->ev_used = 0;
+    r->ev_aux_used = 0;
     return ZCU_OK;
 }
 
@@ -281,10 +426,26 @@ int zcu_render_kernel_ms(zcu_ctx* ctx, zcu_render* r, float* total_ms, uint32_t*
     return ZCU_OK;
 }
 
+int zcu_render_aux_kernel_ms(zcu_ctx* ctx, zcu_render* r, float* total_ms, uint32_t* launches) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, r && total_ms && launches, "null argument");
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    double sum = 0.0;
+    for (size_t i = 0; i + 1 < r->ev_aux_used; i += 2) {
+        float ms = 0.0f;
+        ZCU_CUDA(ctx, cudaEventElapsedTime(&ms, r->ev_aux[i], r->ev_aux[i + 1]));
+        sum += ms;
+    }
+    *total_ms = (float)sum;
+    *launches = (uint32_t)(r->ev_aux_used / 2);
+    r->ev_aux_used = 0;
+    return ZCU_OK;
+}
+
 uint64_t zcu_render_launches_per_run(const zcu_render* r) {
     if (!r) return 0;
     const uint64_t nblocks = (r->cfg.total_frames + r->block_frames - 1) / r->block_frames;
-    return 1 + 2 * nblocks;
+    return r->cfg.mode == ZCU_RENDER_SCAN ? 4 * nblocks : 1 + 2 * nblocks;
 }
 
 }  // extern "C"

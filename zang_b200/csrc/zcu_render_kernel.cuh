@@ -45,7 +45,9 @@ struct __align__(16) DevEvent {
     float freq;
     int32_t note_on;
     float cutoff;
-    uint32_t pad[3];
+    uint32_t cnt0;   // ZCU_RENDER_SCAN: PulseOsc.cnt at this event's frame (k_nice_prepass)
+    uint32_t flags;  // ZCU_RENDER_SCAN: EV_SUPERSEDED | EV_CHANGED (k_nice_prepass)
+    uint32_t pad;
 };
 
 struct RenderArgs {

@@ -560,6 +560,12 @@ class Render:
         _check(self.ctx, lib.zcu_render_kernel_ms(self.ctx._h, self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def aux_kernel_ms(self):
+        """ZCU_RENDER_SCAN: (summed milliseconds, launches) of the zero-state filter pass since the last call."""
+        ms, n = C.c_float(), C.c_uint32()
+        _check(self.ctx, lib.zcu_render_aux_kernel_ms(self.ctx._h, self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
     @property
     def launches_per_run(self):
         return int(lib.zcu_render_launches_per_run(self._h))
