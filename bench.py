@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--seconds", type=float, default=SECONDS)
     ap.add_argument("--block-buffers", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="scan", choices=["exact", "scan"],
+    ap.add_argument("--mode", default="segments", choices=["exact", "scan", "segments"],
                     help="exact: sequential-in-time kernel, bit-exact per voice; scan: time-parallel chunks (exact PulseOsc/Envelope, "
                          "filter start states from a 2x2 f64 scan; per-voice error <= 1e-5, the north-star tolerance)")
     return ap.parse_args()
@@ -199,7 +199,7 @@ def main():
     mix_t = torch.zeros((total_frames, 2), dtype=torch.float32, device="cuda")
     mix = ctx.wrap(mix_t.data_ptr(), total_frames, 2)
     r = Render(ctx, V, total_frames, wl["color"], wl["gains"], channels=2, sample_rate=SAMPLE_RATE, buffer_frames=BUFFER_FRAMES,
-               block_buffers=args.block_buffers, mode=L.RENDER_SCAN if args.mode == "scan" else L.RENDER_EXACT)
+               block_buffers=args.block_buffers, mode={"exact": L.RENDER_EXACT, "scan": L.RENDER_SCAN, "segments": L.RENDER_SEGMENTS}[args.mode])
     r.set_events(off_host, ev_host)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 

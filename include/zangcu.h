@@ -371,9 +371,15 @@ typedef struct zcu_render_config {
     uint32_t channels;        /* 1 or 2: channels of the mix */
     float sample_rate;
     uint32_t first_seed;      /* Noise seed of voice 0 */
-    int32_t mode;             /* ZCU_RENDER_EXACT or ZCU_RENDER_SCAN */
+    int32_t mode;             /* ZCU_RENDER_* */
 } zcu_render_config;
-enum { ZCU_RENDER_EXACT = 0, ZCU_RENDER_SCAN = 1 };
+/* EXACT: every voice sequential in time; per-voice output bit-exact.
+ * SCAN: one warp task per (32 voices, mix buffer); PulseOsc/Envelope start every buffer from exact closed forms, the
+ *   Filter from a chained 2x2 f64 scan over per-buffer zero-state responses.  Per-voice error <= 1e-5 of full scale.
+ * SEGMENTS: the time axis of a launch is cut into as many long segments as fill the GPU once; each segment is rendered
+ *   sequentially, its Filter state warmed up over preceding buffers until the window's homogeneous map is <= 1e-8.
+ *   Same tolerance as SCAN, about half its work; identical to EXACT when there are enough voices for one segment. */
+enum { ZCU_RENDER_EXACT = 0, ZCU_RENDER_SCAN = 1, ZCU_RENDER_SEGMENTS = 2 };
 
 /* per-voice constants: NiceInstrument.color (modules.zig:198) and the mix gains [voices][channels] */
 int zcu_render_create(zcu_ctx*, const zcu_render_config* cfg, const float* voice_color_host,
@@ -393,6 +399,11 @@ int zcu_render_set_profiling(zcu_render*, int enabled);
 int zcu_render_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* launches);
 /* ZCU_RENDER_SCAN only: the same for the zero-state filter pass that precedes each render-kernel launch */
 int zcu_render_aux_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* launches);
+
+/* ZCU_RENDER_SEGMENTS diagnostics of the last run: segments per launch, mix buffers per segment, and the sum / max
+ * over all (voice group, segment) warp tasks of the warm-up length in mix buffers */
+int zcu_render_segment_info(zcu_ctx*, zcu_render*, uint32_t* segments, uint32_t* buffers_per_segment, uint32_t* warm_sum,
+                            uint32_t* warm_max);
 
 /* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
 /* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */

@@ -70,14 +70,24 @@ def test_fused_mix(ctx, channels):
 SCAN_TOL = 1e-5  # BASELINE.json north_star: max abs error <= 1e-5 of full scale (a voice's full scale is 1.0)
 
 
+@pytest.fixture(params=["scan", "segments"])
+def tmode(request, monkeypatch):
+    """The two time-parallel render modes.  SEGMENTS sizes its segments to the GPU, which on a small test job means one
+    segment (= the exact render), so the tests force several segments per launch."""
+    if request.param == "segments":
+        monkeypatch.setenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH", "5")
+        return L.RENDER_SEGMENTS
+    return L.RENDER_SCAN
+
+
 @pytest.mark.parametrize("voices,total,bb", [(70, 8 * 1024, 3), (33, 5 * 1024 + 300, 0), (64, 40 * 1024, 16)])
-def test_scan_mode_voices_within_tolerance(ctx, voices, total, bb):
+def test_scan_mode_voices_within_tolerance(ctx, tmode, voices, total, bb):
     """ZCU_RENDER_SCAN (time-parallel chunks, zcu_render_scan.cuh): PulseOsc and Envelope start every chunk from an
     exact closed form, the Filter from a chained f64 2x2 scan, so per-voice output is held to the north-star
     tolerance instead of bit-exactness; where the filter has not yet run (before a voice's first note) it is exact."""
     wl = small_workload(voices, total, seed=31 + voices)
     _, want, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(0, total))
-    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=bb, mode=L.RENDER_SCAN)
+    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=bb, mode=tmode)
     r.set_events(wl["event_off"], wl["events"])
     vo = ctx.buf(total, voices)
     r.run_voices(0, vo)
@@ -93,12 +103,43 @@ def test_scan_mode_voices_within_tolerance(ctx, voices, total, bb):
     r.free()
 
 
-def test_scan_mode_matches_exact_mode_mix(ctx):
+def test_segments_mode_with_one_segment_is_the_exact_render(ctx, monkeypatch):
+    monkeypatch.setenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH", "1")
+    voices, total = 50, 7 * 1024 + 11
+    wl = small_workload(voices, total, seed=5)
+    _, want, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(0, total))
+    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=3, mode=L.RENDER_SEGMENTS)
+    r.set_events(wl["event_off"], wl["events"])
+    vo = ctx.buf(total, voices)
+    r.run_voices(0, vo)
+    assert_bit_exact(vo.download(), want, "segments mode, one segment per launch")
+    r.free()
+
+
+def test_segments_mode_warm_up_is_adaptive(ctx, monkeypatch):
+    """Low notes (cutoff = 8 x freq, resonance 0.7) damp slowly: the warm-up window must grow until its homogeneous
+    map is <= 1e-8, and the result must still be within tolerance."""
+    monkeypatch.setenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH", "4")
+    voices, total = 32, 48 * 1024
+    wl = synth.polyphony_bank(voices, total, SR, seed=77, mean_on=0.3, mean_off=0.02)
+    wl["events"]["freq"] *= np.float32(0.125)  # three octaves down: decay over several mix buffers
+    _, want, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(0, total))
+    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=0, mode=L.RENDER_SEGMENTS)
+    r.set_events(wl["event_off"], wl["events"])
+    vo = ctx.buf(total, voices)
+    r.run_voices(0, vo)
+    assert_close(vo.download(), want, SCAN_TOL, "segments mode, slow filters")
+    info = r.segment_info()
+    assert info["segments"] == 4 and info["warm_max"] >= 4, info
+    r.free()
+
+
+def test_scan_mode_matches_exact_mode_mix(ctx, tmode):
     voices, total = 200, 6 * 1024 + 100
     wl = small_workload(voices, total, seed=7)
     want, _, _ = oracle.render_nice(wl, total, SR, channels=2)
     mixes = []
-    for mode in (L.RENDER_EXACT, L.RENDER_SCAN):
+    for mode in (L.RENDER_EXACT, tmode):
         r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=2, mode=mode)
         r.set_events(wl["event_off"], wl["events"])
         mix = ctx.buf(total, 2)

@@ -25,7 +25,7 @@ FMT_UNSIGNED8, FMT_SIGNED16_LSB, FMT_SIGNED24_LSB, FMT_SIGNED32_LSB = range(4)
 DIST_OVERDRIVE, DIST_CLIP = 0, 1
 AUDIO_SIGNED8, AUDIO_SIGNED16_LSB = 0, 1
 INSTR_NICE = 0
-RENDER_EXACT, RENDER_SCAN = 0, 1
+RENDER_EXACT, RENDER_SCAN, RENDER_SEGMENTS = 0, 1, 2
 MAX_POLYPHONY = 32
 
 # ---- POD dtypes -------------------------------------------------------------------------------------
@@ -203,6 +203,7 @@ PROTOTYPES = {
     "zcu_render_set_profiling": (_I, [_P, _I]),
     "zcu_render_kernel_ms": (_I, [_P, _P, _P, _P]),
     "zcu_render_aux_kernel_ms": (_I, [_P, _P, _P, _P]),
+    "zcu_render_segment_info": (_I, [_P, _P, _P, _P, _P, _P]),
     "zcu_nccl_unique_id": (_I, [_P]),
     "zcu_nccl_init": (_I, [_P, _I, _I, _P]),
     "zcu_nccl_reduce_mix": (_I, [_P, _P, _I]),

@@ -13,12 +13,14 @@
 // (deterministic) into the mix.
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <new>
 #include <vector>
 
 #include "zcu_internal.h"
 #include "zcu_render_kernel.cuh"
 #include "zcu_render_scan.cuh"
+#include "zcu_render_seg.cuh"
 
 using namespace zcu;
 
@@ -50,6 +52,11 @@ struct zcu_render {
     Mat2* d_M;             // [block chunks][V]
     float2* d_sstart;      // [block chunks][V]
     double2* d_fstate;     // [V]
+    // ZCU_RENDER_SEGMENTS (zcu_render_seg.cuh)
+    float2* d_carry[2];    // [V] filter state at a launch boundary, double buffered
+    uint32_t* d_warm_stats;  // [2] sum / max of warm-up buffers over the warp tasks of the last run
+    uint32_t seg_slots;    // resident warps of k_nice_seg_render on this device
+    uint32_t last_nseg, last_seg_chunks;
 };
 
 namespace {
@@ -163,7 +170,103 @@ int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uin
     return ZCU_OK;
 }
 
+// ZCU_RENDER_SEGMENTS: one launch per block of mix buffers; (voice groups x segments) fills the resident warps once
+int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+    const zcu_render_config& c = r->cfg;
+    constexpr int RT = 64;
+    const size_t smem = scan_render_smem_bytes<RT>();
+    static bool attr_set = false;
+    if (!attr_set) {
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<1, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<2, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    if (r->seg_slots == 0) {
+        int per_sm = 0;
+        ZCU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nice_seg_render<2, false, RT>, 128, smem));
+        r->seg_slots = (uint32_t)std::max(1, per_sm) * (uint32_t)ctx->sm_count * 4u;
+    }
+    ZCU_CUDA(ctx, cudaMemsetAsync(r->d_carry[0], 0, (size_t)c.voices * sizeof(float2), ctx->stream));
+    ZCU_CUDA(ctx, cudaMemsetAsync(r->d_warm_stats, 0, 2 * sizeof(uint32_t), ctx->stream));
+    int flip = 0;
+    for (uint32_t F0 = 0; F0 < end_frame; F0 += r->block_frames) {
+        SegArgs g;
+        ScanArgs& a = g.s;
+        a.V = c.voices;
+        a.C = c.channels;
+        a.L = c.buffer_frames;
+        a.total_frames = c.total_frames;
+        a.F0 = F0;
+        a.F1 = std::min(F0 + r->block_frames, end_frame);
+        a.nchunks = (a.F1 - a.F0 + a.L - 1) / a.L;
+        a.nvgroups = r->nwarps;
+        a.sample_rate = c.sample_rate;
+        a.color = r->d_color;
+        a.gains = r->d_gains;
+        a.event_off = r->d_event_off;
+        a.events = r->d_events;
+        a.snaps = r->d_snaps;
+        a.cursor = r->d_cursor;
+        a.zs = nullptr;
+        a.M = nullptr;
+        a.sstart = nullptr;
+        a.fstate = nullptr;
+        a.partial = r->d_partial;
+        a.vout = vout;
+        a.vout_first = vout_first;
+        a.vout_frames = vout_frames;
+        // segments: as many as fill the resident warps once, each at least 8 mix buffers long
+        uint32_t nseg = std::max(1u, r->seg_slots / a.nvgroups);
+        uint32_t min_chunks = 8;
+        if (const char* e = getenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH")) {  // tuning / tests
+            nseg = std::max(1, atoi(e));
+            min_chunks = 1;
+        }
+        uint32_t seg_chunks = std::max((a.nchunks + nseg - 1) / nseg, std::min(min_chunks, a.nchunks));
+        nseg = (a.nchunks + seg_chunks - 1) / seg_chunks;
+        g.nseg = nseg;
+        g.seg_chunks = seg_chunks;
+        g.carry = nullptr;
+        g.warm_stats = r->d_warm_stats;
+        r->last_nseg = nseg;
+        r->last_seg_chunks = seg_chunks;
+        const uint32_t tasks = a.nvgroups * nseg;
+        const uint32_t grid = (tasks + 3) / 4;
+        const float2* cin = r->d_carry[flip];
+        float2* cout = r->d_carry[flip ^ 1];
+        flip ^= 1;
+        if (vout) {
+            if (c.channels == 2)
+                k_nice_seg_render<2, true, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
+            else
+                k_nice_seg_render<1, true, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
+            ctx->launches++;
+        } else {
+            if (r->profiling) {
+                int rc = record_pair_begin(ctx, r->ev, r->ev_used);
+                if (rc != ZCU_OK) return rc;
+            }
+            if (c.channels == 2)
+                k_nice_seg_render<2, false, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
+            else
+                k_nice_seg_render<1, false, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
+            if (r->profiling) {
+                ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used + 1], ctx->stream));
+                r->ev_used += 2;
+            }
+            const size_t n = (size_t)(a.F1 - a.F0) * c.channels;
+            k_partial_reduce<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(r->d_partial, mix + (size_t)F0 * c.channels, r->nwarps, n);
+            ctx->launches += 2;
+        }
+        ZCU_CUDA(ctx, cudaGetLastError());
+    }
+    return ZCU_OK;
+}
+
 int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+    if (r->cfg.mode == ZCU_RENDER_SEGMENTS) return render_blocks_seg(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
     if (r->cfg.mode == ZCU_RENDER_SCAN) return render_blocks_scan(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
     const zcu_render_config& c = r->cfg;
     k_state_reset<<<(c.voices + 127) / 128, 128, 0, ctx->stream>>>(r->d_state, r->d_event_off, c.voices);
@@ -242,7 +345,7 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     ZCU_REQUIRE(ctx, cfg->instrument == ZCU_INSTR_NICE, "unknown instrument");
     ZCU_REQUIRE(ctx, cfg->channels == 1 || cfg->channels == 2, "channels must be 1 or 2");
     ZCU_REQUIRE(ctx, cfg->voices > 0 && cfg->buffer_frames > 0 && cfg->total_frames > 0, "empty render");
-    ZCU_REQUIRE(ctx, cfg->mode == ZCU_RENDER_EXACT || cfg->mode == ZCU_RENDER_SCAN, "unknown render mode");
+    ZCU_REQUIRE(ctx, cfg->mode == ZCU_RENDER_EXACT || cfg->mode == ZCU_RENDER_SCAN || cfg->mode == ZCU_RENDER_SEGMENTS, "unknown render mode");
     zcu_render* r = new (std::nothrow) zcu_render();
     if (!r) return ZCU_ERR_OOM;
     r->d_color = r->d_gains = r->d_partial = nullptr;
@@ -260,13 +363,25 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     r->d_zs = r->d_sstart = nullptr;
     r->d_M = nullptr;
     r->d_fstate = nullptr;
+    r->d_carry[0] = r->d_carry[1] = nullptr;
+    r->d_warm_stats = nullptr;
+    r->seg_slots = 0;
+    r->last_nseg = r->last_seg_chunks = 0;
     r->debug_skip_mask = 0;
     r->d_debug_cycles = nullptr;
     if (const char* m = getenv("ZCU_RENDER_DEBUG_SKIP_MASK")) r->debug_skip_mask = (uint32_t)atoi(m);  // profiling aid, wrong results
     r->ctx = ctx;
     r->cfg = *cfg;
     const bool scan = cfg->mode == ZCU_RENDER_SCAN;
-    const uint32_t bb = cfg->block_buffers ? cfg->block_buffers : (scan ? 256 : 64);
+    const bool segm = cfg->mode == ZCU_RENDER_SEGMENTS;
+    uint32_t bb = cfg->block_buffers ? cfg->block_buffers : (scan ? 256 : 64);
+    if (segm && !cfg->block_buffers) {
+        // one launch for as much of the job as a 3 GB partial-mix buffer allows (the whole 60 s job at 4096 voices)
+        const uint64_t per_buffer = (uint64_t)((cfg->voices + 31) / 32) * cfg->buffer_frames * cfg->channels * 4;
+        const uint64_t fit = std::max<uint64_t>(1, 3000000000ull / per_buffer);
+        const uint64_t all = (cfg->total_frames + cfg->buffer_frames - 1) / cfg->buffer_frames;
+        bb = (uint32_t)std::min(fit, all);
+    }
     r->block_frames = bb * cfg->buffer_frames;
     r->nwarps = (cfg->voices + 31) / 32;
     const uint32_t V = cfg->voices, C = cfg->channels;
@@ -275,6 +390,13 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     if (e == cudaSuccess) e = cudaMalloc(&r->d_state, (size_t)V * sizeof(NiceVoiceState));
     if (e == cudaSuccess) e = cudaMalloc(&r->d_event_off, (size_t)(V + 1) * 4);
     if (e == cudaSuccess) e = cudaMalloc(&r->d_partial, (size_t)r->nwarps * r->block_frames * C * 4);
+    if (segm) {
+        r->nchunks_total = (cfg->total_frames + cfg->buffer_frames - 1) / cfg->buffer_frames;
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_cursor, (size_t)r->nchunks_total * V * 4);
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_carry[0], (size_t)V * sizeof(float2));
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_carry[1], (size_t)V * sizeof(float2));
+        if (e == cudaSuccess) e = cudaMalloc(&r->d_warm_stats, 2 * sizeof(uint32_t));
+    }
     if (scan) {
         r->nchunks_total = (cfg->total_frames + cfg->buffer_frames - 1) / cfg->buffer_frames;
         const size_t bc = (size_t)bb * V;
@@ -328,6 +450,9 @@ void zcu_render_free(zcu_render* r) {
     cudaFree(r->d_M);
     cudaFree(r->d_sstart);
     cudaFree(r->d_fstate);
+    cudaFree(r->d_carry[0]);
+    cudaFree(r->d_carry[1]);
+    cudaFree(r->d_warm_stats);
     for (cudaEvent_t e : r->ev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : r->ev_aux)
@@ -349,7 +474,7 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
         r->d_events = nullptr;
         r->h_events = nullptr;
         r->d_snaps = nullptr;
-        if (r->cfg.mode == ZCU_RENDER_SCAN) ZCU_CUDA(ctx, cudaMalloc(&r->d_snaps, (size_t)(n ? n : 1) * sizeof(EnvSnap)));
+        if (r->cfg.mode != ZCU_RENDER_EXACT) ZCU_CUDA(ctx, cudaMalloc(&r->d_snaps, (size_t)(n ? n : 1) * sizeof(EnvSnap)));
         ZCU_CUDA(ctx, cudaMalloc(&r->d_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
         ZCU_CUDA(ctx, cudaMallocHost(&r->h_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
     } else {
@@ -357,18 +482,35 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     }
     r->nevents = n;
     // per-call host scalar of modules.zig:231-234 (cos, sqrt): once per event, on the host
+    // (a small direct-mapped memo keyed by the bits of freq: a bank plays few distinct pitches, and the memo returns
+    // the very value the function would)
+    struct Memo { uint32_t key; float cutoff; bool valid; };
+    static thread_local Memo memo[1024];
+    static thread_local float memo_sr = 0.0f;
+    if (memo_sr != r->cfg.sample_rate) {
+        for (Memo& m : memo) m.valid = false;
+        memo_sr = r->cfg.sample_rate;
+    }
     for (uint32_t i = 0; i < n; i++) {
         DevEvent& d = r->h_events[i];
         d.frame = events_host[i].frame;
         d.note_id = events_host[i].note_id;
         d.freq = events_host[i].freq;
         d.note_on = events_host[i].note_on;
-        d.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, r->cfg.sample_rate);
+        uint32_t key;
+        memcpy(&key, &events_host[i].freq, 4);
+        Memo& m = memo[(key * 2654435761u) >> 22];
+        if (!m.valid || m.key != key) {
+            m.key = key;
+            m.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, r->cfg.sample_rate);
+            m.valid = true;
+        }
+        d.cutoff = m.cutoff;
         d.cnt0 = d.flags = d.pad = 0;
     }
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, r->h_events, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
-    if (r->cfg.mode == ZCU_RENDER_SCAN) {
+    if (r->cfg.mode != ZCU_RENDER_EXACT) {
         PrepassArgs p;
         p.V = V;
         p.L = r->cfg.buffer_frames;
@@ -445,7 +587,21 @@ int zcu_render_aux_kernel_ms(zcu_ctx* ctx, zcu_render* r, float* total_ms, uint3
 uint64_t zcu_render_launches_per_run(const zcu_render* r) {
     if (!r) return 0;
     const uint64_t nblocks = (r->cfg.total_frames + r->block_frames - 1) / r->block_frames;
+    if (r->cfg.mode == ZCU_RENDER_SEGMENTS) return 2 * nblocks;
     return r->cfg.mode == ZCU_RENDER_SCAN ? 4 * nblocks : 1 + 2 * nblocks;
+}
+
+int zcu_render_segment_info(zcu_ctx* ctx, zcu_render* r, uint32_t* segments, uint32_t* buffers_per_segment, uint32_t* warm_sum, uint32_t* warm_max) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, r && r->cfg.mode == ZCU_RENDER_SEGMENTS, "not a ZCU_RENDER_SEGMENTS render");
+    uint32_t h[2] = {0, 0};
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ZCU_CUDA(ctx, cudaMemcpy(h, r->d_warm_stats, sizeof(h), cudaMemcpyDeviceToHost));
+    if (segments) *segments = r->last_nseg;
+    if (buffers_per_segment) *buffers_per_segment = r->last_seg_chunks;
+    if (warm_sum) *warm_sum = h[0];
+    if (warm_max) *warm_max = h[1];
+    return ZCU_OK;
 }
 
 }  // extern "C"

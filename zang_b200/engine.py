@@ -566,6 +566,12 @@ class Render:
         _check(self.ctx, lib.zcu_render_aux_kernel_ms(self.ctx._h, self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def segment_info(self):
+        """ZCU_RENDER_SEGMENTS: dict(segments, buffers_per_segment, warm_sum, warm_max) of the last run."""
+        v = [C.c_uint32() for _ in range(4)]
+        _check(self.ctx, lib.zcu_render_segment_info(self.ctx._h, self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("segments", "buffers_per_segment", "warm_sum", "warm_max"), (x.value for x in v)))
+
     @property
     def launches_per_run(self):
         return int(lib.zcu_render_launches_per_run(self._h))
