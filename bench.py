@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--seconds", type=float, default=SECONDS)
     ap.add_argument("--block-buffers", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-modes", action="store_true", help="skip the comparison runs of the other render modes")
     ap.add_argument("--mode", default="segments", choices=["exact", "scan", "segments"],
                     help="exact: sequential-in-time kernel, bit-exact per voice; scan: time-parallel chunks (exact PulseOsc/Envelope, "
                          "filter start states from a 2x2 f64 scan; per-voice error <= 1e-5, the north-star tolerance)")
@@ -73,6 +74,19 @@ def ncu_traffic_bytes_per_launch():
             return json.load(f)
     except Exception:
         return None
+
+
+MODE_INFO = {
+    "exact": ("k_render_nice", "k_render_nice (fused PulseOsc+Filter+Envelope+mix, Trigger replay on device, sequential in time)",
+              "exact: every voice sequential in time; per-voice output bit-exact vs the oracle"),
+    "scan": ("k_nice_scan_render", "k_nice_scan_render (pass 3 of zero-state pass / 2x2 f64 chain / render; one warp per 32 voices x mix buffer)",
+             "scan: one warp task per (32 voices, mix buffer); PulseOsc/Envelope exact closed forms, Filter start states from a chained "
+             "2x2 f64 scan; per-voice error <= 1e-5 of full scale (tests/test_gpu_instrument.py)"),
+    "segments": ("k_nice_seg_render", "k_nice_seg_render (fused PulseOsc+Filter+Envelope+mix; (32 voices x time segment) per warp, Filter warm-up "
+                 "verified by the window's homogeneous map)",
+                 "segments: time axis cut into GPU-filling segments rendered sequentially; PulseOsc/Envelope exact closed forms, Filter state "
+                 "by warm-up until the window map <= 1e-8; per-voice error <= 1e-5 of full scale (tests/test_gpu_instrument.py)"),
+}
 
 
 class ClockSampler:
@@ -267,12 +281,16 @@ def main():
         value = voice_samples / (ms_per_step * 1e-3)
         e2e_value = voice_samples / (ms_e2e_step * 1e-3)
         peak, peak_src = measured_peak()
-        block_frames = (args.block_buffers or 64) * BUFFER_FRAMES
+        kernel_key, kernel_desc, mode_desc = MODE_INFO[args.mode]
+        frames_per_launch_cfg = total_frames * args.steps / max(kern_launches, 1)
+        block_frames = int(round(frames_per_launch_cfg))
         avg_launch_ms = kern_ms / max(kern_launches, 1)
         frames_per_launch = total_frames * args.steps / max(kern_launches, 1)
         algo_bytes_per_launch = ALGO_BYTES_PER_VOICE_SAMPLE * V * frames_per_launch
         achieved = algo_bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9
         traffic = ncu_traffic_bytes_per_launch()
+        if traffic and traffic.get("kernel") != kernel_key:
+            traffic = None
         h2d = n_events * 32 + (V + 1) * 4  # device event records (note event + host-evaluated cutoff, 32 B) + offsets
         d2h = total_frames * 2 * 4
         line = {
@@ -283,19 +301,40 @@ def main():
                                    f"{args.seconds:g} s @48 kHz in 1024-frame buffers, stereo mix (BASELINE.json configs[1])",
                        "voices_per_gpu": V, "voices_total": V * world, "frames": total_frames, "block_frames": block_frames,
                        "parallelism": f"voices sharded over {world} GPU(s); one NCCL reduce of the stereo mix per job" if world > 1 else "1 GPU",
-                       "render_mode": "exact (bit-exact per voice vs oracle)",
+                       "render_mode": mode_desc,
                        "l2": "flushed between timed steps (256 MiB memset, untimed)"},
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": ms_e2e_step},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "k_render_nice (fused PulseOsc+Filter+Envelope+mix, Trigger replay on device)",
+            "roofline": {"bound": "hbm", "kernel": kernel_desc,
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
                          "algorithmic_bytes_per_launch": algo_bytes_per_launch, "avg_launch_ms": avg_launch_ms,
                          "launches_timed": int(kern_launches), "kernel_share_of_step": kern_ms / sum(ms_steps), "peak_source": peak_src,
-                         "note": "algorithmic bytes = 64 B/voice-sample of the un-fused module chain; the fused kernel keeps them in registers"},
+                         "note": "algorithmic bytes = 64 B/voice-sample of the un-fused module chain; the fused kernel keeps them in registers, so the "
+                                 "kernel is issue-bound (ncu: >90% issue slots busy), not HBM-bound; frac > 1 is the fusion"},
         }
+        if args.mode == "segments":
+            line["config"]["segments"] = r.segment_info()
+        if world == 1 and not args.no_other_modes:
+            # the same job through the other render modes (device timed, inputs resident, L2 flushed), for comparison
+            others = {}
+            for m, mid in (("exact", L.RENDER_EXACT), ("scan", L.RENDER_SCAN), ("segments", L.RENDER_SEGMENTS)):
+                if m == args.mode:
+                    continue
+                r2 = Render(ctx, V, total_frames, wl["color"], wl["gains"], channels=2, sample_rate=SAMPLE_RATE, buffer_frames=BUFFER_FRAMES, mode=mid)
+                r2.set_events(off_host, ev_host)
+
+                def step_other():
+                    mix_t.zero_()
+                    r2.run(mix)
+                step_other()
+                ms_o = timed(step_other, 3)
+                others[m] = {"ms_per_step": sum(ms_o) / len(ms_o), "value": voice_samples / (sum(ms_o) / len(ms_o) * 1e-3), "steps": 3,
+                             "render_mode": MODE_INFO[m][2]}
+                r2.free()
+            line["other_modes"] = others
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_reference_run(1, 0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
