@@ -344,6 +344,19 @@ int64_t zcu_poly_voice_spans(zcu_poly_voice* pv, const int32_t* param_note_on, f
                              uint32_t num_buffers, uint32_t last_buffer_frames, uint32_t* voice_off_out, zcu_span* spans_out,
                              uint64_t max_spans);
 
+/* A bank of monophonic voices, each with its own ImpulseQueue + Trigger (examples/example_polyphony.zig:61-92 per voice).
+ * Voice v owns events[event_off[v] .. event_off[v+1]) (absolute frames, chronological; zcu_note_event below).  Every mix
+ * buffer's events are pushed into the voice's queue (capacity 32, notes.zig:108-118) and the Trigger splits the buffer.
+ * Writes the span table of the block [first_frame, first_frame + num_frames) in the CSR layout of zcu_spans_upload:
+ * frames block relative, span.param = GLOBAL event index.  first_frame must be a multiple of buffer_frames.  Returns the
+ * span count; if it exceeds max_spans nothing is written, state is untouched and the count is returned negated. */
+struct zcu_note_event;
+typedef struct zcu_bank_trigger { zcu_trigger trigger; uint32_t next_event; } zcu_bank_trigger;
+void zcu_bank_trigger_init(zcu_bank_trigger* state, uint32_t voices, const uint32_t* event_off);
+int64_t zcu_bank_spans(zcu_bank_trigger* state, uint32_t voices, const uint32_t* event_off, const struct zcu_note_event* events,
+                       uint32_t buffer_frames, uint32_t total_frames, uint32_t first_frame, uint32_t num_frames,
+                       uint32_t* voice_off_out, zcu_span* spans_out, uint64_t max_spans);
+
 /* ---- fused instrument banks (B200-first path for the benchmark configs) ----------------------- */
 /* A note event of one voice with an ABSOLUTE frame position in the whole render.  Voice v owns
  * events[event_off[v] .. event_off[v+1]), chronological.  The device replays Trigger semantics

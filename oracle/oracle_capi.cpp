@@ -11,6 +11,7 @@
 
 #include "../include/zangcu.h"
 #include "zang_oracle.hpp"
+#include "bank_oracle.hpp"
 #include "song_oracle.hpp"
 
 using namespace zo;
@@ -479,6 +480,80 @@ double orc_render_nice(uint32_t V, uint32_t total_frames, uint32_t buffer_frames
         if (mix)
             for (uint32_t t = 0; t < nthreads; t++)
                 for (size_t i = 0; i < (size_t)total_frames * channels; i++) mix[i] += partial[t][i];
+    }
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+}
+
+// ---- instrument banks of BASELINE.json configs[2..4] (bank_oracle.hpp) --------------------------------------------
+// kind 0: SamplerVoice (voice_f = fake_sample_rate[V]; pcm = mono/multi-channel sample)   configs[3]
+// kind 1: SfxVoice     (voice_i = filter type[V]; nodes = 3 curve nodes per job; seeds first_seed + v)   configs[4]
+// kind 2: FmDetunedVoice (in0 = detune_in, in1 = index_in, [total_frames][V])   configs[2]
+// Per voice and per mix buffer: push the buffer's events into the voice's ImpulseQueue, run the Trigger, paint.
+// voices_out: [nframes][V] window of the un-mixed voice outputs starting at first_frame; mix (optional): += gains * voice.
+double orc_render_bank(int kind, uint32_t V, uint32_t total_frames, uint32_t buffer_frames, float sample_rate,
+                       const uint32_t* event_off, const zcu_note_event* events, const float* voice_f, const int32_t* voice_i,
+                       const zcu_curve_node* nodes, const uint8_t* pcm, uint64_t pcm_len, uint32_t pcm_channels, uint32_t pcm_rate,
+                       int pcm_format, const float* in0, const float* in1, uint32_t first_seed, const float* gains, uint32_t channels,
+                       float* mix, float* voices_out, uint32_t first_frame, uint32_t nframes) {
+    auto t_begin = std::chrono::steady_clock::now();
+    std::vector<float> out(buffer_frames), a0(buffer_frames), a1(buffer_frames);
+    std::vector<std::vector<float>> tb(6, std::vector<float>(buffer_frames));
+    float* temps[6];
+    for (int i = 0; i < 6; i++) temps[i] = tb[i].data();
+    for (uint32_t v = 0; v < V; v++) {
+        SamplerVoice sv;
+        SfxVoice fx(first_seed + v);
+        FmDetunedVoice fm;
+        Trigger<InstrParams> trig;
+        Notes<InstrParams>::ImpulseQueue iq;
+        std::vector<CurveNode> cn(3);
+        if (kind == 0) sv.fake_sample_rate = voice_f[v];
+        if (kind == 1) {
+            fx.type = (Filter::Type)voice_i[v];
+            for (int i = 0; i < 3; i++) cn[i] = CurveNode{nodes[3 * v + i].value, nodes[3 * v + i].t};
+            fx.nodes = cn.data();
+        }
+        const Sampler::Sample smp{pcm_channels, pcm_rate, (Sampler::Format)pcm_format, pcm, (size_t)pcm_len};
+        uint32_t ei = event_off[v];
+        const uint32_t ee = event_off[v + 1];
+        for (uint32_t start = 0; start < total_frames; start += buffer_frames) {
+            const uint32_t len = std::min(buffer_frames, total_frames - start);
+            Span span{0, len};
+            zero(span, out.data());
+            while (ei < ee && events[ei].frame < start + len) {
+                if (kind == 0)
+                    sv.iq.push(events[ei].frame - start, events[ei].note_id, Sampler::Params{events[ei].freq, smp, 0, true});
+                else
+                    iq.push(events[ei].frame - start, events[ei].note_id, InstrParams{sample_rate, events[ei].freq, events[ei].note_on != 0});
+                ei++;
+            }
+            if (kind == 0) {
+                sv.paint(span, out.data(), temps, sample_rate);
+            } else {
+                if (kind == 2)
+                    for (uint32_t f = 0; f < len; f++) {
+                        a0[f] = in0[(size_t)(start + f) * V + v];
+                        a1[f] = in1[(size_t)(start + f) * V + v];
+                    }
+                auto ctr = trig.counter(span, iq.consume());
+                Trigger<InstrParams>::NewPaintReturnValue r;
+                while (trig.next(ctr, r)) {
+                    if (kind == 1)
+                        fx.paint(r.span, out.data(), temps, r.note_id_changed, {r.params.sample_rate, r.params.note_on});
+                    else
+                        fm.paint(r.span, out.data(), temps, r.note_id_changed, r.params, a0.data(), a1.data());
+                }
+            }
+            if (mix)
+                for (uint32_t f = 0; f < len; f++)
+                    for (uint32_t c = 0; c < channels; c++)
+                        mix[(size_t)(start + f) * channels + c] += gains[(size_t)v * channels + c] * out[f];
+            if (voices_out)
+                for (uint32_t f = 0; f < len; f++) {
+                    const uint32_t af = start + f;
+                    if (af >= first_frame && af < first_frame + nframes) voices_out[(size_t)(af - first_frame) * V + v] = out[f];
+                }
+        }
     }
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
 }

@@ -75,8 +75,28 @@ def render_case():
     return {"workload": digest(wl["event_off"], wl["events"], wl["color"], wl["gains"]), "voices": digest(vo), "mix": digest(mix)}
 
 
+def bank_cases():
+    """configs[2..4] graphs (oracle/bank_oracle.hpp) on small seeded workloads.  The FM and sampler chains evaluate libm
+    sinf / atanf per sample, so their digests pin the oracle on THIS libm only (values are rounded to 1e-5 before hashing)."""
+    def q(a):
+        return np.round(a.astype(np.float64) * 1e5).astype(np.int64)
+    out = {}
+    wl = synth.sfx_bank(20, 4 * 1024, seed=5)
+    _, vo, _ = oracle.render_bank(oracle.BANK_SFX, wl, 4 * 1024, 48000.0, first_seed=3)
+    out["sfx"] = digest(vo)
+    wl = synth.sampler_bank(12, 5 * 1024, 44100.0, seed=11, mean_gap=0.03)
+    pcm = synth.pcm_loop(frames=3000, seed=3)
+    _, vo, _ = oracle.render_bank(oracle.BANK_SAMPLER, wl, 5 * 1024, 44100.0, pcm=pcm, pcm_meta=(1, 44100, L.FMT_SIGNED16_LSB))
+    out["sampler_q1e-5"] = digest(q(vo))
+    wl = synth.fm_bank(10, 5 * 1024, 48000.0, seed=21, mean_note=0.04)
+    d, i = synth.fm_mod_inputs(10, 5 * 1024)
+    _, vo, _ = oracle.render_bank(oracle.BANK_FM, wl, 5 * 1024, 48000.0, in0=d, in1=i)
+    out["fm_q1e-4"] = digest(np.round(vo.astype(np.float64) * 1e4).astype(np.int64))
+    return out
+
+
 def build():
-    return {"modules": module_cases(), "excerpts": excerpts(), "render_nice": render_case()}
+    return {"modules": module_cases(), "excerpts": excerpts(), "render_nice": render_case(), "banks": bank_cases()}
 
 
 if __name__ == "__main__":

@@ -133,3 +133,30 @@ def song_render(notes, total_frames, sample_rate=48000.0, want_mix=True):
     secs = orc.orc_song_render_events(ptr(counts), ptr(t), ptr(ids), ptr(fr), ptr(on), total_frames, sample_rate, ptr(pcm), ptr(mix))
     assert secs >= 0
     return pcm, mix, secs
+
+
+# ---- instrument banks of BASELINE.json configs[2..4] (oracle/bank_oracle.hpp) ---------------------------
+orc.orc_render_bank.argtypes = [_I, _U, _U, _U, _F, _P, _P, _P, _P, _P, _P, _U64, _U, _U, _I, _P, _P, _U, _P, _U, _P, _P, _U, _U]
+orc.orc_render_bank.restype = C.c_double
+BANK_SAMPLER, BANK_SFX, BANK_FM = 0, 1, 2
+
+
+def render_bank(kind, wl, total_frames, sample_rate, buffer_frames=1024, window=None, want_mix=False, pcm=None, pcm_meta=(1, 44100, 1),
+                in0=None, in1=None, first_seed=0, channels=2):
+    """Oracle render of a configs[2..4] bank.  Returns (mix or None, voices window, seconds)."""
+    off = np.ascontiguousarray(wl["event_off"], dtype=np.uint32)
+    ev = np.ascontiguousarray(wl["events"], dtype=L.note_event_dtype)
+    V = off.size - 1
+    first, n = window if window is not None else (0, total_frames)
+    vo = np.zeros((n, V), dtype=np.float32)
+    mix = np.zeros((total_frames, channels), dtype=np.float32) if want_mix else None
+    vf = np.ascontiguousarray(wl["fake_sample_rate"], dtype=np.float32) if "fake_sample_rate" in wl else None
+    vi = np.ascontiguousarray(wl["filter_type"], dtype=np.int32) if "filter_type" in wl else None
+    nodes = np.ascontiguousarray(wl["nodes"], dtype=L.curve_node_dtype) if "nodes" in wl else None
+    gains = np.ascontiguousarray(wl["gains"], dtype=np.float32)
+    for a in (in0, in1):
+        assert a is None or (a.dtype == np.float32 and a.shape == (total_frames, V) and a.flags.c_contiguous)
+    secs = orc.orc_render_bank(kind, V, total_frames, buffer_frames, sample_rate, ptr(off), ptr(ev), ptr(vf), ptr(vi), ptr(nodes), ptr(pcm),
+                               0 if pcm is None else pcm.size, pcm_meta[0], pcm_meta[1], pcm_meta[2], ptr(in0), ptr(in1), first_seed,
+                               ptr(gains), channels, ptr(mix), ptr(vo), first, n)
+    return mix, vo, secs

@@ -241,3 +241,33 @@ def test_impulse_queue_semantics():  # notes.zig:102-127
         for k in range(a.length):
             assert (a.impulses[k].frame, a.impulses[k].note_id, a.impulses[k].event_id, a.params[k]) == (
                 b.impulses[k].frame, b.impulses[k].note_id, b.impulses[k].event_id, b.params[k])
+
+
+def test_bank_spans_match_the_per_buffer_trigger_replay():
+    """zcu_bank_spans (one C call per block for a whole bank) against the per-voice, per-buffer zcu_trigger_run replay,
+    block by block with carried state, including same-frame events and more than 32 events in one buffer."""
+    from zang_b200 import synth
+    from zang_b200.events import BankTrigger
+    total, bf = 9 * 1024 + 77, 1024
+    wl = synth.fm_bank(23, total, 48000.0, seed=4, mean_note=0.002)   # ~10 events per buffer
+    ev, eo = wl["events"], wl["event_off"]
+    ev["frame"][eo[3] + 1] = ev["frame"][eo[3]]  # two impulses on one frame: the second wins (trigger_test.zig:117-132)
+    # voice 0: 40 events inside mix buffer 2 -> the ImpulseQueue keeps the first 32 (notes.zig:108-118)
+    first_in_b2 = int(eo[0] + np.searchsorted(ev["frame"][eo[0]:eo[1]], 2 * bf))
+    assert first_in_b2 + 40 < eo[1]
+    ev["frame"][first_in_b2:first_in_b2 + 40] = 2 * bf + 5 + 20 * np.arange(40)
+    later = slice(first_in_b2 + 40, int(eo[1]))
+    ev["frame"][later] = np.maximum(ev["frame"][later], 3 * bf + 1)
+    ev["frame"][later] = np.maximum.accumulate(ev["frame"][later])
+    assert np.diff(eo).max() > 100
+    bt = BankTrigger(eo, ev, total, bf)
+    for first, n in ((0, 4 * bf), (4 * bf, 2 * bf), (6 * bf, total - 6 * bf)):
+        off, spans = bt.spans(first, n)
+        off2, spans2 = synth.spans_from_events(eo, ev, total, bf, first_frame=first, num_frames=n)
+        for v in range(1, eo.size - 1):  # spans_from_events does not model the queue capacity: voice 0 is checked below
+            assert np.array_equal(spans[off[v]:off[v + 1]], spans2[off2[v]:off2[v + 1]]), v
+        if first == 0:
+            s0 = spans[off[0]:off[1]]
+            in_b2 = s0[(s0["start"] >= 2 * bf) & (s0["start"] < 3 * bf)]
+            assert in_b2["param"].max() == first_in_b2 + 31  # events 33..40 of that buffer were dropped
+            assert in_b2["end"].max() == 3 * bf

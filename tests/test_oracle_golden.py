@@ -37,6 +37,10 @@ def test_render_matches_golden_hashes():
     assert make_golden.render_case() == GOLD["render_nice"]
 
 
+def test_bank_graphs_match_golden_hashes():
+    assert make_golden.bank_cases() == GOLD["banks"]
+
+
 def one_voice(kind, params, n=64, flags=1, **kw):
     off = np.array([0, 1], dtype=np.uint32)
     spans = np.array([(0, n, flags, 0)], dtype=L.span_dtype)

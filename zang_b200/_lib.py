@@ -69,6 +69,7 @@ curve_node_dtype = np.dtype([("value", "<f4"), ("t", "<f4")])
 impulse_dtype = np.dtype([("frame", "<u4"), ("note_id", "<u4"), ("event_id", "<u4")])
 song_event_dtype = np.dtype([("t", "<f4"), ("note_id", "<u4"), ("param", "<u4")])
 note_event_dtype = np.dtype([("frame", "<u4"), ("note_id", "<u4"), ("freq", "<f4"), ("note_on", "<i4")])
+bank_trigger_dtype = np.dtype([("has_note", "<i4"), ("note_id", "<u4"), ("param", "<u4"), ("next_event", "<u4")])
 poly_slot_dtype = np.dtype([("used", "<i4"), ("note_id", "<u4"), ("event_id", "<u4"), ("note_on", "<i4")])
 
 
@@ -194,6 +195,8 @@ PROTOTYPES = {
     "zcu_poly_voice_init": (_I, [_P, _P, _U, _U]),
     "zcu_poly_voice_reset": (None, [_P]),
     "zcu_poly_voice_spans": (C.c_int64, [_P, _P, _F, _U, _U, _U, _P, _P, _U64]),
+    "zcu_bank_trigger_init": (None, [_P, _U, _P]),
+    "zcu_bank_spans": (C.c_int64, [_P, _U, _P, _P, _U, _U, _U, _U, _P, _P, _U64]),
     "zcu_render_create": (_I, [_P, _P, _P, _P, _P]),
     "zcu_render_free": (None, [_P]),
     "zcu_render_set_events": (_I, [_P, _P, _P, _P]),

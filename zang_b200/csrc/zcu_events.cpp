@@ -260,4 +260,52 @@ int64_t zcu_poly_voice_spans(zcu_poly_voice* pv, const int32_t* param_note_on, f
     return (int64_t)total;
 }
 
+// ---- a bank of monophonic voices (examples/example_polyphony.zig:61-92 per voice) -------------------------
+void zcu_bank_trigger_init(zcu_bank_trigger* state, uint32_t voices, const uint32_t* event_off) {
+    for (uint32_t v = 0; v < voices; v++) {
+        zcu_trigger_init(&state[v].trigger);
+        state[v].next_event = event_off ? event_off[v] : 0;
+    }
+}
+
+int64_t zcu_bank_spans(zcu_bank_trigger* state, uint32_t voices, const uint32_t* event_off, const zcu_note_event* events,
+                       uint32_t buffer_frames, uint32_t total_frames, uint32_t first_frame, uint32_t num_frames,
+                       uint32_t* voice_off_out, zcu_span* spans_out, uint64_t max_spans) {
+    if (!state || !event_off || !voice_off_out || buffer_frames == 0 || first_frame % buffer_frames != 0) return 0;
+    std::vector<zcu_bank_trigger> w(state, state + voices);  // commit only when the table fits
+    std::vector<zcu_span> all;
+    std::vector<uint32_t> off(voices + 1, 0);
+    zcu_impulse imps[32];
+    uint32_t params[32];
+    zcu_span tmp[40];
+    const uint32_t end_frame = first_frame + num_frames < total_frames ? first_frame + num_frames : total_frames;
+    for (uint32_t v = 0; v < voices; v++) {
+        off[v] = (uint32_t)all.size();
+        const uint32_t e0 = event_off[v], e1 = event_off[v + 1];
+        uint32_t ei = w[v].next_event;
+        for (uint32_t start = first_frame; start < end_frame; start += buffer_frames) {
+            const uint32_t len = (total_frames - start < buffer_frames) ? total_frames - start : buffer_frames;
+            // ImpulseQueue.push (notes.zig:102-127) of this buffer's events: capacity 32, later ones are dropped
+            uint32_t n = 0;
+            while (ei < e1 && events[ei].frame < start + len) {
+                if (n < 32) {
+                    imps[n] = zcu_impulse{events[ei].frame - start, events[ei].note_id, ei - e0 + 1};
+                    params[n] = ei;
+                    n++;
+                }
+                ei++;
+            }
+            const uint32_t k = zcu_trigger_run(&w[v].trigger, 0, len, imps, params, n, start - first_frame, tmp, 40);
+            all.insert(all.end(), tmp, tmp + (k < 40 ? k : 40));
+        }
+        w[v].next_event = ei;
+    }
+    off[voices] = (uint32_t)all.size();
+    if (all.size() > max_spans || (!all.empty() && !spans_out)) return -(int64_t)all.size();
+    std::memcpy(voice_off_out, off.data(), (size_t)(voices + 1) * sizeof(uint32_t));
+    if (!all.empty()) std::memcpy(spans_out, all.data(), all.size() * sizeof(zcu_span));
+    std::memcpy(state, w.data(), (size_t)voices * sizeof(zcu_bank_trigger));
+    return (int64_t)all.size();
+}
+
 }  // extern "C"

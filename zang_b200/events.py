@@ -118,3 +118,28 @@ class PolyphonyDispatcher:
         rc = lib.zcu_poly_dispatcher_dispatch(C.byref(self._pd), ptr(imp), ptr(rows), ptr(on), n, ptr(oi), ptr(op), ptr(oc))
         assert rc == L.OK
         return [(oi[s, :oc[s]].copy(), [params[r] for r in op[s, :oc[s]]]) for s in range(self.polyphony)]
+
+
+class BankTrigger:
+    """One ImpulseQueue + Trigger per voice of a bank (examples/example_polyphony.zig:61-92 per voice), replayed on the
+    host by libzangcu (zcu_bank_spans).  Events carry absolute frames; span.param is the global event index."""
+
+    def __init__(self, event_off, events, total_frames, buffer_frames=1024):
+        self.event_off = np.ascontiguousarray(event_off, dtype=np.uint32)
+        self.events = np.ascontiguousarray(events, dtype=L.note_event_dtype)
+        self.voices = self.event_off.size - 1
+        self.total_frames, self.buffer_frames = int(total_frames), int(buffer_frames)
+        self.state = np.zeros(self.voices, dtype=L.bank_trigger_dtype)
+        lib.zcu_bank_trigger_init(ptr(self.state), self.voices, ptr(self.event_off))
+
+    def spans(self, first_frame, num_frames):
+        """(voice_off[V+1], spans) of the block; Trigger state is carried to the next call."""
+        nbuf = (num_frames + self.buffer_frames - 1) // self.buffer_frames
+        cap = self.voices * nbuf + int(self.events.size) + 16
+        off = np.zeros(self.voices + 1, dtype=np.uint32)
+        spans = np.zeros(cap, dtype=L.span_dtype)
+        n = lib.zcu_bank_spans(ptr(self.state), self.voices, ptr(self.event_off), ptr(self.events), self.buffer_frames, self.total_frames,
+                               int(first_frame), int(num_frames), ptr(off), ptr(spans), cap)
+        if n < 0:
+            raise RuntimeError(f"span table needs {-n} rows, {cap} provided")
+        return off, spans[:n].copy()
