@@ -324,6 +324,10 @@ int zcu_poly_dispatcher_dispatch(zcu_poly_dispatcher* pd, const zcu_impulse* imp
  * up to n times with the reference's exact f32 rounding, in O(binades) instead of O(n).
  * Returns the number of adds performed (< n only when the ramp finished). */
 uint32_t zcu_ramp_advance(float* t, float t_step, uint32_t n, int32_t* finished);
+/* The same closed form for the un-clamped f32 accumulators: n times `t += step` (SineOsc.zig:49-62, Sampler.zig:130) and
+ * n times `t += step; t -= trunc(t)` (Cycle.zig:44-46).  These are what lets a paint call start in the middle of a span. */
+void zcu_accum_advance(float* t, float step, uint32_t n);
+void zcu_cycle_advance(float* t, float step, uint32_t n);
 
 /* Voice(T) of examples/example_song.zig:287-350 without the module paint: a NoteTracker feeding a
  * PolyphonyDispatcher feeding one Trigger per sub-voice. */

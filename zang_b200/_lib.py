@@ -195,6 +195,8 @@ PROTOTYPES = {
     "zcu_poly_voice_init": (_I, [_P, _P, _U, _U]),
     "zcu_poly_voice_reset": (None, [_P]),
     "zcu_poly_voice_spans": (C.c_int64, [_P, _P, _F, _U, _U, _U, _P, _P, _U64]),
+    "zcu_accum_advance": (None, [_P, _F, _U]),
+    "zcu_cycle_advance": (None, [_P, _F, _U]),
     "zcu_bank_trigger_init": (None, [_P, _U, _P]),
     "zcu_bank_spans": (C.c_int64, [_P, _U, _P, _P, _U, _U, _U, _U, _P, _P, _U64]),
     "zcu_render_create": (_I, [_P, _P, _P, _P, _P]),

@@ -95,7 +95,9 @@ int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a,
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
         attr_set = true;
     }
-    k_paint_lockstep<BasicMod<OP, ROWS>><<<warps, 32, smem, ctx->stream>>>(pa, T);
+    uint32_t nseg, seg_frames;
+    zcu_paint_segments(ctx, pa.V, pa.frames, T, true, &nseg, &seg_frames);
+    k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(warps, nseg), 32, smem, ctx->stream>>>(pa, T, seg_frames);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;

@@ -210,6 +210,9 @@ uint32_t zcu_ramp_advance(float* t, float t_step, uint32_t n, int32_t* finished)
     return done;
 }
 
+void zcu_accum_advance(float* t, float step, uint32_t n) { zcu::accum_advance(*t, step, n); }
+void zcu_cycle_advance(float* t, float step, uint32_t n) { zcu::cycle_advance(*t, step, n); }
+
 // ---- Voice(T) event logic (examples/example_song.zig:287-350) ------------------------------------------
 int zcu_poly_voice_init(zcu_poly_voice* pv, const zcu_song_event* song, uint32_t song_len, uint32_t polyphony) {
     if (!pv) return ZCU_ERR_INVALID;

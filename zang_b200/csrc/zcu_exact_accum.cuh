@@ -11,6 +11,7 @@
 // Host + device: the same code is unit-tested on the CPU against the plain loop (tests/test_exact_accum.py).
 #pragma once
 
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 
@@ -50,9 +51,12 @@ ZCU_HD float ea_add(float a, float b) {
 #endif
 }
 
-// Painter's ramp clock: applies `t += step; if (t >= 1) { t = 1; finished }` up to n times, stopping after
-// the add that finishes.  Returns the number of adds performed; *finished tells whether the last one hit 1.
-ZCU_HD uint32_t ramp_advance(float& t, float step, uint32_t n, bool& finished) {
+// Applies `t += step` up to n times with the reference's exact f32 rounding, in O(binades) instead of O(n).
+//   STOP   stop after the add that makes t >= 1 (*finished = true); CLAMP additionally sets t = 1 then
+//          (painter.zig:102-106).  Without STOP every one of the n adds is performed (SineOsc.zig:49-62, Sampler.zig:130).
+// Returns the number of adds performed.
+template <bool STOP, bool CLAMP>
+ZCU_HD uint32_t accum_core(float& t, float step, uint32_t n, bool& finished) {
     finished = false;
     uint32_t done = 0;
     const uint32_t sb = ea_bits(step);
@@ -64,7 +68,8 @@ ZCU_HD uint32_t ramp_advance(float& t, float step, uint32_t n, bool& finished) {
         const uint32_t et = (tb >> 23) & 0xFFu;
         uint32_t d = 0, k = 0;
         bool jump = false;
-        if (fast_ok && (tb >> 31) == 0 && et != 0 && et < 127u && es < et) {  // t normal and below 1
+        // t positive and normal (below 1 when the clock stops there), step's exponent below t's
+        if (fast_ok && (tb >> 31) == 0 && et != 0 && et < (STOP ? 127u : 0xFFu) && es < et) {
             const uint32_t shift = et - es;  // >= 1
             const uint32_t m = (tb & 0x7FFFFFu) | 0x800000u;
             bool settled = true;
@@ -97,14 +102,40 @@ ZCU_HD uint32_t ramp_advance(float& t, float step, uint32_t n, bool& finished) {
         if (!jump) {
             t = ea_add(t, step);
             done++;
-            if (t >= 1.0f) {
-                t = 1.0f;
+            if (STOP && t >= 1.0f) {
+                if (CLAMP) t = 1.0f;
                 finished = true;
                 return done;
             }
         }
     }
     return done;
+}
+
+// Painter's ramp clock: `t += step; if (t >= 1) { t = 1; finished }` up to n times, stopping after the add that finishes.
+ZCU_HD uint32_t ramp_advance(float& t, float step, uint32_t n, bool& finished) { return accum_core<true, true>(t, step, n, finished); }
+
+// n plain adds (SineOsc's and Sampler's phase between the wraps at the end of a paint call)
+ZCU_HD void accum_advance(float& t, float step, uint32_t n) {
+    bool f;
+    accum_core<false, false>(t, step, n, f);
+}
+
+// Cycle.zig:44-46: `t += step; t -= trunc(t)` n times.  Between wraps it is a plain accumulator below 1.
+ZCU_HD void cycle_advance(float& t, float step, uint32_t n) {
+    if (!(step > 0.0f) || !(step < 0.00390625f) || !(t >= 0.0f) || !(t < 1.0f)) {  // fast wraps (or odd values): the plain loop
+        for (uint32_t i = 0; i < n; i++) {
+            t = ea_add(t, step);
+            t = t - truncf(t);
+        }
+        return;
+    }
+    while (n > 0) {
+        bool wrapped;
+        const uint32_t k = accum_core<true, false>(t, step, n, wrapped);
+        n -= k;
+        if (wrapped) t = t - truncf(t);
+    }
 }
 
 }  // namespace zcu

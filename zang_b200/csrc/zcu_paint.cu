@@ -1,4 +1,7 @@
 // zcu_paint.cu — instantiation and launch of the lockstep paint kernel for every module variant.
+#include <algorithm>
+#include <cstdlib>
+
 #include "zcu_internal.h"
 #include "zcu_paint_kernel.cuh"
 
@@ -26,13 +29,30 @@ int launch(zcu_ctx* ctx, const PaintArgs& a) {
         attr_set = true;
     }
     const uint32_t grid = (a.V + 31) / 32;
-    k_paint_lockstep<M><<<grid, 32, smem, ctx->stream>>>(a, T);
+    uint32_t nseg, seg_frames;
+    zcu_paint_segments(ctx, a.V, a.frames, T, M::SKIP, &nseg, &seg_frames);
+    k_paint_lockstep<M><<<dim3(grid, nseg), 32, smem, ctx->stream>>>(a, T, seg_frames);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;
 }
 
 }  // namespace
+
+void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, uint32_t T, bool skippable, uint32_t* nseg_out, uint32_t* seg_frames_out) {
+    uint32_t nseg = 1, seg_frames = frames;
+    if (skippable && frames > 0) {
+        const uint32_t grid = (voices + 31) / 32;
+        nseg = std::max(1u, 16u * (uint32_t)ctx->sm_count / std::max(1u, grid));
+        if (const char* e = getenv("ZCU_PAINT_SEGMENTS")) nseg = (uint32_t)std::max(1, atoi(e));
+        seg_frames = (frames + nseg - 1) / nseg;
+        seg_frames = std::max(seg_frames, std::min(256u, frames));
+        seg_frames = (seg_frames + T - 1) / T * T;
+        nseg = (frames + seg_frames - 1) / seg_frames;
+    }
+    *nseg_out = nseg;
+    *seg_frames_out = seg_frames;
+}
 
 int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     PaintArgs a;

@@ -10,6 +10,12 @@
 // cp.async (LDGSTS), two stages deep: while tile i is consumed, tile i+1 of the output buffer and of
 // every input buffer is in flight.  Each thread only ever reads the shared-memory words it copied
 // itself, so no block-level barrier is needed, only cp.async.wait_group.
+//
+// Time parallelism: 32 voices are one warp, so a small bank would leave the chip empty.  For modules whose state has an
+// exact closed-form skip-ahead (M::SKIP: integer oscillator phases, the binade-stepped f32 accumulators of SineOsc /
+// Sampler / Cycle / Painter, the Envelope machine, stateless modules) the frame axis is additionally cut into segments
+// (blockIdx.y): a thread first walks its voice's spans up to its segment start with M::advance() instead of painting,
+// then paints its segment.  The result is bit-identical to the sequential walk; only the last segment stores the state.
 #pragma once
 
 #include <cuda_pipeline.h>
@@ -19,7 +25,7 @@
 namespace zcu {
 
 template <class M>
-__global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T) {
+__global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames) {
     extern __shared__ float smem[];
     const uint32_t tid = threadIdx.x, nt = blockDim.x;
     const uint32_t v = blockIdx.x * nt + tid;
@@ -38,9 +44,14 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T) 
     // smem layout [stage][buf][T][nt]
     auto sm = [&](uint32_t stage, int buf, uint32_t j) -> float* { return smem + ((size_t)(stage * nb + buf) * T + j) * nt + tid; };
 
+    // this CTA's segment of the frame axis (seg_frames is a multiple of T)
+    const uint32_t f_begin = M::SKIP ? blockIdx.y * seg_frames : 0u;
+    const uint32_t f_end = M::SKIP ? min(a.frames, f_begin + seg_frames) : a.frames;
+    if (f_begin >= f_end) return;
+
     auto issue = [&](uint32_t tile) {
         const uint32_t f0 = tile * T;
-        const uint32_t n = min(T, a.frames - f0);
+        const uint32_t n = min(T, f_end - f0);
         const uint32_t stage = tile & 1u;
         for (int b = 0; b < nb; b++) {
             const float* src = bufs[b] + (size_t)f0 * V + v;
@@ -59,10 +70,31 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T) 
         s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
     }
     bool active = false;
+    if (M::SKIP && f_begin > 0) {
+        // spans that end before the segment: state only
+        while (s_end <= f_begin) {
+            m.begin_span(a, s_param, s_flags, s_end - s_start);
+            m.advance(s_end - s_start);
+            m.end_span(a);
+            k++;
+            if (k < ke) {
+                const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+            } else {
+                s_start = s_end = 0xFFFFFFFFu;
+            }
+        }
+        if (s_start < f_begin) {  // the span that straddles the segment start
+            m.begin_span(a, s_param, s_flags, s_end - s_start);
+            m.advance(f_begin - s_start);
+            active = true;
+        }
+    }
 
-    const uint32_t ntiles = (a.frames + T - 1) / T;
-    if (ntiles > 0) issue(0);
-    for (uint32_t tile = 0; tile < ntiles; tile++) {
+    const uint32_t tile0 = f_begin / T;
+    const uint32_t ntiles = (f_end + T - 1) / T;
+    if (ntiles > tile0) issue(tile0);
+    for (uint32_t tile = tile0; tile < ntiles; tile++) {
         if (tile + 1 < ntiles) {
             issue(tile + 1);
             __pipeline_wait_prior(1);
@@ -70,7 +102,7 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T) 
             __pipeline_wait_prior(0);
         }
         const uint32_t f0 = tile * T;
-        const uint32_t n = min(T, a.frames - f0);
+        const uint32_t n = min(T, f_end - f0);
         const uint32_t stage = tile & 1u;
         if (!active && s_start >= f0 + n) continue;  // nothing of this voice in the tile
         float* optr = a.out + (size_t)f0 * V + v;
@@ -102,6 +134,7 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T) 
             }
         }
     }
+    if (f_end < a.frames) return;  // not the last segment: its state is somebody else's start
     if (active) m.end_span(a);
     m.store(a, v);
 }

@@ -76,31 +76,6 @@ __device__ __forceinline__ zcu_envelope_params nice_env_params(float sample_rate
     return ep;
 }
 
-// Envelope state after n more samples of the span that e.begin() has just entered: the per-sample loop of
-// EnvelopeCore::sample() with the ramp clock advanced in closed form.  last_value is a pure function of
-// (t, start, goal), so evaluating it once at the final t gives the bits the per-sample loop would leave.
-__device__ inline void env_advance(EnvelopeCore& e, uint32_t n) {
-    while (n > 0) {
-        if (e.mode != EnvelopeCore::M_RAMP_ON && e.mode != EnvelopeCore::M_RAMP_OFF) return;  // flat / idle: time invariant
-        PainterDev& p = e.painter;
-        bool finished = false;
-        float t = p.t;
-        const uint32_t k = ramp_advance(t, p.t_step, n, finished);
-        p.t = t;
-        const float it = 1.0f - t;
-        float tp;
-        if (p.kind == ZCU_CURVE_LINEAR)
-            tp = t;
-        else if (p.kind == ZCU_CURVE_SQUARED)
-            tp = 1.0f - it * it;
-        else
-            tp = 1.0f - it * it * it;
-        p.last_value = p.start + tp * p.gms;
-        n -= k;
-        if (finished) e.on_ramp_finished();
-    }
-}
-
 __device__ __forceinline__ uint32_t pulse_ifreq(float sample_rate, float freq) {  // PulseOsc.zig:82-89
     if (freq < 0.0f || freq > sample_rate / 8.0f) return 0u;
     const float basefrq = 4294967296.0f / sample_rate;
