@@ -58,6 +58,7 @@ def main():
     ap.add_argument("--voices", default="4096,65536")
     ap.add_argument("--buffers", type=int, default=8)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--only", default="", help="substring filter on the module name")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "module_bw.json"))
     args = ap.parse_args()
     peaks = {}
@@ -84,6 +85,8 @@ def main():
         del host
         smp = None
         for name, kind, bps, prow, inputs in module_cases():
+            if args.only and args.only not in name:
+                continue
             mod = E.MODULE_CLASSES[kind](ctx, V)
             kw = {k: ins[k] for k in inputs}
             ms_best = 1e30
@@ -101,7 +104,7 @@ def main():
             print(f"V={V:6d} {name:26s} {ms_best:9.3f} ms  {vs:10.3e} vs/s  {gbs:8.1f} GB/s  {gbs / peak:6.3f} of {peak:.0f}", flush=True)
         # whole-buffer basics (spans == NULL)
         a, b = ins["input"], ins["cutoff"]
-        for name, bps, fn in [("zero", 4, lambda: ctx.zero(None, out)), ("copy", 8, lambda: ctx.copy(None, out, a)),
+        for name, bps, fn in [] if args.only else [("zero", 4, lambda: ctx.zero(None, out)), ("copy", 8, lambda: ctx.copy(None, out, a)),
                               ("addInto", 12, lambda: ctx.addInto(None, out, a)), ("multiply", 16, lambda: ctx.multiply(None, out, a, b)),
                               ("multiplyWithScalar", 8, lambda: ctx.multiplyWithScalar(None, out, 0.5))]:
             ms_best = 1e30

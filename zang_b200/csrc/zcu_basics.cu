@@ -87,16 +87,15 @@ int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a,
     pa.in1 = OpTraits<OP>::reads_b ? b : nullptr;
     if (pa.V == 0 || pa.frames == 0) return ZCU_OK;
     const uint32_t warps = (pa.V + 31) / 32;
-    const uint32_t T = warps <= 4 * 148 ? 64u : 32u;
     int nb = 1 + (pa.in0 ? 1 : 0) + (pa.in1 ? 1 : 0);
+    uint32_t T, nseg, seg_frames;
+    zcu_paint_segments(ctx, pa.V, pa.frames, nb, true, &T, &nseg, &seg_frames);
     const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
         attr_set = true;
     }
-    uint32_t nseg, seg_frames;
-    zcu_paint_segments(ctx, pa.V, pa.frames, T, true, &nseg, &seg_frames);
     k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(warps, nseg), 32, smem, ctx->stream>>>(pa, T, seg_frames);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());

@@ -72,9 +72,11 @@ int zcu_fail(zcu_ctx* ctx, int code, const char* fmt, ...);
         if (!(cond)) return zcu_fail((ctx), ZCU_ERR_INVALID, "%s: %s", __func__, (msg));    \
     } while (0)
 
-// Segments of the frame axis for the lockstep paint kernel (modules with an exact skip-ahead only): enough CTAs for ~16
-// warps per SM, each segment at least 256 frames and a multiple of the tile T.  ZCU_PAINT_SEGMENTS overrides (tests).
-void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, uint32_t T, bool skippable, uint32_t* nseg, uint32_t* seg_frames);
+// Tile depth T and segments of the frame axis for the lockstep paint kernel.  Modules with an exact skip-ahead are cut into
+// as many segments as fill the chip's resident one-warp CTAs exactly once (each at least 256 frames, a multiple of T);
+// the others get one segment.  nbufs = staged buffers (output + inputs).  ZCU_PAINT_SEGMENTS overrides (tests).
+void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, int nbufs, bool skippable, uint32_t* T, uint32_t* nseg,
+                        uint32_t* seg_frames);
 
 // copies `bytes` of host memory into arena slot `slot` (stream ordered) and returns the device ptr
 int zcu_arena_upload(zcu_ctx* ctx, int slot, const void* host, size_t bytes, void** dev_out);

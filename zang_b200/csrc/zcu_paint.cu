@@ -9,19 +9,14 @@ using namespace zcu;
 
 namespace {
 
-uint32_t pick_tile(uint32_t V) {
-    // few voices -> few warps on the chip -> deeper prefetch per warp; many voices -> more warps per SM
-    const uint32_t warps = (V + 31) / 32;
-    return warps <= 4 * 148 ? 64u : 32u;
-}
-
 template <class M>
 int launch(zcu_ctx* ctx, const PaintArgs& a) {
-    const uint32_t T = pick_tile(a.V);
     int nb = 1;
     if (M::NIN >= 1 && a.in0) nb++;
     if (M::NIN >= 2 && a.in1) nb++;
     if (M::NIN >= 3 && a.in2) nb++;
+    uint32_t T, nseg, seg_frames;
+    zcu_paint_segments(ctx, a.V, a.frames, nb, M::SKIP, &T, &nseg, &seg_frames);
     const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
@@ -29,8 +24,6 @@ int launch(zcu_ctx* ctx, const PaintArgs& a) {
         attr_set = true;
     }
     const uint32_t grid = (a.V + 31) / 32;
-    uint32_t nseg, seg_frames;
-    zcu_paint_segments(ctx, a.V, a.frames, T, M::SKIP, &nseg, &seg_frames);
     k_paint_lockstep<M><<<dim3(grid, nseg), 32, smem, ctx->stream>>>(a, T, seg_frames);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
@@ -39,17 +32,26 @@ int launch(zcu_ctx* ctx, const PaintArgs& a) {
 
 }  // namespace
 
-void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, uint32_t T, bool skippable, uint32_t* nseg_out, uint32_t* seg_frames_out) {
+void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, int nbufs, bool skippable, uint32_t* T_out, uint32_t* nseg_out,
+                        uint32_t* seg_frames_out) {
+    const uint32_t grid = std::max(1u, (voices + 31) / 32);
+    const uint32_t sms = (uint32_t)ctx->sm_count;
+    // tile: deep prefetch when there are few warps on the chip, shallow when there are many
+    uint32_t T = (!skippable && grid <= 4 * sms) ? 64u : 32u;
     uint32_t nseg = 1, seg_frames = frames;
     if (skippable && frames > 0) {
-        const uint32_t grid = (voices + 31) / 32;
-        nseg = std::max(1u, 16u * (uint32_t)ctx->sm_count / std::max(1u, grid));
-        if (const char* e = getenv("ZCU_PAINT_SEGMENTS")) nseg = (uint32_t)std::max(1, atoi(e));
+        // resident one-warp CTAs per SM: the hardware limit of 32, or what the staging tiles leave of ~220 KB of shared memory
+        const uint32_t per_cta = 2u * (uint32_t)nbufs * T * 32u * 4u + 1024u;
+        const uint32_t resident = std::min(32u, (220u * 1024u) / per_cta) * sms;
+        // one full wave: a second, partly filled wave would cost as much as the first
+        nseg = std::max(1u, std::min(resident, 24u * sms) / grid);
+        if (const char* e = getenv("ZCU_PAINT_SEGMENTS")) nseg = (uint32_t)std::max(1, atoi(e));  // tuning / tests
         seg_frames = (frames + nseg - 1) / nseg;
         seg_frames = std::max(seg_frames, std::min(256u, frames));
         seg_frames = (seg_frames + T - 1) / T * T;
         nseg = (frames + seg_frames - 1) / seg_frames;
     }
+    *T_out = T;
     *nseg_out = nseg;
     *seg_frames_out = seg_frames;
 }

@@ -29,7 +29,8 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
     extern __shared__ float smem[];
     const uint32_t tid = threadIdx.x, nt = blockDim.x;
     const uint32_t v = blockIdx.x * nt + tid;
-    if (v >= a.V) return;  // whole-lane exit is safe: no block or warp level synchronisation below
+    const uint32_t lanes = __ballot_sync(0xffffffffu, v < a.V);  // the lanes that take part in the per-run warp reductions
+    if (v >= a.V) return;
 
     const float* bufs[4];
     int nb = 0;
@@ -104,10 +105,11 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
         const uint32_t f0 = tile * T;
         const uint32_t n = min(T, f_end - f0);
         const uint32_t stage = tile & 1u;
-        if (!active && s_start >= f0 + n) continue;  // nothing of this voice in the tile
         float* optr = a.out + (size_t)f0 * V + v;
-#pragma unroll 1
-        for (uint32_t j = 0; j < n; j++) {
+        // Frames are walked in runs: up to the nearest span boundary of any of the warp's voices (one warp reduction per
+        // run), so that the per-frame code carries no span bookkeeping and can be unrolled.
+        uint32_t j = 0;
+        while (j < n) {
             const uint32_t f = f0 + j;
             if (active && f == s_end) {
                 m.end_span(a);
@@ -124,14 +126,25 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
                 m.begin_span(a, s_param, s_flags, s_end - s_start);
                 active = true;
             }
+            const uint32_t next_boundary = active ? s_end : s_start;
+            const uint32_t run = min(n - j, __reduce_min_sync(lanes, next_boundary - f));
             if (active) {
-                float acc = *sm(stage, i_out, j);
-                const float x0 = i_in0 >= 0 ? *sm(stage, i_in0, j) : 0.0f;
-                const float x1 = i_in1 >= 0 ? *sm(stage, i_in1, j) : 0.0f;
-                const float x2 = i_in2 >= 0 ? *sm(stage, i_in2, j) : 0.0f;
-                m.sample(acc, x0, x1, x2);
-                optr[(size_t)j * V] = acc;
+                const float* so = sm(stage, i_out, j);
+                const float* s0 = i_in0 >= 0 ? sm(stage, i_in0, j) : so;
+                const float* s1 = i_in1 >= 0 ? sm(stage, i_in1, j) : so;
+                const float* s2 = i_in2 >= 0 ? sm(stage, i_in2, j) : so;
+                float* op = optr + (size_t)j * V;
+#pragma unroll 4
+                for (uint32_t r = 0; r < run; r++) {
+                    float acc = so[r * 32];
+                    const float x0 = i_in0 >= 0 ? s0[r * 32] : 0.0f;
+                    const float x1 = i_in1 >= 0 ? s1[r * 32] : 0.0f;
+                    const float x2 = i_in2 >= 0 ? s2[r * 32] : 0.0f;
+                    m.sample(acc, x0, x1, x2);
+                    op[(size_t)r * V] = acc;
+                }
             }
+            j += run;
         }
     }
     if (f_end < a.frames) return;  // not the last segment: its state is somebody else's start
