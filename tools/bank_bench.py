@@ -1,0 +1,117 @@
+"""Throughput of the instrument banks of BASELINE.json configs[1..4] through the DROP-IN module path (every line of the
+reference-style paint body = one C-ABI call over all voices), at the configs' voice counts, one block of mix buffers.
+
+Reported per config: device time of the module chain for the block (CUDA events on the context stream, span tables already
+uploaded), voice-samples/s, and the algorithmic HBM GB/s (SURVEY.md §8d bytes per voice-sample of the un-fused chain);
+plus the host time to build and upload the block's span tables (Trigger replay in libzangcu).
+
+  python tools/bank_bench.py [--out gpurun_out/bank_bench.json]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from zang_b200 import _lib as L  # noqa: E402
+from zang_b200 import banks, synth  # noqa: E402
+from zang_b200 import engine as E  # noqa: E402
+
+
+def run(ctx, name, bank, frames, ntemps, bytes_per_vs, peak, ins=(), reps=3):
+    V = bank.voices
+    out = ctx.buf(frames, V)
+    temps = [ctx.buf(frames, V) for _ in range(ntemps)]
+    t_host = time.perf_counter()
+    prepared = bank.prepare_block(0, frames)
+    ctx.sync()
+    t_host = time.perf_counter() - t_host
+    best = 1e30
+    launches0 = ctx.launch_count
+    for rep in range(reps + 1):
+        ctx.zero(None, out)
+        ctx.timer_start()
+        bank.paint_block(0, frames, out, temps, *ins, prepared=prepared)
+        ms = ctx.timer_stop_ms()
+        if rep > 0:
+            best = min(best, ms)
+    launches = (ctx.launch_count - launches0) // (reps + 1)
+    vs = V * frames / (best * 1e-3)
+    gbs = vs * bytes_per_vs / 1e9
+    res = dict(config=name, voices=V, frames=frames, ms=best, voice_samples_per_s=vs, algorithmic_bytes_per_voice_sample=bytes_per_vs,
+               gbs=gbs, frac_of_peak=gbs / peak, host_span_tables_ms=t_host * 1e3, launches_per_block=launches)
+    print(f"{name:34s} V={V:6d} frames={frames:6d} {best:9.3f} ms  {vs:10.3e} vs/s  {gbs:8.1f} GB/s  {gbs / peak:5.3f} of peak   "
+          f"(host span tables {t_host * 1e3:7.1f} ms, {launches} launches)", flush=True)
+    for b in [out] + temps + list(prepared):
+        b.free()
+    return res
+
+
+class NiceBankAdapter:
+    """configs[1] through the un-fused NiceInstrumentBank (engine.py), for comparison with the fused render."""
+
+    def __init__(self, ctx, wl, sr, total):
+        from zang_b200.events import BankTrigger
+        self.ctx, self.voices = ctx, wl["color"].size
+        self.bank = E.NiceInstrumentBank(ctx, self.voices, 0.3)
+        self.trigger = BankTrigger(wl["event_off"], wl["events"], total, 1024)
+        ev = wl["events"]
+        self.rows = np.zeros(ev.size, dtype=E.NiceInstrumentBank.Params)
+        self.rows["sample_rate"], self.rows["freq"], self.rows["note_on"] = sr, ev["freq"], ev["note_on"]
+
+    def prepare_block(self, first, n):
+        off, spans = self.trigger.spans(first, n)
+        return (self.ctx.spans(self.voices, n, off, spans),)
+
+    def paint_block(self, first, n, out, temps, prepared=None):
+        self.bank.paint(prepared[0], [out], temps, self.rows)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "bank_bench.json"))
+    ap.add_argument("--scale", type=float, default=1.0, help="scale the voice counts (smoke runs)")
+    args = ap.parse_args()
+    peak = 6553.0
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+    except Exception:
+        pass
+    ctx = E.Context(0)
+    res = []
+    sc = args.scale
+    # configs[1] polyphony bank, un-fused: 4096 voices, 64 mix buffers
+    V, frames = int(4096 * sc), 64 * 1024
+    wl = synth.polyphony_bank(V, frames, 48000.0)
+    res.append(run(ctx, "configs[1] NiceInstrument (un-fused)", NiceBankAdapter(ctx, wl, 48000.0, frames), frames, 2, 64, peak))
+    # configs[2] fm/detuned: 16384 voices, 16 mix buffers
+    V, frames = int(16384 * sc), 16 * 1024
+    wl = synth.fm_bank(V, frames, 48000.0)
+    det, idx = synth.fm_mod_inputs(V, frames)
+    ins = (ctx.buf(frames, V, det), ctx.buf(frames, V, idx))
+    del det, idx
+    res.append(run(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 6, 140, peak, ins=ins))
+    for b in ins:
+        b.free()
+    # configs[3] sampler: 2048 voices, 64 mix buffers @44.1 kHz
+    V, frames = int(2048 * sc), 64 * 1024
+    wl = synth.sampler_bank(V, frames, 44100.0)
+    pcm = synth.pcm_loop()
+    smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
+    res.append(run(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 2, 48, peak))
+    # configs[4] SFX batch: 65536 jobs x 24 mix buffers
+    V, frames = int(65536 * sc), 24 * 1024
+    wl = synth.sfx_bank(V, frames)
+    res.append(run(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 3, 100, peak))
+    os.makedirs(os.path.dirname(args.out), exist_ok=True)
+    json.dump(dict(peak_gbs=peak, results=res), open(args.out, "w"), indent=1)
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

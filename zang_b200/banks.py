@@ -60,21 +60,27 @@ class SamplerVoiceBank:
         self.dist_rows = np.zeros(1, dtype=L.param_dtypes[L.MOD_DISTORTION])
         self.dist_rows[0] = (L.DIST_OVERDRIVE, 0.9, 0.5, 0.0)
 
-    def paint_block(self, first_frame, num_frames, out, temps):
+    def prepare_block(self, first_frame, num_frames):
+        """Host side of a block: Trigger replay and upload of the span tables (the reference's per-buffer event logic)."""
         ctx, V = self.ctx, self.voices
-        t0, t1 = temps
         off, spans = self.trigger.spans(first_frame, num_frames)
-        sp_trig = ctx.spans(V, num_frames, off, spans)
-        sp_voice = ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.arange(V)))
-        sp_row0 = ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.zeros(V)))
+        return (ctx.spans(V, num_frames, off, spans),
+                ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.arange(V))),
+                ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.zeros(V))))
+
+    def paint_block(self, first_frame, num_frames, out, temps, prepared=None):
+        ctx = self.ctx
+        t0, t1 = temps
+        sp_trig, sp_voice, sp_row0 = prepared or self.prepare_block(first_frame, num_frames)
         ctx.zero(None, t0)
         self.sampler.paint(sp_trig, [t0], [], self.sampler_rows, self.sample)
         ctx.multiplyWithScalar(None, t0, 2.5)
         ctx.zero(None, t1)
         self.decimator.paint(sp_voice, [t1], [], self.dec_rows, input=t0)
         self.distortion.paint(sp_row0, [out], [], self.dist_rows, input=t1)
-        for s in (sp_trig, sp_voice, sp_row0):
-            s.free()
+        if prepared is None:
+            for s in (sp_trig, sp_voice, sp_row0):
+                s.free()
 
 
 class SfxBank:
@@ -118,11 +124,14 @@ class SfxBank:
         self.env_rows["sustain_volume"] = 0.6
         self.env_rows["note_on"][:ev.size] = ev["note_on"]
 
-    def paint_block(self, first_frame, num_frames, out, temps):
-        ctx, V = self.ctx, self.voices
-        t0, t1, t2 = temps
+    def prepare_block(self, first_frame, num_frames):
         off, spans = self.trigger.spans(first_frame, num_frames)
-        sp = ctx.spans(V, num_frames, off, spans)
+        return (self.ctx.spans(self.voices, num_frames, off, spans),)
+
+    def paint_block(self, first_frame, num_frames, out, temps, prepared=None):
+        ctx = self.ctx
+        t0, t1, t2 = temps
+        (sp,) = prepared or self.prepare_block(first_frame, num_frames)
         ctx.zero(sp, t0)
         self.noise.paint(sp, [t0], [], self.noise_rows)
         ctx.zero(sp, t1)
@@ -132,7 +141,8 @@ class SfxBank:
         ctx.zero(sp, t0)
         self.env.paint(sp, [t0], [], self.env_rows)
         ctx.multiply(sp, out, t2, t0)
-        sp.free()
+        if prepared is None:
+            sp.free()
 
 
 class FmDetunedBank:
@@ -205,11 +215,14 @@ class FmDetunedBank:
         sp_plain["param"] = 0
         return off, spans, sp_porta, sp_env, sp_plain
 
-    def paint_block(self, first_frame, num_frames, out, temps, detune_in, index_in):
-        ctx, V = self.ctx, self.voices
-        t0, t1, t2, t3, t4, t5 = temps
+    def prepare_block(self, first_frame, num_frames):
         off, _, a_porta, a_env, a_plain = self.span_tables(first_frame, num_frames)
-        sp_porta, sp_env, sp = (ctx.spans(V, num_frames, off, a) for a in (a_porta, a_env, a_plain))
+        return tuple(self.ctx.spans(self.voices, num_frames, off, a) for a in (a_porta, a_env, a_plain))
+
+    def paint_block(self, first_frame, num_frames, out, temps, detune_in, index_in, prepared=None):
+        ctx = self.ctx
+        t0, t1, t2, t3, t4, t5 = temps
+        sp_porta, sp_env, sp = prepared or self.prepare_block(first_frame, num_frames)
         ctx.zero(sp, t0)
         self.porta.paint(sp_porta, [t0], [], self.porta_rows)
         ctx.zero(sp, t1)
@@ -225,5 +238,6 @@ class FmDetunedBank:
         self.env.paint(sp_env, [t5], [], self.env_rows)
         ctx.multiply(sp, out, t2, t5)
         ctx.multiply(sp, out, t4, t5)
-        for s in (sp_porta, sp_env, sp):
-            s.free()
+        if prepared is None:
+            for s in (sp_porta, sp_env, sp):
+                s.free()
