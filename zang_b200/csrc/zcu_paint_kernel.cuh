@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
         // spans that end before the segment: state only
         while (s_end <= f_begin) {
             m.begin_span(a, s_param, s_flags, s_end - s_start);
-            m.advance(s_end - s_start);
+            m.advance(a, v, s_start, s_end - s_start);
             m.end_span(a);
             k++;
             if (k < ke) {
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
         }
         if (s_start < f_begin) {  // the span that straddles the segment start
             m.begin_span(a, s_param, s_flags, s_end - s_start);
-            m.advance(f_begin - s_start);
+            m.advance(a, v, s_start, f_begin - s_start);
             active = true;
         }
     }
