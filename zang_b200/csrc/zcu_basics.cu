@@ -86,17 +86,14 @@ int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a,
     pa.in0 = OpTraits<OP>::reads_a ? a : nullptr;
     pa.in1 = OpTraits<OP>::reads_b ? b : nullptr;
     if (pa.V == 0 || pa.frames == 0) return ZCU_OK;
-    const uint32_t warps = (pa.V + 31) / 32;
     int nb = 1 + (pa.in0 ? 1 : 0) + (pa.in1 ? 1 : 0);
-    uint32_t T, nseg, seg_frames;
-    zcu_paint_segments(ctx, pa.V, pa.frames, nb, true, &T, &nseg, &seg_frames);
-    const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
+    const PaintPlan p = zcu_paint_plan(ctx, pa, nb, true);
     static bool attr_set = false;
     if (!attr_set) {
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
         attr_set = true;
     }
-    k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(warps, nseg), 32, smem, ctx->stream>>>(pa, T, seg_frames);
+    k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(pa, p.T, p.seg_frames, p.vec4);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;

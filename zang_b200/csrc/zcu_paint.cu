@@ -15,16 +15,13 @@ int launch(zcu_ctx* ctx, const PaintArgs& a) {
     if (M::NIN >= 1 && a.in0) nb++;
     if (M::NIN >= 2 && a.in1) nb++;
     if (M::NIN >= 3 && a.in2) nb++;
-    uint32_t T, nseg, seg_frames;
-    zcu_paint_segments(ctx, a.V, a.frames, nb, M::SKIP, &T, &nseg, &seg_frames);
-    const size_t smem = (size_t)2 * nb * T * 32 * sizeof(float);
+    const PaintPlan p = zcu_paint_plan(ctx, a, nb, M::SKIP);
     static bool attr_set = false;
     if (!attr_set) {
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * 64 * 32 * 4));
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
         attr_set = true;
     }
-    const uint32_t grid = (a.V + 31) / 32;
-    k_paint_lockstep<M><<<dim3(grid, nseg), 32, smem, ctx->stream>>>(a, T, seg_frames);
+    k_paint_lockstep<M><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;
@@ -34,17 +31,19 @@ int launch(zcu_ctx* ctx, const PaintArgs& a) {
 
 void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, int nbufs, bool skippable, uint32_t* T_out, uint32_t* nseg_out,
                         uint32_t* seg_frames_out) {
-    const uint32_t grid = std::max(1u, (voices + 31) / 32);
+    const uint32_t rv = 32u * kPaintWarps;
+    const uint32_t grid = std::max(1u, (voices + rv - 1) / rv);
     const uint32_t sms = (uint32_t)ctx->sm_count;
-    // tile: deep prefetch when there are few warps on the chip, shallow when there are many
-    uint32_t T = (!skippable && grid <= 4 * sms) ? 64u : 32u;
+    // tile depth: ~24 KB of staging per CTA for one or two buffers, 24-32 KB for three or four
+    uint32_t T = nbufs <= 1 ? 16u : 8u;
+    if (const char* e = getenv("ZCU_PAINT_T")) T = (uint32_t)std::min(16, std::max(1, atoi(e)));  // tuning
     uint32_t nseg = 1, seg_frames = frames;
     if (skippable && frames > 0) {
-        // resident one-warp CTAs per SM: the hardware limit of 32, or what the staging tiles leave of ~220 KB of shared memory
-        const uint32_t per_cta = 2u * (uint32_t)nbufs * T * 32u * 4u + 1024u;
-        const uint32_t resident = std::min(32u, (220u * 1024u) / per_cta) * sms;
+        // resident CTAs per SM: 8 by registers (128 threads x <= 64 registers), or what the staging ring leaves of ~220 KB
+        const uint32_t per_cta = (uint32_t)kPaintStages * (uint32_t)nbufs * T * rv * 4u + 1024u;
+        const uint32_t resident = std::min(8u, (220u * 1024u) / per_cta) * sms;
         // one full wave: a second, partly filled wave would cost as much as the first
-        nseg = std::max(1u, std::min(resident, 24u * sms) / grid);
+        nseg = std::max(1u, resident / grid);
         if (const char* e = getenv("ZCU_PAINT_SEGMENTS")) nseg = (uint32_t)std::max(1, atoi(e));  // tuning / tests
         seg_frames = (frames + nseg - 1) / nseg;
         seg_frames = std::max(seg_frames, std::min(256u, frames));

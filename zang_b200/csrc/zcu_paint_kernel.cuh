@@ -1,15 +1,18 @@
 // zcu_paint_kernel.cuh — the generic "lockstep" paint kernel.
 //
 // One thread per voice, 32 adjacent voices per warp, every warp walks the frame axis of the
-// [frame][voice] buffers in lockstep, so each access is one coalesced 128-byte row.  A voice's
-// spans (= the reference's paint() calls) are entered and left at the voice's own frames; module
-// state lives in registers for the whole block of buffers (Filter l/b, oscillator phase, PRNG ...).
+// [frame][voice] buffers in lockstep.  A voice's spans (= the reference's paint() calls) are entered and
+// left at the voice's own frames; module state lives in registers for the whole block of buffers
+// (Filter l/b, oscillator phase, PRNG ...).
 //
-// Memory pipeline: the strictly sequential recurrences give each warp only one sample of work at a
-// time, so HBM latency is hidden by staging tiles of T frames x 32 voices through shared memory with
-// cp.async (LDGSTS), two stages deep: while tile i is consumed, tile i+1 of the output buffer and of
-// every input buffer is in flight.  Each thread only ever reads the shared-memory words it copied
-// itself, so no block-level barrier is needed, only cp.async.wait_group.
+// Memory pipeline (r01c; measured with tools/ubench_rowtile.cu: 6.1-6.4 TB/s against 3.9-4.5 TB/s for one-warp CTAs
+// issuing 4-byte copies): a CTA is ZCU_PAINT_WARPS warps over 32*W adjacent voices, so that a frame row of the CTA is
+// W*128 contiguous bytes.  Tiles of T frames of the output buffer and of every input buffer are staged through shared
+// memory with 16-byte cp.async (LDGSTS.128: one warp instruction moves a whole 512-byte row), three stages deep.  The
+// module reads its operands from the tile and writes its result back INTO the tile; the finished output tile is then
+// written to HBM by the whole CTA as 16-byte row stores.  HBM therefore only ever sees full-row requests in both
+// directions.  Frames outside every span are written back unchanged; a tile in which no voice of the CTA painted is
+// not written at all.
 //
 // Time parallelism: 32 voices are one warp, so a small bank would leave the chip empty.  For modules whose state has an
 // exact closed-form skip-ahead (M::SKIP: integer oscillator phases, the binade-stepped f32 accumulators of SineOsc /
@@ -24,13 +27,17 @@
 
 namespace zcu {
 
+constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
+constexpr int kPaintStages = 3;   // tiles in the cp.async ring
+
 template <class M>
-__global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames) {
-    extern __shared__ float smem[];
-    const uint32_t tid = threadIdx.x, nt = blockDim.x;
-    const uint32_t v = blockIdx.x * nt + tid;
-    const uint32_t lanes = __ballot_sync(0xffffffffu, v < a.V);  // the lanes that take part in the per-run warp reductions
-    if (v >= a.V) return;
+__global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames, uint32_t vec4) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr uint32_t W = kPaintWarps, S = kPaintStages, RV = 32 * W;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t v0 = blockIdx.x * RV;
+    const uint32_t v = v0 + tid;
+    const bool valid = v < a.V;
 
     const float* bufs[4];
     int nb = 0;
@@ -42,34 +49,58 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
     if (M::NIN >= 3 && a.in2) { i_in2 = nb; bufs[nb++] = a.in2; }
 
     const size_t V = a.V;
-    // smem layout [stage][buf][T][nt]
-    auto sm = [&](uint32_t stage, int buf, uint32_t j) -> float* { return smem + ((size_t)(stage * nb + buf) * T + j) * nt + tid; };
+    // smem layout [stage][buf][T][RV]
+    auto tile_ptr = [&](uint32_t stage, int buf) -> float* { return smem + (size_t)(stage * nb + buf) * T * RV; };
 
     // this CTA's segment of the frame axis (seg_frames is a multiple of T)
     const uint32_t f_begin = M::SKIP ? blockIdx.y * seg_frames : 0u;
     const uint32_t f_end = M::SKIP ? min(a.frames, f_begin + seg_frames) : a.frames;
-    if (f_begin >= f_end) return;
+    if (f_begin >= f_end) return;  // uniform over the CTA
+
+    // cooperative row copies: a row is RV floats; thread t moves chunk c of rows r0, r0 + RPP, ...
+    const uint32_t cw = vec4 ? 4u : 1u;          // floats per chunk (16-byte chunks need V % 4 == 0)
+    const uint32_t cpr = RV / cw;                // chunks per row
+    const uint32_t rpp = RV / cpr;               // rows per pass over the CTA's threads (4 or 1)
+    const uint32_t c = (tid % cpr) * cw, r0 = tid / cpr;
+    const bool c_valid = v0 + c < a.V;
 
     auto issue = [&](uint32_t tile) {
         const uint32_t f0 = tile * T;
         const uint32_t n = min(T, f_end - f0);
-        const uint32_t stage = tile & 1u;
-        for (int b = 0; b < nb; b++) {
-            const float* src = bufs[b] + (size_t)f0 * V + v;
-            for (uint32_t j = 0; j < n; j++) __pipeline_memcpy_async(sm(stage, b, j), src + (size_t)j * V, 4);
+        const uint32_t stage = tile % S;
+        if (c_valid) {
+            for (int b = 0; b < nb; b++) {
+                const float* src = bufs[b] + (size_t)f0 * V + v0 + c;
+                float* dst = tile_ptr(stage, b) + c;
+                if (vec4) {
+                    for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 16);
+                } else {
+                    for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 4);
+                }
+            }
         }
         __pipeline_commit();
     };
 
     M m;
-    m.load(a, v);
-    uint32_t k = a.off[v];
-    const uint32_t ke = a.off[v + 1];
+    uint32_t k = 0, ke = 0;
+    if (valid) {
+        m.load(a, v);
+        k = a.off[v];
+        ke = a.off[v + 1];
+    }
     uint32_t s_start = 0xFFFFFFFFu, s_end = 0xFFFFFFFFu, s_flags = 0, s_param = 0;
     if (k < ke) {
         const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
         s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
     }
+    const uint32_t tile0 = f_begin / T;
+    const uint32_t ntiles = (f_end + T - 1) / T;
+    // the ring is primed before the skip-ahead so that its latency hides behind it
+    for (uint32_t s = 0; s + 1 < S; s++) {
+        if (tile0 + s < ntiles) issue(tile0 + s); else __pipeline_commit();
+    }
+
     bool active = false;
     if (M::SKIP && f_begin > 0) {
         // spans that end before the segment: state only
@@ -92,20 +123,18 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
         }
     }
 
-    const uint32_t tile0 = f_begin / T;
-    const uint32_t ntiles = (f_end + T - 1) / T;
-    if (ntiles > tile0) issue(tile0);
     for (uint32_t tile = tile0; tile < ntiles; tile++) {
-        if (tile + 1 < ntiles) {
-            issue(tile + 1);
-            __pipeline_wait_prior(1);
-        } else {
-            __pipeline_wait_prior(0);
-        }
+        __pipeline_wait_prior(S - 2);
+        __syncthreads();  // tile `tile` has landed for every thread; every thread is done with the stage refilled next
+        if (tile + S - 1 < ntiles) issue(tile + S - 1); else __pipeline_commit();
         const uint32_t f0 = tile * T;
         const uint32_t n = min(T, f_end - f0);
-        const uint32_t stage = tile & 1u;
-        float* optr = a.out + (size_t)f0 * V + v;
+        const uint32_t stage = tile % S;
+        float* so_t = tile_ptr(stage, i_out) + tid;
+        const float* s0_t = i_in0 >= 0 ? tile_ptr(stage, i_in0) + tid : so_t;
+        const float* s1_t = i_in1 >= 0 ? tile_ptr(stage, i_in1) + tid : so_t;
+        const float* s2_t = i_in2 >= 0 ? tile_ptr(stage, i_in2) + tid : so_t;
+        int painted = 0;
         // Frames are walked in runs: up to the nearest span boundary of any of the warp's voices (one warp reduction per
         // run), so that the per-frame code carries no span bookkeeping and can be unrolled.
         uint32_t j = 0;
@@ -127,29 +156,58 @@ __global__ void __launch_bounds__(32) k_paint_lockstep(PaintArgs a, uint32_t T, 
                 active = true;
             }
             const uint32_t next_boundary = active ? s_end : s_start;
-            const uint32_t run = min(n - j, __reduce_min_sync(lanes, next_boundary - f));
+            const uint32_t run = min(n - j, __reduce_min_sync(0xffffffffu, next_boundary - f));
             if (active) {
-                const float* so = sm(stage, i_out, j);
-                const float* s0 = i_in0 >= 0 ? sm(stage, i_in0, j) : so;
-                const float* s1 = i_in1 >= 0 ? sm(stage, i_in1, j) : so;
-                const float* s2 = i_in2 >= 0 ? sm(stage, i_in2, j) : so;
-                float* op = optr + (size_t)j * V;
+                painted = 1;
+                float* so = so_t + j * RV;
+                const float* s0 = s0_t + j * RV;
+                const float* s1 = s1_t + j * RV;
+                const float* s2 = s2_t + j * RV;
 #pragma unroll 4
                 for (uint32_t r = 0; r < run; r++) {
-                    float acc = so[r * 32];
-                    const float x0 = i_in0 >= 0 ? s0[r * 32] : 0.0f;
-                    const float x1 = i_in1 >= 0 ? s1[r * 32] : 0.0f;
-                    const float x2 = i_in2 >= 0 ? s2[r * 32] : 0.0f;
+                    float acc = so[r * RV];
+                    const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
+                    const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
+                    const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
                     m.sample(acc, x0, x1, x2);
-                    op[(size_t)r * V] = acc;
+                    so[r * RV] = acc;
                 }
             }
             j += run;
         }
+        // the finished output tile goes back to HBM as full rows (skipped when nobody in the CTA painted in it)
+        if (__syncthreads_or(painted) && c_valid) {
+            float* dstg = a.out + (size_t)f0 * V + v0 + c;
+            const float* st = tile_ptr(stage, i_out) + c;
+            if (vec4) {
+                for (uint32_t jj = r0; jj < n; jj += rpp) *reinterpret_cast<float4*>(dstg + (size_t)jj * V) = *reinterpret_cast<const float4*>(st + jj * RV);
+            } else {
+                for (uint32_t jj = r0; jj < n; jj += rpp) dstg[(size_t)jj * V] = st[jj * RV];
+            }
+        }
     }
     if (f_end < a.frames) return;  // not the last segment: its state is somebody else's start
+    if (!valid) return;
     if (active) m.end_span(a);
     m.store(a, v);
 }
+
+// launch geometry shared by the module and span-restricted basics launchers
+struct PaintPlan {
+    uint32_t T, nseg, seg_frames, vec4, grid_x;
+    size_t smem;
+};
+
+inline PaintPlan zcu_paint_plan(const zcu_ctx* ctx, const PaintArgs& a, int nb, bool skippable) {
+    PaintPlan p;
+    zcu_paint_segments(ctx, a.V, a.frames, nb, skippable, &p.T, &p.nseg, &p.seg_frames);
+    auto al16 = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
+    p.vec4 = (a.V % 4 == 0 && al16(a.out) && al16(a.in0) && al16(a.in1) && al16(a.in2)) ? 1u : 0u;
+    p.grid_x = (a.V + 32 * kPaintWarps - 1) / (32 * kPaintWarps);
+    p.smem = (size_t)kPaintStages * nb * p.T * 32 * kPaintWarps * sizeof(float);
+    return p;
+}
+
+constexpr int kPaintMaxSmem = kPaintStages * 4 * 16 * 32 * kPaintWarps * 4;  // 4 buffers, T <= 16
 
 }  // namespace zcu
