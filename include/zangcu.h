@@ -154,6 +154,17 @@ const char* zcu_last_error(zcu_ctx* ctx); /* never NULL */
 void* zcu_ctx_stream(zcu_ctx* ctx);       /* the cudaStream_t every call is enqueued on */
 uint64_t zcu_ctx_launch_count(zcu_ctx* ctx); /* kernels launched by this library on this ctx so far */
 
+/* Arithmetic mode of the module paints (zcu_paint_*).
+ * ZCU_PAINT_EXACT (default): every module walks each voice's frames in the reference's order; all state-carrying
+ *   modules are bit-identical to the sequential paint() loops.
+ * ZCU_PAINT_TOLERANCE: modules whose state forgets its start (Filter, src/modules/Filter.zig:124-147) are also cut
+ *   into time segments; a segment starts from a warm-up over the preceding frames whose residual influence is verified
+ *   on the device (homogeneous map of the window <= 1e-8), else from the previous segment's end state.  Output within
+ *   1e-5 of full scale of the exact mode; every other module is unaffected. */
+enum { ZCU_PAINT_EXACT = 0, ZCU_PAINT_TOLERANCE = 1 };
+int zcu_ctx_set_paint_mode(zcu_ctx* ctx, int mode);
+int zcu_ctx_paint_mode(const zcu_ctx* ctx);
+
 /* device-side timing (CUDA events on the context stream) */
 int zcu_timer_start(zcu_ctx* ctx);
 int zcu_timer_stop_ms(zcu_ctx* ctx, float* ms); /* records, synchronises, returns elapsed */

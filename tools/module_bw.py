@@ -59,6 +59,7 @@ def main():
     ap.add_argument("--buffers", type=int, default=8)
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--only", default="", help="substring filter on the module name")
+    ap.add_argument("--tolerance", action="store_true", help="ZCU_PAINT_TOLERANCE: Filter cut into verified time segments")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "module_bw.json"))
     args = ap.parse_args()
     peaks = {}
@@ -68,6 +69,8 @@ def main():
         pass
     peak = float(peaks.get("hbm_gbs", 6553.0))
     ctx = E.Context(0)
+    if args.tolerance:
+        ctx.set_paint_mode(L.PAINT_TOLERANCE)
     results = []
     for V in [int(x) for x in args.voices.split(",")]:
         NB = args.buffers
@@ -122,7 +125,7 @@ def main():
         for x in list(ins.values()) + [out, flush, sp]:
             x.free()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
-    json.dump(dict(peak_gbs=peak, results=results), open(args.out, "w"), indent=1)
+    json.dump(dict(peak_gbs=peak, paint_mode="tolerance" if args.tolerance else "exact", results=results), open(args.out, "w"), indent=1)
     ctx.close()
 
 

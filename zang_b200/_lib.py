@@ -26,6 +26,7 @@ DIST_OVERDRIVE, DIST_CLIP = 0, 1
 AUDIO_SIGNED8, AUDIO_SIGNED16_LSB = 0, 1
 INSTR_NICE = 0
 RENDER_EXACT, RENDER_SCAN, RENDER_SEGMENTS = 0, 1, 2
+PAINT_EXACT, PAINT_TOLERANCE = 0, 1
 MAX_POLYPHONY = 32
 
 # ---- POD dtypes -------------------------------------------------------------------------------------
@@ -123,6 +124,8 @@ PROTOTYPES = {
     "zcu_last_error": (C.c_char_p, [_P]),
     "zcu_ctx_stream": (_P, [_P]),
     "zcu_ctx_launch_count": (_U64, [_P]),
+    "zcu_ctx_set_paint_mode": (_I, [_P, _I]),
+    "zcu_ctx_paint_mode": (_I, [_P]),
     "zcu_timer_start": (_I, [_P]),
     "zcu_timer_stop_ms": (_I, [_P, _P]),
     "zcu_buf_alloc": (_I, [_P, _U, _U, _P]),

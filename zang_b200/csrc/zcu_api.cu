@@ -89,6 +89,8 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 4; i++)
         if (ctx->arena[i]) cudaFree(ctx->arena[i]);
+    if (ctx->chain) cudaFree(ctx->chain);
+    if (ctx->chain_flags) cudaFree(ctx->chain_flags);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->stream && ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -103,6 +105,13 @@ int zcu_ctx_sync(zcu_ctx* ctx) {
 const char* zcu_last_error(zcu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 void* zcu_ctx_stream(zcu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 uint64_t zcu_ctx_launch_count(zcu_ctx* ctx) { return ctx ? ctx->launches : 0; }
+int zcu_ctx_set_paint_mode(zcu_ctx* ctx, int mode) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, mode == ZCU_PAINT_EXACT || mode == ZCU_PAINT_TOLERANCE, "unknown paint mode");
+    ctx->paint_mode = mode;
+    return ZCU_OK;
+}
+int zcu_ctx_paint_mode(const zcu_ctx* ctx) { return ctx ? ctx->paint_mode : ZCU_PAINT_EXACT; }
 
 int zcu_timer_start(zcu_ctx* ctx) {
     if (!ctx) return ZCU_ERR_INVALID;

@@ -20,6 +20,13 @@ struct zcu_ctx {
     void* arena[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t arena_bytes[4] = {0, 0, 0, 0};
     int sm_count = 148;
+    // ZCU_PAINT_TOLERANCE: published segment end states + ready flags (stamped with paint_epoch) of the lockstep kernel
+    int paint_mode = 0;
+    void* chain = nullptr;
+    size_t chain_bytes = 0;
+    uint32_t* chain_flags = nullptr;
+    size_t chain_flag_count = 0;
+    uint32_t paint_epoch = 0;
     // NCCL (loaded lazily with dlopen)
     void* nccl_comm = nullptr;
     int nccl_rank = 0, nccl_nranks = 1;

@@ -23,9 +23,16 @@
 
 #include <cuda_pipeline.h>
 
+#include <type_traits>
+
 #include "zcu_modules.cuh"
 
 namespace zcu {
+
+template <class M, class = void>
+struct WarmOf { static constexpr bool value = false; };
+template <class M>
+struct WarmOf<M, std::void_t<decltype(M::WARM)>> { static constexpr bool value = M::WARM; };
 
 constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
 constexpr int kPaintStages = 3;   // tiles in the cp.async ring
@@ -53,8 +60,11 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     auto tile_ptr = [&](uint32_t stage, int buf) -> float* { return smem + (size_t)(stage * nb + buf) * T * RV; };
 
     // this CTA's segment of the frame axis (seg_frames is a multiple of T)
-    const uint32_t f_begin = M::SKIP ? blockIdx.y * seg_frames : 0u;
-    const uint32_t f_end = M::SKIP ? min(a.frames, f_begin + seg_frames) : a.frames;
+    constexpr bool kWarm = WarmOf<M>::value;
+    const bool warm = kWarm && a.chain != nullptr;  // tolerance mode: segments start from a verified warm-up or the chain
+    const bool segmented = M::SKIP || warm;
+    const uint32_t f_begin = segmented ? blockIdx.y * seg_frames : 0u;
+    const uint32_t f_end = segmented ? min(a.frames, f_begin + seg_frames) : a.frames;
     if (f_begin >= f_end) return;  // uniform over the CTA
 
     // cooperative row copies: a row is RV floats; thread t moves chunk c of rows r0, r0 + RPP, ...
@@ -69,7 +79,8 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         const uint32_t n = min(T, f_end - f0);
         const uint32_t stage = tile % S;
         if (c_valid) {
-            for (int b = 0; b < nb; b++) {
+            // warm-up tiles (before the segment) only read the inputs: the output rows there belong to the previous segment
+            for (int b = (kWarm && f0 < f_begin) ? 1 : 0; b < nb; b++) {
                 const float* src = bufs[b] + (size_t)f0 * V + v0 + c;
                 float* dst = tile_ptr(stage, b) + c;
                 if (vec4) {
@@ -96,12 +107,81 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     }
     const uint32_t tile0 = f_begin / T;
     const uint32_t ntiles = (f_end + T - 1) / T;
+    uint32_t tile_first = tile0;
+    bool active = false;
+    bool pristine = false;
+    if constexpr (kWarm) {
+        if (warm && f_begin > 0) {
+            // Tolerance mode.  The state at f_begin is approximated by running the module from zero state over the Wf frames
+            // before the segment; the error is (homogeneous map of the window) x (true state at the window start), and the
+            // module tracks that map (warm_ok).  Wf: the largest per-voice estimate in the CTA, from the constants of the span
+            // at f_begin; no warm-up at all if that exceeds warm_cap (then the segment waits for its predecessor's end state).
+            __shared__ uint32_t s_w;
+            if (tid == 0) s_w = 0;
+            __syncthreads();
+            const uint32_t f_lo = f_begin > a.warm_cap ? f_begin - a.warm_cap : 0u;
+            uint32_t kk = k;
+            uint32_t p_start = s_start, p_end = s_end, p_flags = s_flags, p_param = s_param;
+            uint32_t est = 0;
+            pristine = s_start >= f_begin;  // nothing painted before the segment: the loaded state is the start state
+            if (valid && !pristine) {
+                // first span that reaches into [f_lo, ...): everything before it cannot matter
+                while (p_end <= f_lo) {
+                    kk++;
+                    if (kk < ke) {
+                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
+                        p_start = s.x; p_end = s.y; p_flags = s.z; p_param = s.w;
+                    } else {
+                        p_start = p_end = 0xFFFFFFFFu;
+                    }
+                }
+                k = kk; s_start = p_start; s_end = p_end; s_flags = p_flags; s_param = p_param;
+                // the span painting at f_begin (or the last one before it) provides the constants of the estimate
+                uint32_t q_param = 0xFFFFFFFFu, q_flags = 0, q_len = 0;
+                while (p_start < f_begin) {
+                    q_param = p_param; q_flags = p_flags; q_len = p_end - p_start;
+                    kk++;
+                    if (kk >= ke) break;
+                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
+                    p_start = s.x; p_end = s.y; p_flags = s.z; p_param = s.w;
+                }
+                est = 0xFFFFFFFFu;  // painted before, but not inside the longest window: only the chain knows the state
+                if (q_param != 0xFFFFFFFFu) {
+                    m.begin_span(a, q_param, q_flags, q_len);
+                    est = m.warm_estimate(a.warm_cap);
+                }
+                atomicMax(&s_w, est);
+            }
+            __syncthreads();
+            uint32_t Wf = s_w;
+            if (Wf > a.warm_cap) Wf = 0;  // hopeless: chain
+            Wf = min((Wf + T - 1) / T * T, f_begin / T * T);
+            if (Wf == f_begin) Wf = 0;    // a window back to frame 0 is the sequential walk: chain instead
+            const uint32_t f_w = f_begin - Wf;
+            tile_first = f_w / T;
+            if (valid && !pristine) {
+                m.warm_begin();
+                while (s_end <= f_w) {
+                    k++;
+                    if (k < ke) {
+                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                        s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+                    } else {
+                        s_start = s_end = 0xFFFFFFFFu;
+                    }
+                }
+                if (s_start < f_w) {  // entered in the middle: only the span's constants are needed
+                    m.begin_span(a, s_param, s_flags, s_end - s_start);
+                    active = true;
+                }
+            }
+        }
+    }
     // the ring is primed before the skip-ahead so that its latency hides behind it
     for (uint32_t s = 0; s + 1 < S; s++) {
-        if (tile0 + s < ntiles) issue(tile0 + s); else __pipeline_commit();
+        if (tile_first + s < ntiles) issue(tile_first + s); else __pipeline_commit();
     }
 
-    bool active = false;
     if (M::SKIP && f_begin > 0) {
         // spans that end before the segment: state only
         while (s_end <= f_begin) {
@@ -123,7 +203,25 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         }
     }
 
-    for (uint32_t tile = tile0; tile < ntiles; tile++) {
+    for (uint32_t tile = tile_first; tile < ntiles; tile++) {
+        if constexpr (kWarm) {
+            if (warm && f_begin > 0 && tile == tile0) {
+                // end of the warm-up: keep the warmed state if every voice of the CTA verified its window, otherwise wait
+                // for the end state the previous segment publishes (CTAs are dispatched in blockIdx order, so the
+                // predecessor is resident or done: no deadlock; an undamped filter degenerates to the sequential walk)
+                const bool ok = !valid || pristine || (tile_first < tile0 && m.warm_ok());
+                if (!__syncthreads_and(ok)) {
+                    if (tid == 0) {
+                        const volatile uint32_t* fl = a.chain_flags + (size_t)(blockIdx.y - 1) * gridDim.x + blockIdx.x;
+                        while (*fl != a.epoch) __nanosleep(256);
+                        __threadfence();
+                    }
+                    __syncthreads();
+                    if (valid && !pristine) m.chain_load(a.chain + (size_t)(blockIdx.y - 1) * V + v);
+                }
+            }
+        }
+        const bool warm_tile = kWarm && tile < tile0;
         __pipeline_wait_prior(S - 2);
         __syncthreads();  // tile `tile` has landed for every thread; every thread is done with the stage refilled next
         if (tile + S - 1 < ntiles) issue(tile + S - 1); else __pipeline_commit();
@@ -157,6 +255,24 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             }
             const uint32_t next_boundary = active ? s_end : s_start;
             const uint32_t run = min(n - j, __reduce_min_sync(0xffffffffu, next_boundary - f));
+            if constexpr (kWarm) {
+                if (warm_tile) {
+                    if (active) {
+                        const float* s0 = s0_t + j * RV;
+                        const float* s1 = s1_t + j * RV;
+                        const float* s2 = s2_t + j * RV;
+#pragma unroll 4
+                        for (uint32_t r = 0; r < run; r++) {
+                            const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
+                            const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
+                            const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
+                            m.sample_warm(x0, x1, x2);
+                        }
+                    }
+                    j += run;
+                    continue;
+                }
+            }
             if (active) {
                 painted = 1;
                 float* so = so_t + j * RV;
@@ -184,6 +300,14 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             } else {
                 for (uint32_t jj = r0; jj < n; jj += rpp) dstg[(size_t)jj * V] = st[jj * RV];
             }
+        }
+    }
+    if constexpr (kWarm) {
+        if (warm && f_end < a.frames) {  // publish the end state for a successor that could not verify its warm-up
+            if (valid) m.chain_store(a.chain + (size_t)blockIdx.y * V + v);
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) atomicExch(a.chain_flags + (size_t)blockIdx.y * gridDim.x + blockIdx.x, a.epoch);
         }
     }
     if (f_end < a.frames) return;  // not the last segment: its state is somebody else's start

@@ -54,6 +54,13 @@ class Context:
     def launch_count(self):
         return int(lib.zcu_ctx_launch_count(self._h))
 
+    def set_paint_mode(self, mode):
+        """L.PAINT_EXACT (default, bit-exact) or L.PAINT_TOLERANCE (Filter cut into verified time segments)."""
+        _check(self, lib.zcu_ctx_set_paint_mode(self._h, int(mode)))
+
+    def paint_mode(self):
+        return int(lib.zcu_ctx_paint_mode(self._h))
+
     def timer_start(self):
         _check(self, lib.zcu_timer_start(self._h))
 
