@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libzangcu.so")
+LIB_PATH = os.environ.get("ZANGCU_LIB", os.path.join(_HERE, "libzangcu.so"))  # override: A/B builds of the same ABI
 
 # ---- error codes / enums (zangcu.h) ---------------------------------------------------------------
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_OOM, ERR_UNSUPPORTED, ERR_NCCL = range(7)

@@ -34,6 +34,13 @@ struct WarmOf { static constexpr bool value = false; };
 template <class M>
 struct WarmOf<M, std::void_t<decltype(M::WARM)>> { static constexpr bool value = M::WARM; };
 
+// m.sample_warm() for modules that have it (the call sits in a generic lambda, where a plain member call would be looked up
+// for every module)
+template <class M, bool = WarmOf<M>::value>
+struct WarmCall { static __device__ __forceinline__ void sample(M&, float, float, float) {} };
+template <class M>
+struct WarmCall<M, true> { static __device__ __forceinline__ void sample(M& m, float x0, float x1, float x2) { m.sample_warm(x0, x1, x2); } };
+
 constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
 constexpr int kPaintStages = 3;   // tiles in the cp.async ring
 
@@ -46,14 +53,13 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const uint32_t v = v0 + tid;
     const bool valid = v < a.V;
 
-    const float* bufs[4];
-    int nb = 0;
-    const int i_out = nb;
-    bufs[nb++] = a.out;
+    // staged buffers: slot 0 = output, then the inputs that are present (no pointer array: it would live in local memory)
+    int nb = 1;
+    const int i_out = 0;
     int i_in0 = -1, i_in1 = -1, i_in2 = -1;
-    if (M::NIN >= 1 && a.in0) { i_in0 = nb; bufs[nb++] = a.in0; }
-    if (M::NIN >= 2 && a.in1) { i_in1 = nb; bufs[nb++] = a.in1; }
-    if (M::NIN >= 3 && a.in2) { i_in2 = nb; bufs[nb++] = a.in2; }
+    if (M::NIN >= 1 && a.in0) i_in0 = nb++;
+    if (M::NIN >= 2 && a.in1) i_in1 = nb++;
+    if (M::NIN >= 3 && a.in2) i_in2 = nb++;
 
     const size_t V = a.V;
     // smem layout [stage][buf][T][RV]
@@ -74,21 +80,25 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const uint32_t c = (tid % cpr) * cw, r0 = tid / cpr;
     const bool c_valid = v0 + c < a.V;
 
+    auto copy_rows = [&](const float* buf, int slot, uint32_t stage, uint32_t f0, uint32_t n) {
+        const float* src = buf + (size_t)f0 * V + v0 + c;
+        float* dst = tile_ptr(stage, slot) + c;
+        if (vec4) {
+            for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 16);
+        } else {
+            for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 4);
+        }
+    };
     auto issue = [&](uint32_t tile) {
         const uint32_t f0 = tile * T;
         const uint32_t n = min(T, f_end - f0);
         const uint32_t stage = tile % S;
         if (c_valid) {
             // warm-up tiles (before the segment) only read the inputs: the output rows there belong to the previous segment
-            for (int b = (kWarm && f0 < f_begin) ? 1 : 0; b < nb; b++) {
-                const float* src = bufs[b] + (size_t)f0 * V + v0 + c;
-                float* dst = tile_ptr(stage, b) + c;
-                if (vec4) {
-                    for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 16);
-                } else {
-                    for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 4);
-                }
-            }
+            if (!(kWarm && f0 < f_begin)) copy_rows(a.out, i_out, stage, f0, n);
+            if (M::NIN >= 1 && i_in0 >= 0) copy_rows(a.in0, i_in0, stage, f0, n);
+            if (M::NIN >= 2 && i_in1 >= 0) copy_rows(a.in1, i_in1, stage, f0, n);
+            if (M::NIN >= 3 && i_in2 >= 0) copy_rows(a.in2, i_in2, stage, f0, n);
         }
         __pipeline_commit();
     };
@@ -203,25 +213,10 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         }
     }
 
-    for (uint32_t tile = tile_first; tile < ntiles; tile++) {
-        if constexpr (kWarm) {
-            if (warm && f_begin > 0 && tile == tile0) {
-                // end of the warm-up: keep the warmed state if every voice of the CTA verified its window, otherwise wait
-                // for the end state the previous segment publishes (CTAs are dispatched in blockIdx order, so the
-                // predecessor is resident or done: no deadlock; an undamped filter degenerates to the sequential walk)
-                const bool ok = !valid || pristine || (tile_first < tile0 && m.warm_ok());
-                if (!__syncthreads_and(ok)) {
-                    if (tid == 0) {
-                        const volatile uint32_t* fl = a.chain_flags + (size_t)(blockIdx.y - 1) * gridDim.x + blockIdx.x;
-                        while (*fl != a.epoch) __nanosleep(256);
-                        __threadfence();
-                    }
-                    __syncthreads();
-                    if (valid && !pristine) m.chain_load(a.chain + (size_t)(blockIdx.y - 1) * V + v);
-                }
-            }
-        }
-        const bool warm_tile = kWarm && tile < tile0;
+    // one tile of the ring: wait, refill, walk the frames in runs, write the output tile back.  WT = warm-up tile (tolerance
+    // mode, before the segment): the module only advances its state, nothing is read from or written to the output.
+    auto do_tile = [&](uint32_t tile, auto wt_tag) {
+        constexpr bool WT = decltype(wt_tag)::value;
         __pipeline_wait_prior(S - 2);
         __syncthreads();  // tile `tile` has landed for every thread; every thread is done with the stage refilled next
         if (tile + S - 1 < ntiles) issue(tile + S - 1); else __pipeline_commit();
@@ -255,38 +250,30 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             }
             const uint32_t next_boundary = active ? s_end : s_start;
             const uint32_t run = min(n - j, __reduce_min_sync(0xffffffffu, next_boundary - f));
-            if constexpr (kWarm) {
-                if (warm_tile) {
-                    if (active) {
-                        const float* s0 = s0_t + j * RV;
-                        const float* s1 = s1_t + j * RV;
-                        const float* s2 = s2_t + j * RV;
-#pragma unroll 4
-                        for (uint32_t r = 0; r < run; r++) {
-                            const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
-                            const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
-                            const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
-                            m.sample_warm(x0, x1, x2);
-                        }
-                    }
-                    j += run;
-                    continue;
-                }
-            }
             if (active) {
-                painted = 1;
                 float* so = so_t + j * RV;
                 const float* s0 = s0_t + j * RV;
                 const float* s1 = s1_t + j * RV;
                 const float* s2 = s2_t + j * RV;
+                if constexpr (WT) {
 #pragma unroll 4
-                for (uint32_t r = 0; r < run; r++) {
-                    float acc = so[r * RV];
-                    const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
-                    const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
-                    const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
-                    m.sample(acc, x0, x1, x2);
-                    so[r * RV] = acc;
+                    for (uint32_t r = 0; r < run; r++) {
+                        const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
+                        const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
+                        const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
+                        WarmCall<M>::sample(m, x0, x1, x2);
+                    }
+                } else {
+                    painted = 1;
+#pragma unroll 4
+                    for (uint32_t r = 0; r < run; r++) {
+                        float acc = so[r * RV];
+                        const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
+                        const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
+                        const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
+                        m.sample(acc, x0, x1, x2);
+                        so[r * RV] = acc;
+                    }
                 }
             }
             j += run;
@@ -301,7 +288,28 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 for (uint32_t jj = r0; jj < n; jj += rpp) dstg[(size_t)jj * V] = st[jj * RV];
             }
         }
+    };
+
+    if constexpr (kWarm) {
+        if (warm && f_begin > 0) {
+            for (uint32_t tile = tile_first; tile < tile0; tile++) do_tile(tile, std::true_type{});
+            // end of the warm-up: keep the warmed state if every voice of the CTA verified its window, otherwise wait for the
+            // end state the previous segment publishes (CTAs are dispatched in blockIdx order, so the predecessor is resident
+            // or done: no deadlock; an undamped filter degenerates to the sequential walk)
+            const bool ok = !valid || pristine || (tile_first < tile0 && m.warm_ok());
+            if (!__syncthreads_and(ok)) {
+                if (tid == 0) {
+                    const volatile uint32_t* fl = a.chain_flags + (size_t)(blockIdx.y - 1) * gridDim.x + blockIdx.x;
+                    while (*fl != a.epoch) __nanosleep(256);
+                    __threadfence();
+                }
+                __syncthreads();
+                if (valid && !pristine) m.chain_load(a.chain + (size_t)(blockIdx.y - 1) * V + v);
+            }
+        }
     }
+    for (uint32_t tile = tile0; tile < ntiles; tile++) do_tile(tile, std::false_type{});
+
     if constexpr (kWarm) {
         if (warm && f_end < a.frames) {  // publish the end state for a successor that could not verify its warm-up
             if (valid) m.chain_store(a.chain + (size_t)blockIdx.y * V + v);
