@@ -76,6 +76,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "bank_bench.json"))
     ap.add_argument("--scale", type=float, default=1.0, help="scale the voice counts (smoke runs)")
+    ap.add_argument("--exact", action="store_true", help="ZCU_PAINT_EXACT (default here: ZCU_PAINT_TOLERANCE, Filter in verified time segments)")
     args = ap.parse_args()
     peak = 6553.0
     try:
@@ -83,6 +84,7 @@ def main():
     except Exception:
         pass
     ctx = E.Context(0)
+    ctx.set_paint_mode(L.PAINT_EXACT if args.exact else L.PAINT_TOLERANCE)
     res = []
     sc = args.scale
     # configs[1] polyphony bank, un-fused: 4096 voices, 64 mix buffers
@@ -109,7 +111,7 @@ def main():
     wl = synth.sfx_bank(V, frames)
     res.append(run(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 3, 100, peak))
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
-    json.dump(dict(peak_gbs=peak, results=res), open(args.out, "w"), indent=1)
+    json.dump(dict(peak_gbs=peak, paint_mode="exact" if args.exact else "tolerance", results=res), open(args.out, "w"), indent=1)
     ctx.close()
 
 

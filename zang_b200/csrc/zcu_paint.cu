@@ -56,7 +56,7 @@ int launch(zcu_ctx* ctx, PaintArgs a) {
         a.chain = (float2*)ctx->chain;
         a.chain_flags = ctx->chain_flags;
         a.epoch = ++ctx->paint_epoch;
-        a.warm_cap = p.seg_frames;
+        a.warm_cap = (uint32_t)std::min<uint64_t>(a.frames, 8ull * p.seg_frames);  // a window longer than this: chain instead
     } else if (!M::SKIP) {
         p.nseg = 1;
         p.seg_frames = a.frames;
