@@ -56,7 +56,10 @@ enum {
     ZCU_MOD_DECIMATOR = 10,  /* src/modules/Decimator.zig */
     ZCU_MOD_DISTORTION = 11, /* src/modules/Distortion.zig */
     ZCU_MOD_CYCLE = 12,      /* src/modules/Cycle.zig */
-    ZCU_MOD_COUNT = 13
+    /* the delay line and the echo modules built on it (next-row scope) */
+    ZCU_MOD_SIMPLE_DELAY = 13,    /* examples/modules.zig:341-388 over src/zang/delay.zig:7-91 */
+    ZCU_MOD_FILTERED_ECHOES = 14, /* examples/modules.zig:392-460 */
+    ZCU_MOD_COUNT = 15
 };
 
 /* ---- opaque handles ----------------------------------------------------------------------- */
@@ -96,6 +99,9 @@ typedef struct {                                                /* Curve.zig:36-
 typedef struct { float t; } zcu_sampler_state;                  /* Sampler.zig:69 */
 typedef struct { float dval, dcount; } zcu_decimator_state;     /* Decimator.zig:11-12 */
 typedef struct { float t; } zcu_cycle_state;                    /* Cycle.zig:14 */
+/* zang.Delay (delay.zig:9-10): the index; the delay_buffer itself lives in the bank ([delay_samples][voices] f32) */
+typedef struct { uint32_t index; } zcu_delay_state;
+typedef struct { uint32_t index; float l, b; } zcu_echoes_state; /* FilteredEchoes: Delay + Filter (modules.zig:403-404) */
 
 enum { ZCU_ENV_IDLE = 0, ZCU_ENV_ATTACK = 1, ZCU_ENV_DECAY = 2, ZCU_ENV_SUSTAIN = 3, ZCU_ENV_RELEASE = 4 };
 
@@ -140,6 +146,7 @@ typedef struct { float sample_rate, fake_sample_rate; } zcu_decimator_params;   
 enum { ZCU_DIST_OVERDRIVE = 0, ZCU_DIST_CLIP = 1 };
 typedef struct { int32_t type; float ingain, outgain, offset; } zcu_distortion_params;   /* Distortion.zig:13-19 */
 typedef struct { float sample_rate, speed; } zcu_cycle_params;                            /* Cycle.zig:9-12 */
+typedef struct { float feedback_volume, cutoff; } zcu_echoes_params;                      /* modules.zig:396-400 (input = buffer arg) */
 
 /* ---- library / context --------------------------------------------------------------------- */
 int zcu_abi_version(void);
@@ -187,6 +194,14 @@ int zcu_bank_reset(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed);
 size_t zcu_bank_state_size(int module_kind); /* sizeof the per-voice state POD (0 = stateless) */
 int zcu_bank_get_state(zcu_ctx* ctx, const zcu_bank* bank, void* host, size_t bytes); /* checkpoint */
 int zcu_bank_set_state(zcu_ctx* ctx, zcu_bank* bank, const void* host, size_t bytes); /* resume */
+
+/* Banks of the delay modules (ZCU_MOD_SIMPLE_DELAY, ZCU_MOD_FILTERED_ECHOES): `delay_samples` is the comptime parameter
+ * of zang.Delay (delay.zig:7); the bank owns one zeroed delay line per voice (delay.zig:12-17), [delay_samples][voices].
+ * zcu_bank_reset zeroes it again (delay.zig:19-22).  get/set_delay_line: checkpoint / resume of the lines. */
+int zcu_delay_bank_create(zcu_ctx* ctx, int module_kind, uint32_t voices, uint32_t delay_samples, zcu_bank** out);
+uint32_t zcu_bank_delay_samples(const zcu_bank* bank);
+int zcu_bank_get_delay_line(zcu_ctx* ctx, const zcu_bank* bank, float* host, size_t bytes);
+int zcu_bank_set_delay_line(zcu_ctx* ctx, zcu_bank* bank, const float* host, size_t bytes);
 
 /* ---- span tables ----------------------------------------------------------------------------- */
 /* voice_off has voices+1 entries; spans of voice v are spans[voice_off[v] .. voice_off[v+1]), sorted
@@ -249,6 +264,14 @@ int zcu_paint_distortion(zcu_ctx*, const zcu_spans*, const zcu_distortion_params
                          zcu_buf* out, const zcu_buf* input);
 int zcu_paint_cycle(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_cycle_params*, uint32_t nparams,
                     zcu_buf* out, const zcu_buf* speed);
+
+/* SimpleDelay.paint (examples/modules.zig:362-386): out += the input of delay_samples painted frames ago.  Exact, sequential
+ * in time (one segment); the delay line is read and written in place, per voice, in paint order. */
+int zcu_paint_simple_delay(zcu_ctx*, zcu_bank*, const zcu_spans*, zcu_buf* out, const zcu_buf* input);
+/* FilteredEchoes.paint (examples/modules.zig:409-459): y = lowpass(delayed * feedback_volume + input), out += y, y goes
+ * back into the delay line.  The reference's temps never exist: one pass, one read of input, one read-modify-write of out. */
+int zcu_paint_filtered_echoes(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_echoes_params*, uint32_t nparams,
+                              zcu_buf* out, const zcu_buf* input);
 
 /* Filter.cutoffFromFrequency (Filter.zig:20-23): host scalar, f32 arithmetic */
 float zcu_filter_cutoff_from_frequency(float frequency, float sample_rate);

@@ -12,6 +12,7 @@
 #include "../include/zangcu.h"
 #include "zang_oracle.hpp"
 #include "bank_oracle.hpp"
+#include "delay_oracle.hpp"
 #include "song_oracle.hpp"
 
 using namespace zo;
@@ -259,6 +260,87 @@ int orc_paint(int kind, uint32_t V, uint32_t frames, const uint32_t* off, const 
             }
             co.scatter(s, e, o.data());
         }
+    }
+    return 0;
+}
+
+// ---- delay modules: kind = ZCU_MOD_SIMPLE_DELAY / ZCU_MOD_FILTERED_ECHOES -------------------------------------
+// state: zcu_delay_state / zcu_echoes_state rows; line: [delay_samples][V] f32 (the per-voice delay_buffer, voice fastest);
+// params: zcu_echoes_params rows (FilteredEchoes only).  Each span is one reference paint() call, chunked as the reference does.
+int orc_paint_delay(int kind, uint32_t V, uint32_t frames, const uint32_t* off, const zcu_span* spans, const void* params,
+                    uint32_t nparams, void* state, float* line, uint32_t delay_samples, float* out, const float* in0) {
+    std::vector<float> o(frames), i0(frames), t0(frames), t1(frames);
+    for (uint32_t v = 0; v < V; v++) {
+        Col co{out, V, v}, c0{(float*)in0, V, v};
+        Delay d(delay_samples);
+        for (uint32_t q = 0; q < delay_samples; q++) d.delay_buffer[q] = line[(size_t)q * V + v];
+        Filter flt;
+        if (kind == ZCU_MOD_SIMPLE_DELAY) {
+            d.delay_buffer_index = ((zcu_delay_state*)state)[v].index;
+        } else {
+            auto& st = ((zcu_echoes_state*)state)[v];
+            d.delay_buffer_index = st.index;
+            flt.l = st.l;
+            flt.b = st.b;
+        }
+        for (uint32_t k = off[v]; k < off[v + 1]; k++) {
+            const zcu_span& zs = spans[k];
+            const uint32_t s = zs.start, e = zs.end;
+            const bool nic = (zs.flags & ZCU_SPAN_NOTE_ID_CHANGED) != 0;
+            co.gather(s, e, o.data());
+            c0.gather(s, e, i0.data());
+            Span sp{0, (size_t)(e - s)};
+            if (kind == ZCU_MOD_SIMPLE_DELAY) {
+                SimpleDelay m(1);
+                m.delay = d;
+                m.paint(sp, o.data(), nic, i0.data());
+                d = m.delay;
+            } else if (kind == ZCU_MOD_FILTERED_ECHOES) {
+                if (zs.param >= nparams) return 2;
+                const auto& p = ((const zcu_echoes_params*)params)[zs.param];
+                FilteredEchoes m(1);
+                m.delay = d;
+                m.filter = flt;
+                m.paint(sp, o.data(), t0.data(), t1.data(), nic, {i0.data(), p.feedback_volume, p.cutoff});
+                d = m.delay;
+                flt = m.filter;
+            } else {
+                return 1;
+            }
+            co.scatter(s, e, o.data());
+        }
+        for (uint32_t q = 0; q < delay_samples; q++) line[(size_t)q * V + v] = d.delay_buffer[q];
+        if (kind == ZCU_MOD_SIMPLE_DELAY) {
+            ((zcu_delay_state*)state)[v].index = (uint32_t)d.delay_buffer_index;
+        } else {
+            auto& st = ((zcu_echoes_state*)state)[v];
+            st.index = (uint32_t)d.delay_buffer_index;
+            st.l = flt.l;
+            st.b = flt.b;
+        }
+    }
+    return 0;
+}
+
+// StereoEchoes (examples/modules.zig:462-525) on V independent mono inputs: out_l/out_r/input are [frames][V]; one paint() call per
+// mix buffer of buffer_frames (the un-triggered call pattern of example_delay.zig).  State starts from init() and is not returned.
+int orc_stereo_echoes(uint32_t V, uint32_t frames, uint32_t buffer_frames, uint32_t main_delay, float feedback_volume, float cutoff,
+                      const float* input, float* out_l, float* out_r) {
+    std::vector<float> in(frames), l(frames), r(frames), t[4];
+    for (auto& x : t) x.resize(frames);
+    for (uint32_t v = 0; v < V; v++) {
+        Col ci{(float*)input, V, v}, cl{out_l, V, v}, cr{out_r, V, v};
+        ci.gather(0, frames, in.data());
+        cl.gather(0, frames, l.data());
+        cr.gather(0, frames, r.data());
+        StereoEchoes m(main_delay);
+        float* temps[4] = {t[0].data(), t[1].data(), t[2].data(), t[3].data()};
+        for (uint32_t f = 0; f < frames; f += buffer_frames) {
+            const Span sp{f, std::min<size_t>(frames, (size_t)f + buffer_frames)};
+            m.paint(sp, l.data(), r.data(), temps, f == 0, in.data(), feedback_volume, cutoff);
+        }
+        cl.scatter(0, frames, l.data());
+        cr.scatter(0, frames, r.data());
     }
     return 0;
 }

@@ -24,6 +24,8 @@ _P, _I, _U, _F, _U64 = C.c_void_p, C.c_int, C.c_uint32, C.c_float, C.c_uint64
 orc.orc_basic.argtypes = [_I, _U, _U, _P, _P, _P, _P, _P, _F]
 orc.orc_paint.argtypes = [_I, _U, _U, _P, _P, _P, _U, _P, _P, _P, _P, _P, _P, _U64, _P]
 orc.orc_state_init.argtypes = [_I, _U, _U, _P]
+orc.orc_paint_delay.argtypes = [_I, _U, _U, _P, _P, _P, _U, _P, _P, _U, _P, _P]
+orc.orc_stereo_echoes.argtypes = [_U, _U, _U, _U, _F, _F, _P, _P, _P]
 orc.orc_cutoff_from_frequency.argtypes = [_F, _F]
 orc.orc_cutoff_from_frequency.restype = _F
 orc.orc_xoshiro_seed.argtypes = [_U64, _P]
@@ -71,6 +73,28 @@ def paint(kind, off, spans, params, state, out, in0=None, in1=None, in2=None, au
     rc = orc.orc_paint(kind, V, frames, ptr(off), ptr(spans), ptr(params), params.size, ptr(state), ptr(out), ptr(in0), ptr(in1),
                        ptr(in2), ptr(aux), aux_len, ptr(meta))
     assert rc == 0, rc
+
+
+def paint_delay(kind, off, spans, params, state, line, out, in0):
+    """SimpleDelay / FilteredEchoes: in-place on `out`, `state` (index[, l, b] rows) and `line` ([delay_samples][V] f32)."""
+    frames, V = out.shape
+    assert line.dtype == np.float32 and line.flags.c_contiguous and line.shape[1] == V
+    if params is None:
+        params = np.zeros(1, dtype=L.param_dtypes[kind])
+    params = np.ascontiguousarray(params, dtype=L.param_dtypes[kind]).reshape(-1)
+    rc = orc.orc_paint_delay(kind, V, frames, ptr(off), ptr(spans), ptr(params), params.size, ptr(state), ptr(line), line.shape[0], ptr(out),
+                             ptr(in0))
+    assert rc == 0, rc
+
+
+def stereo_echoes(inp, buffer_frames, main_delay, feedback_volume, cutoff):
+    """StereoEchoes over V mono inputs ([frames][V]), painted buffer by buffer from init(); returns (left, right)."""
+    frames, V = inp.shape
+    left = np.zeros_like(inp)
+    right = np.zeros_like(inp)
+    rc = orc.orc_stereo_echoes(V, frames, buffer_frames, main_delay, float(feedback_volume), float(cutoff), ptr(inp), ptr(left), ptr(right))
+    assert rc == 0, rc
+    return left, right
 
 
 def basic(op, off, spans, dest, a=None, b=None, scalar=0.0):

@@ -185,6 +185,8 @@ size_t zcu_bank_state_size(int kind) {
         case ZCU_MOD_SAMPLER: return sizeof(zcu_sampler_state);
         case ZCU_MOD_DECIMATOR: return sizeof(zcu_decimator_state);
         case ZCU_MOD_CYCLE: return sizeof(zcu_cycle_state);
+        case ZCU_MOD_SIMPLE_DELAY: return sizeof(zcu_delay_state);
+        case ZCU_MOD_FILTERED_ECHOES: return sizeof(zcu_echoes_state);
         default: return 0;  // Gate, Distortion: stateless
     }
 }
@@ -192,6 +194,7 @@ int zcu_bank_create(zcu_ctx* ctx, int kind, uint32_t voices, uint32_t first_seed
     if (!ctx || !out) return ZCU_ERR_INVALID;
     *out = nullptr;
     ZCU_REQUIRE(ctx, kind >= 0 && kind < ZCU_MOD_COUNT, "unknown module kind");
+    ZCU_REQUIRE(ctx, kind != ZCU_MOD_SIMPLE_DELAY && kind != ZCU_MOD_FILTERED_ECHOES, "delay modules: use zcu_delay_bank_create");
     zcu_bank* b = new zcu_bank{ctx, kind, voices, nullptr, zcu_bank_state_size(kind)};
     size_t bytes = b->stride * voices;
     if (bytes) {
@@ -209,12 +212,51 @@ int zcu_bank_create(zcu_ctx* ctx, int kind, uint32_t voices, uint32_t first_seed
     *out = b;
     return ZCU_OK;
 }
+int zcu_delay_bank_create(zcu_ctx* ctx, int kind, uint32_t voices, uint32_t delay_samples, zcu_bank** out) {
+    if (!ctx || !out) return ZCU_ERR_INVALID;
+    *out = nullptr;
+    ZCU_REQUIRE(ctx, kind == ZCU_MOD_SIMPLE_DELAY || kind == ZCU_MOD_FILTERED_ECHOES, "not a delay module kind");
+    ZCU_REQUIRE(ctx, delay_samples > 0, "delay_samples must be > 0");
+    zcu_bank* b = new zcu_bank{ctx, kind, voices, nullptr, zcu_bank_state_size(kind)};
+    b->delay_samples = delay_samples;
+    const size_t bytes = b->stride * voices, lbytes = (size_t)delay_samples * voices * sizeof(float);
+    cudaError_t e = cudaSuccess;
+    if (bytes) e = cudaMalloc(&b->d, bytes);
+    if (e == cudaSuccess && lbytes) e = cudaMalloc(&b->line, lbytes);
+    if (e != cudaSuccess) {
+        zcu_bank_free(b);
+        return zcu_fail(ctx, ZCU_ERR_OOM, "cudaMalloc(%zu + %zu) failed: %s", bytes, lbytes, cudaGetErrorString(e));
+    }
+    int rc = zcu_launch_bank_init(ctx, b, 0);
+    if (rc) {
+        zcu_bank_free(b);
+        return rc;
+    }
+    *out = b;
+    return ZCU_OK;
+}
+uint32_t zcu_bank_delay_samples(const zcu_bank* bank) { return bank ? bank->delay_samples : 0; }
+int zcu_bank_get_delay_line(zcu_ctx* ctx, const zcu_bank* bank, float* host, size_t bytes) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, bank && host, "null argument");
+    ZCU_REQUIRE(ctx, bytes == (size_t)bank->delay_samples * bank->voices * sizeof(float), "size mismatch");
+    if (bytes) ZCU_CUDA(ctx, cudaMemcpyAsync(host, bank->line, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ZCU_OK;
+}
+int zcu_bank_set_delay_line(zcu_ctx* ctx, zcu_bank* bank, const float* host, size_t bytes) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, bank && host, "null argument");
+    ZCU_REQUIRE(ctx, bytes == (size_t)bank->delay_samples * bank->voices * sizeof(float), "size mismatch");
+    if (bytes) ZCU_CUDA(ctx, cudaMemcpyAsync(bank->line, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ZCU_OK;
+}
 void zcu_bank_free(zcu_bank* bank) {
     if (!bank) return;
-    if (bank->d) {
-        cudaStreamSynchronize(bank->ctx->stream);
-        cudaFree(bank->d);
-    }
+    if (bank->d || bank->line) cudaStreamSynchronize(bank->ctx->stream);
+    if (bank->d) cudaFree(bank->d);
+    if (bank->line) cudaFree(bank->line);
     delete bank;
 }
 int zcu_bank_reset(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed) {
@@ -362,6 +404,8 @@ static int paint_call(zcu_ctx* ctx, int kind, zcu_bank* bank, const zcu_spans* s
     pl.in2 = in2 ? in2->d : nullptr;
     pl.aux = aux_dev;
     pl.aux_len = aux_len;
+    pl.line = bank ? bank->line : nullptr;
+    pl.delay_samples = bank ? bank->delay_samples : 0;
     if (smp) {
         pl.aux = smp->d;
         pl.aux_len = smp->len;
@@ -432,6 +476,19 @@ int zcu_paint_distortion(zcu_ctx* c, const zcu_spans* s, const zcu_distortion_pa
 }
 int zcu_paint_cycle(zcu_ctx* c, zcu_bank* b, const zcu_spans* s, const zcu_cycle_params* p, uint32_t n, zcu_buf* out, const zcu_buf* speed) {
     return paint_call(c, ZCU_MOD_CYCLE, b, s, p, sizeof *p, n, out, speed, nullptr, nullptr, false, nullptr, 0, nullptr);
+}
+
+int zcu_paint_simple_delay(zcu_ctx* c, zcu_bank* b, const zcu_spans* s, zcu_buf* out, const zcu_buf* input) {
+    // SimpleDelay.Params holds nothing but the input slice (modules.zig:345-347): whatever rows the spans name are empty
+    const std::vector<uint32_t> rows(s ? (size_t)s->max_param + 1 : 1, 0u);
+    if (c && b) ZCU_REQUIRE(c, b->line != nullptr, "bank has no delay line (zcu_delay_bank_create)");
+    return paint_call(c, ZCU_MOD_SIMPLE_DELAY, b, s, rows.data(), sizeof(uint32_t), (uint32_t)rows.size(), out, input, nullptr, nullptr, true, nullptr, 0,
+                      nullptr);
+}
+int zcu_paint_filtered_echoes(zcu_ctx* c, zcu_bank* b, const zcu_spans* s, const zcu_echoes_params* p, uint32_t n, zcu_buf* out,
+                              const zcu_buf* input) {
+    if (c && b) ZCU_REQUIRE(c, b->line != nullptr, "bank has no delay line (zcu_delay_bank_create)");
+    return paint_call(c, ZCU_MOD_FILTERED_ECHOES, b, s, p, sizeof *p, n, out, input, nullptr, nullptr, true, nullptr, 0, nullptr);
 }
 
 float zcu_filter_cutoff_from_frequency(float frequency, float sample_rate) {  // Filter.zig:20-23

@@ -265,6 +265,13 @@ __global__ void k_bank_init(int kind, void* state, uint32_t V, uint32_t first_se
             ((zcu_decimator_state*)state)[v] = s;
         } break;
         case ZCU_MOD_CYCLE: ((zcu_cycle_state*)state)[v].t = 0.0f; break;
+        case ZCU_MOD_SIMPLE_DELAY: ((zcu_delay_state*)state)[v].index = 0; break;  // delay.zig:12-17
+        case ZCU_MOD_FILTERED_ECHOES: {
+            zcu_echoes_state s;
+            s.index = 0;
+            s.l = s.b = 0.0f;
+            ((zcu_echoes_state*)state)[v] = s;
+        } break;
         default: break;
     }
 }
@@ -308,6 +315,7 @@ int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed) {
     k_bank_init<<<(bank->voices + 127) / 128, 128, 0, ctx->stream>>>(bank->kind, bank->d, bank->voices, first_seed);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
+    if (bank->line) ZCU_CUDA(ctx, cudaMemsetAsync(bank->line, 0, (size_t)bank->delay_samples * bank->voices * sizeof(float), ctx->stream));
     return ZCU_OK;
 }
 

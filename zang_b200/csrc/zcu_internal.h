@@ -45,6 +45,8 @@ struct zcu_bank {
     uint32_t voices;
     void* d;        // voices * stride bytes
     size_t stride;  // sizeof the state POD
+    float* line = nullptr;        // delay modules: [delay_samples][voices]
+    uint32_t delay_samples = 0;
 };
 
 struct zcu_spans {
@@ -105,6 +107,8 @@ struct PaintLaunch {
     uint64_t aux_len;
     uint32_t smp_channels, smp_rate;
     int smp_format;
+    float* line;             // delay modules
+    uint32_t delay_samples;
 };
 int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl);
 int zcu_launch_basic(zcu_ctx* ctx, int op, const zcu_spans* spans, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b, float scalar);

@@ -118,6 +118,8 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     a.smp.num_channels = pl.smp_channels;
     a.smp.sample_rate = pl.smp_rate;
     a.smp.format = pl.smp_format;
+    a.line = pl.line;
+    a.delay_samples = pl.delay_samples;
     if (a.V == 0 || a.frames == 0) return ZCU_OK;
     const bool b0 = pl.in0 != nullptr, b1 = pl.in1 != nullptr, b2 = pl.in2 != nullptr;
     switch (pl.kind) {
@@ -143,6 +145,8 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
         case ZCU_MOD_SAMPLER: return launch<SamplerMod>(ctx, a);
         case ZCU_MOD_DECIMATOR: return launch<DecimatorMod>(ctx, a);
         case ZCU_MOD_DISTORTION: return launch<DistortionMod>(ctx, a);
+        case ZCU_MOD_SIMPLE_DELAY: return launch<SimpleDelayMod>(ctx, a);
+        case ZCU_MOD_FILTERED_ECHOES: return launch<FilteredEchoesMod>(ctx, a);
         case ZCU_MOD_CYCLE: return b0 ? launch<CycleMod<true>>(ctx, a) : launch<CycleMod<false>>(ctx, a);
         default: return zcu_fail(ctx, ZCU_ERR_INVALID, "unknown module kind %d", pl.kind);
     }

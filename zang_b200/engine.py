@@ -398,6 +398,81 @@ class Cycle(_Module):
         _check(self.ctx, lib.zcu_paint_cycle(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(speed)))
 
 
+class DelayBank(Bank):
+    """zang.Delay(delay_samples).init() for every voice (src/zang/delay.zig:7-17): index POD + a zeroed delay line per voice."""
+
+    def __init__(self, ctx, kind, voices, delay_samples):
+        self.ctx, self.kind, self.voices, self.delay_samples = ctx, kind, int(voices), int(delay_samples)
+        h = C.c_void_p()
+        _check(ctx, lib.zcu_delay_bank_create(ctx._h, kind, self.voices, self.delay_samples, C.byref(h)))
+        self._h = h
+
+    def get_delay_line(self):
+        out = np.zeros((self.delay_samples, self.voices), dtype=np.float32)
+        _check(self.ctx, lib.zcu_bank_get_delay_line(self.ctx._h, self._h, ptr(out), out.nbytes))
+        return out
+
+    def set_delay_line(self, line):
+        line = np.ascontiguousarray(line, dtype=np.float32)
+        _check(self.ctx, lib.zcu_bank_set_delay_line(self.ctx._h, self._h, ptr(line), line.nbytes))
+
+
+class SimpleDelay:
+    """examples/modules.zig:341-388: Params = {input}; outputs[0] += input delayed by delay_samples painted frames."""
+    kind = L.MOD_SIMPLE_DELAY
+    num_outputs = 1
+    num_temps = 0
+
+    def __init__(self, ctx, voices, delay_samples):
+        self.ctx, self.voices = ctx, voices
+        self.bank = DelayBank(ctx, self.kind, voices, delay_samples)
+
+    def paint(self, spans, outputs, temps, input):
+        _check(self.ctx, lib.zcu_paint_simple_delay(self.ctx._h, self.bank._h, spans._h, outputs[0]._h, _h(input)))
+
+
+class FilteredEchoes:
+    """examples/modules.zig:392-460: Params = {input, feedback_volume, cutoff}.  The reference's two temps are not needed."""
+    kind = L.MOD_FILTERED_ECHOES
+    num_outputs = 1
+    num_temps = 0
+    Params = L.param_dtypes[L.MOD_FILTERED_ECHOES]
+
+    def __init__(self, ctx, voices, delay_samples):
+        self.ctx, self.voices = ctx, voices
+        self.bank = DelayBank(ctx, self.kind, voices, delay_samples)
+
+    def paint(self, spans, outputs, temps, params, input):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_filtered_echoes(self.ctx._h, self.bank._h, spans._h, ptr(p), p.size, outputs[0]._h, _h(input)))
+
+
+class StereoEchoes:
+    """examples/modules.zig:462-525 composed from the C-ABI calls, line by line: outputs = [left, right], temps = 2 buffers
+    (the reference needs 4: two of them are FilteredEchoes' internal temps, which the device module keeps in registers)."""
+    num_outputs = 2
+    num_temps = 2
+    Params = L.param_dtypes[L.MOD_FILTERED_ECHOES]
+
+    def __init__(self, ctx, voices, main_delay):
+        self.ctx = ctx
+        half = int(main_delay) // 2  # :463
+        self.delay0 = SimpleDelay(ctx, voices, half)
+        self.delay1 = SimpleDelay(ctx, voices, half)
+        self.echoes = FilteredEchoes(ctx, voices, int(main_delay))
+
+    def paint(self, spans, outputs, temps, params, input):
+        ctx = self.ctx
+        ctx.addInto(spans, outputs[0], input)                                   # :497
+        ctx.addInto(spans, outputs[1], input)                                   # :498
+        ctx.zero(spans, temps[0])                                               # :501
+        self.delay0.paint(spans, [temps[0]], [], input)                         # :502-504
+        ctx.zero(spans, temps[1])                                               # :506
+        self.echoes.paint(spans, [temps[1]], [], params, input=temps[0])        # :507-511
+        ctx.addInto(spans, outputs[0], temps[1])                                # :513
+        self.delay1.paint(spans, [outputs[1]], [], temps[1])                    # :514-516
+
+
 MODULE_CLASSES = {c.kind: c for c in (SineOsc, PulseOsc, TriSawOsc, Noise, Envelope, Gate, Filter, Portamento, Curve, Sampler,
                                       Decimator, Distortion, Cycle)}
 
