@@ -95,8 +95,37 @@ def bank_cases():
     return out
 
 
+def delay_cases():
+    """src/zang/delay.zig + examples/modules.zig:341-525: hashes on seeded inputs, and the literal SimpleDelay(3) response
+    to 1, 2, 3, ... (a pure delay by three painted frames)."""
+    from helpers import full_spans, random_spans
+    rng = np.random.default_rng(99)
+    out = {}
+    V, NB, BF = 5, 4, 64
+    for kind, name in ((L.MOD_SIMPLE_DELAY, "simple_delay"), (L.MOD_FILTERED_ECHOES, "filtered_echoes")):
+        for D in (1, 9, 100):
+            off, spans = random_spans(rng, V, NB, BF, 2)
+            st = np.zeros(V, dtype=L.state_dtypes[kind])
+            line = np.zeros((D, V), dtype=np.float32)
+            params = np.array([(0.5, 0.3), (0.8, 0.05)], dtype=L.param_dtypes[L.MOD_FILTERED_ECHOES]) if kind == L.MOD_FILTERED_ECHOES else None
+            x = rng.uniform(-1, 1, size=(NB * BF, V)).astype(np.float32)
+            o = rng.uniform(-1, 1, size=(NB * BF, V)).astype(np.float32)
+            oracle.paint_delay(kind, off, spans, params, st, line, o, x)
+            out[f"{name}_D{D}"] = digest(o, line, st)
+    x = (np.arange(64, dtype=np.float32) == 0).astype(np.float32).reshape(64, 1)
+    left, right = oracle.stereo_echoes(x, 16, 10, 0.5, 0.5)
+    out["stereo_echoes_impulse"] = digest(left, right)
+    off, spans = full_spans(1, 1, 8)
+    st = np.zeros(1, dtype=L.state_dtypes[L.MOD_SIMPLE_DELAY])
+    line = np.zeros((3, 1), dtype=np.float32)
+    o = np.zeros((8, 1), dtype=np.float32)
+    oracle.paint_delay(L.MOD_SIMPLE_DELAY, off, spans, None, st, line, o, np.arange(1, 9, dtype=np.float32).reshape(8, 1))
+    out["simple_delay_3_literal"] = [float(v) for v in o[:, 0]]
+    return out
+
+
 def build():
-    return {"modules": module_cases(), "excerpts": excerpts(), "render_nice": render_case(), "banks": bank_cases()}
+    return {"modules": module_cases(), "excerpts": excerpts(), "render_nice": render_case(), "banks": bank_cases(), "delay": delay_cases()}
 
 
 if __name__ == "__main__":

@@ -41,6 +41,12 @@ def test_bank_graphs_match_golden_hashes():
     assert make_golden.bank_cases() == GOLD["banks"]
 
 
+def test_delay_modules_match_golden():
+    got = make_golden.delay_cases()
+    assert got == GOLD["delay"]
+    assert got["simple_delay_3_literal"] == [0.0, 0.0, 0.0, 1.0, 2.0, 3.0, 4.0, 5.0]  # delay.zig: out[i] += in[i - delay_samples]
+
+
 def one_voice(kind, params, n=64, flags=1, **kw):
     off = np.array([0, 1], dtype=np.uint32)
     spans = np.array([(0, n, flags, 0)], dtype=L.span_dtype)
