@@ -171,6 +171,12 @@ uint64_t zcu_ctx_launch_count(zcu_ctx* ctx); /* kernels launched by this library
 enum { ZCU_PAINT_EXACT = 0, ZCU_PAINT_TOLERANCE = 1 };
 int zcu_ctx_set_paint_mode(zcu_ctx* ctx, int mode);
 int zcu_ctx_paint_mode(const zcu_ctx* ctx);
+/* Noise (src/modules/Noise.zig) is painted in time segments that start from an exact jump of the xoshiro256++ state by the
+ * number of samples painted before the segment.  Zig's Random.float(f32) draws a second u64 with probability 2^-41 per
+ * sample; a jump cannot foresee that, and the voice's later segments of that one call are then one draw behind the
+ * sequential loop.  This counter (since context creation; synchronises the stream) tells how often it happened: 0 means
+ * every Noise paint so far is bit-identical to the reference loop.  Expected once per 2.2e12 noise samples. */
+int zcu_ctx_noise_resync_count(zcu_ctx* ctx, uint64_t* out);
 
 /* device-side timing (CUDA events on the context stream) */
 int zcu_timer_start(zcu_ctx* ctx);

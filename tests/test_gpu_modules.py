@@ -186,3 +186,28 @@ def test_paint_argument_errors(ctx):
     bad = np.array([(10, 5, 0, 0)], dtype=L.span_dtype)
     h = C.c_void_p()
     assert lib.zcu_spans_upload(ctx._h, 4, 64, ptr(off), ptr(bad), C.byref(h)) == L.ERR_INVALID
+
+
+@pytest.mark.parametrize("color", [L.NOISE_WHITE, L.NOISE_PINK], ids=["white", "pink"])
+def test_noise_time_segments_bit_exact(ctx, color):
+    """Noise is painted in time segments that start from an exact GF(2) jump of the xoshiro256++ state (zcu_paint.cu:
+    ensure_xjump): a long block, random spans with gaps (every voice has its own number of draws before a segment) and spans
+    straddling segment starts (pink mode replays the 7-tap filter from the span start) must reproduce the sequential loop."""
+    Vn, NB, bf = 70, 96, 1024
+    frames = NB * bf
+    rng = np.random.default_rng(123 + color)
+    off, spans = random_spans(rng, Vn, NB, bf, 1, max_cuts=2, p_empty=0.2, p_gap=0.3)
+    params = np.array([(color,)], dtype=L.param_dtypes[L.MOD_NOISE])
+    mod = E.Noise(ctx, Vn, first_seed=1000)
+    ostate = oracle.state_init(L.MOD_NOISE, Vn, first_seed=1000)
+    out0 = rng.uniform(-1, 1, size=(frames, Vn)).astype(np.float32)
+    want = out0.copy()
+    oracle.paint(L.MOD_NOISE, off, spans, params, ostate, want)
+    d_out = ctx.buf(frames, Vn, out0)
+    sp = ctx.spans(Vn, frames, off, spans)
+    mod.paint(sp, [d_out], [], params)
+    assert_bit_exact(d_out.download(), want, "noise in time segments")
+    assert state_equal(mod.bank.get_state(), ostate)
+    assert ctx.noise_resync_count() == 0
+    d_out.free()
+    sp.free()

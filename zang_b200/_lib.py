@@ -130,6 +130,7 @@ PROTOTYPES = {
     "zcu_ctx_launch_count": (_U64, [_P]),
     "zcu_ctx_set_paint_mode": (_I, [_P, _I]),
     "zcu_ctx_paint_mode": (_I, [_P]),
+    "zcu_ctx_noise_resync_count": (_I, [_P, _P]),
     "zcu_timer_start": (_I, [_P]),
     "zcu_timer_stop_ms": (_I, [_P, _P]),
     "zcu_buf_alloc": (_I, [_P, _U, _U, _P]),

@@ -89,6 +89,8 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 4; i++)
         if (ctx->arena[i]) cudaFree(ctx->arena[i]);
+    if (ctx->xjump) cudaFree(ctx->xjump);
+    if (ctx->xjump_resync) cudaFree(ctx->xjump_resync);
     if (ctx->chain) cudaFree(ctx->chain);
     if (ctx->chain_flags) cudaFree(ctx->chain_flags);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -112,6 +114,16 @@ int zcu_ctx_set_paint_mode(zcu_ctx* ctx, int mode) {
     return ZCU_OK;
 }
 int zcu_ctx_paint_mode(const zcu_ctx* ctx) { return ctx ? ctx->paint_mode : ZCU_PAINT_EXACT; }
+int zcu_ctx_noise_resync_count(zcu_ctx* ctx, uint64_t* out) {
+    if (!ctx || !out) return ZCU_ERR_INVALID;
+    *out = 0;
+    if (!ctx->xjump_resync) return ZCU_OK;
+    unsigned long long h = 0;
+    ZCU_CUDA(ctx, cudaMemcpyAsync(&h, ctx->xjump_resync, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *out = h;
+    return ZCU_OK;
+}
 
 int zcu_timer_start(zcu_ctx* ctx) {
     if (!ctx) return ZCU_ERR_INVALID;

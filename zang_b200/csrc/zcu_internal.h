@@ -27,6 +27,9 @@ struct zcu_ctx {
     uint32_t* chain_flags = nullptr;
     size_t chain_flag_count = 0;
     uint32_t paint_epoch = 0;
+    // Noise skip-ahead: xoshiro256 jump matrices (built on first use) and the device counter of unforeseeable extra draws
+    void* xjump = nullptr;
+    unsigned long long* xjump_resync = nullptr;
     // NCCL (loaded lazily with dlopen)
     void* nccl_comm = nullptr;
     int nccl_rank = 0, nccl_nranks = 1;

@@ -1,6 +1,8 @@
 // zcu_paint.cu — instantiation and launch of the lockstep paint kernel for every module variant.
 #include <algorithm>
 #include <cstdlib>
+#include <type_traits>
+#include <vector>
 
 #include "zcu_internal.h"
 #include "zcu_paint_kernel.cuh"
@@ -32,6 +34,55 @@ int ensure_chain(zcu_ctx* ctx, size_t states, size_t flags) {
     return ZCU_OK;
 }
 
+// ---- xoshiro256 jump matrices for the Noise skip-ahead ------------------------------------------------------------
+// State transition of xoshiro256 (the "++" only scrambles the output), linear over GF(2).  A matrix is stored by columns:
+// column j = image of the state with only bit j set, 4 x u64.
+struct XMat { uint64_t c[256][4]; };
+void xo_step(uint64_t s[4]) {
+    const uint64_t t = s[1] << 17;
+    s[2] ^= s[0];
+    s[3] ^= s[1];
+    s[1] ^= s[2];
+    s[0] ^= s[3];
+    s[2] ^= t;
+    s[3] = (s[3] << 45) | (s[3] >> 19);
+}
+void xm_apply(const XMat& m, const uint64_t x[4], uint64_t y[4]) {
+    uint64_t o[4] = {0, 0, 0, 0};
+    for (int j = 0; j < 256; j++)
+        if ((x[j >> 6] >> (j & 63)) & 1)
+            for (int q = 0; q < 4; q++) o[q] ^= m.c[j][q];
+    for (int q = 0; q < 4; q++) y[q] = o[q];
+}
+void xm_mul(const XMat& a, const XMat& b, XMat& out) {  // out = a * b (b first)
+    for (int j = 0; j < 256; j++) xm_apply(a, b.c[j], out.c[j]);
+}
+int ensure_xjump(zcu_ctx* ctx) {
+    if (ctx->xjump) return ZCU_OK;
+    constexpr int LEVELS = 6, DIGITS = 15;
+    std::vector<XMat> tab((size_t)LEVELS * DIGITS);
+    XMat p;  // T^(16^k)
+    for (int j = 0; j < 256; j++) {
+        uint64_t e[4] = {0, 0, 0, 0};
+        e[j >> 6] = 1ull << (j & 63);
+        xo_step(e);
+        for (int q = 0; q < 4; q++) p.c[j][q] = e[q];
+    }
+    for (int k = 0; k < LEVELS; k++) {
+        tab[(size_t)k * DIGITS] = p;
+        for (int d = 2; d <= DIGITS; d++) xm_mul(p, tab[(size_t)k * DIGITS + d - 2], tab[(size_t)k * DIGITS + d - 1]);
+        XMat next;
+        xm_mul(p, tab[(size_t)k * DIGITS + DIGITS - 1], next);
+        p = next;
+    }
+    ZCU_CUDA(ctx, cudaMalloc(&ctx->xjump, tab.size() * sizeof(XMat)));
+    ZCU_CUDA(ctx, cudaMemcpyAsync(ctx->xjump, tab.data(), tab.size() * sizeof(XMat), cudaMemcpyHostToDevice, ctx->stream));
+    ZCU_CUDA(ctx, cudaMalloc((void**)&ctx->xjump_resync, sizeof(unsigned long long)));
+    ZCU_CUDA(ctx, cudaMemsetAsync(ctx->xjump_resync, 0, sizeof(unsigned long long), ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // tab is a host temporary
+    return ZCU_OK;
+}
+
 bool overlaps(const float* a, const float* b, size_t n) { return a && b && a < b + n && b < a + n; }
 
 template <class M>
@@ -45,7 +96,18 @@ int launch(zcu_ctx* ctx, PaintArgs a) {
     const size_t n = (size_t)a.V * a.frames;
     const bool warm = WarmOf<M>::value && ctx->paint_mode == ZCU_PAINT_TOLERANCE && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
                       !overlaps(a.out, a.in2, n);
-    PaintPlan p = zcu_paint_plan(ctx, a, nb, M::SKIP || warm);
+    bool skip = M::SKIP;
+    if (std::is_same<M, NoiseMod>::value) {
+        // jumps are tabulated for fewer than 16^6 painted samples per call; longer blocks walk the frames in one segment
+        skip = a.frames < (1u << 24);
+        if (skip) {
+            int rc = ensure_xjump(ctx);
+            if (rc) return rc;
+        }
+        a.xjump = skip ? (const ulonglong2*)ctx->xjump : nullptr;
+        a.xjump_resync = skip ? ctx->xjump_resync : nullptr;
+    }
+    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm);
     a.chain = nullptr;
     a.chain_flags = nullptr;
     a.epoch = 0;
@@ -57,7 +119,7 @@ int launch(zcu_ctx* ctx, PaintArgs a) {
         a.chain_flags = ctx->chain_flags;
         a.epoch = ++ctx->paint_epoch;
         a.warm_cap = (uint32_t)std::min<uint64_t>(a.frames, 8ull * p.seg_frames);  // a window longer than this: chain instead
-    } else if (!M::SKIP) {
+    } else if (!skip) {
         p.nseg = 1;
         p.seg_frames = a.frames;
     }
@@ -120,6 +182,8 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     a.smp.format = pl.smp_format;
     a.line = pl.line;
     a.delay_samples = pl.delay_samples;
+    a.xjump = nullptr;
+    a.xjump_resync = nullptr;
     if (a.V == 0 || a.frames == 0) return ZCU_OK;
     const bool b0 = pl.in0 != nullptr, b1 = pl.in1 != nullptr, b2 = pl.in2 != nullptr;
     switch (pl.kind) {

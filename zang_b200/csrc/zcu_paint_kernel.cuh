@@ -41,6 +41,12 @@ struct WarmCall { static __device__ __forceinline__ void sample(M&, float, float
 template <class M>
 struct WarmCall<M, true> { static __device__ __forceinline__ void sample(M& m, float x0, float x1, float x2) { m.sample_warm(x0, x1, x2); } };
 
+// m.advance_done() for modules whose advance() only accumulates (M::LAZY)
+template <class M, class = void>
+struct LazyCall { static __device__ __forceinline__ void done(M&) {} };
+template <class M>
+struct LazyCall<M, std::enable_if_t<M::LAZY>> { static __device__ __forceinline__ void done(M& m) { m.advance_done(); } };
+
 constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
 constexpr int kPaintStages = 3;   // tiles in the cp.async ring
 
@@ -211,6 +217,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             m.advance(a, v, s_start, f_begin - s_start);
             active = true;
         }
+        LazyCall<M>::done(m);
     }
 
     // one tile of the ring: wait, refill, walk the frames in runs, write the output tile back.  WT = warm-up tile (tolerance

@@ -61,6 +61,11 @@ class Context:
     def paint_mode(self):
         return int(lib.zcu_ctx_paint_mode(self._h))
 
+    def noise_resync_count(self):
+        n = C.c_uint64()
+        _check(self, lib.zcu_ctx_noise_resync_count(self._h, C.byref(n)))
+        return int(n.value)
+
     def timer_start(self):
         _check(self, lib.zcu_timer_start(self._h))
 
