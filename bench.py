@@ -335,6 +335,38 @@ def main():
                              "render_mode": MODE_INFO[m][2]}
                 r2.free()
             line["other_modes"] = others
+            # The same bank through the DROP-IN module path: the reference's paint body call by call (zero, PulseOsc,
+            # multiplyWithScalar, zero, Filter, zero, Envelope, multiply = 8 C-ABI calls per block over all voices,
+            # examples/modules.zig:220-246), temps in HBM, on the first 64 mix buffers of the job.  This is the HBM-bound form of
+            # the workload: 64 algorithmic bytes per voice-sample against the measured copy peak.
+            try:
+                from zang_b200.events import BankTrigger
+                from zang_b200 import engine as E
+                bf = 64 * BUFFER_FRAMES
+                nb = E.NiceInstrumentBank(ctx, V, 0.3)
+                soff, sspans = BankTrigger(wl["event_off"], wl["events"], total_frames, BUFFER_FRAMES).spans(0, bf)
+                sp = ctx.spans(V, bf, soff, sspans)
+                rows = np.zeros(wl["events"].size, dtype=E.NiceInstrumentBank.Params)
+                rows["sample_rate"], rows["freq"], rows["note_on"] = SAMPLE_RATE, wl["events"]["freq"], wl["events"]["note_on"]
+                bufs = [ctx.buf(bf, V) for _ in range(3)]
+                dp = {}
+                for pm, pname in ((L.PAINT_TOLERANCE, "tolerance"), (L.PAINT_EXACT, "exact")):
+                    ctx.set_paint_mode(pm)
+
+                    def step_dropin():
+                        nb.paint(sp, [bufs[0]], bufs[1:], rows)
+                    step_dropin()
+                    ms_d = timed(step_dropin, 3)
+                    ms_avg = sum(ms_d) / len(ms_d)
+                    gbs = V * bf * 64 / (ms_avg * 1e-3) / 1e9
+                    dp[pname] = {"ms_per_block": ms_avg, "value": V * bf / (ms_avg * 1e-3), "algorithmic_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+                ctx.set_paint_mode(L.PAINT_EXACT)
+                line["dropin_module_path"] = {"block_frames": bf, "calls_per_block": 8, "bytes_per_voice_sample": 64, "paint_modes": dp,
+                                              "note": "tolerance = Filter in device-verified time segments (<= 1e-5), everything else bit-exact; exact = every module bit-exact"}
+                for b in bufs + [sp]:
+                    b.free()
+            except Exception as e:  # the headline number must not depend on the comparison leg
+                line["dropin_module_path"] = {"error": repr(e)}
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_reference_run(1, 0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}

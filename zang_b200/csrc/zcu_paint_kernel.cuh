@@ -34,6 +34,12 @@ struct WarmOf { static constexpr bool value = false; };
 template <class M>
 struct WarmOf<M, std::void_t<decltype(M::WARM)>> { static constexpr bool value = M::WARM; };
 
+// M::WRITE_ONLY: the module overwrites its output without reading it (zero / set / copy): the output tile is not loaded
+template <class M, class = void>
+struct WriteOnlyOf { static constexpr bool value = false; };
+template <class M>
+struct WriteOnlyOf<M, std::void_t<decltype(M::WRITE_ONLY)>> { static constexpr bool value = M::WRITE_ONLY; };
+
 // m.sample_warm() for modules that have it (the call sits in a generic lambda, where a plain member call would be looked up
 // for every module)
 template <class M, bool = WarmOf<M>::value>
@@ -73,6 +79,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
 
     // this CTA's segment of the frame axis (seg_frames is a multiple of T)
     constexpr bool kWarm = WarmOf<M>::value;
+    constexpr bool kWriteOnly = WriteOnlyOf<M>::value;
     const bool warm = kWarm && a.chain != nullptr;  // tolerance mode: segments start from a verified warm-up or the chain
     const bool segmented = M::SKIP || warm;
     const uint32_t f_begin = segmented ? blockIdx.y * seg_frames : 0u;
@@ -101,7 +108,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         const uint32_t stage = tile % S;
         if (c_valid) {
             // warm-up tiles (before the segment) only read the inputs: the output rows there belong to the previous segment
-            if (!(kWarm && f0 < f_begin)) copy_rows(a.out, i_out, stage, f0, n);
+            if (!kWriteOnly && !(kWarm && f0 < f_begin)) copy_rows(a.out, i_out, stage, f0, n);
             if (M::NIN >= 1 && i_in0 >= 0) copy_rows(a.in0, i_in0, stage, f0, n);
             if (M::NIN >= 2 && i_in1 >= 0) copy_rows(a.in1, i_in1, stage, f0, n);
             if (M::NIN >= 3 && i_in2 >= 0) copy_rows(a.in2, i_in2, stage, f0, n);
@@ -235,6 +242,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         const float* s1_t = i_in1 >= 0 ? tile_ptr(stage, i_in1) + tid : so_t;
         const float* s2_t = i_in2 >= 0 ? tile_ptr(stage, i_in2) + tid : so_t;
         int painted = 0;
+        uint32_t painted_mask = 0;  // kWriteOnly: the frames of this tile (T <= 16) this voice painted
         // Frames are walked in runs: up to the nearest span boundary of any of the warp's voices (one warp reduction per
         // run), so that the per-frame code carries no span bookkeeping and can be unrolled.
         uint32_t j = 0;
@@ -272,9 +280,10 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                     }
                 } else {
                     painted = 1;
+                    if (kWriteOnly) painted_mask |= ((1u << run) - 1u) << j;
 #pragma unroll 4
                     for (uint32_t r = 0; r < run; r++) {
-                        float acc = so[r * RV];
+                        float acc = kWriteOnly ? 0.0f : so[r * RV];
                         const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
                         const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
                         const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
@@ -284,6 +293,29 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 }
             }
             j += run;
+        }
+        if constexpr (kWriteOnly) {
+            // the tile holds only what was painted: full rows when every voice of the CTA painted every frame of the tile,
+            // otherwise every voice stores its own frames (one coalesced 128-byte row piece per warp and frame)
+            const bool full = !valid || painted_mask == (n >= 32 ? 0xFFFFFFFFu : (1u << n) - 1u);
+            if (__syncthreads_and(full)) {
+                if (c_valid) {
+                    float* dstg = a.out + (size_t)f0 * V + v0 + c;
+                    const float* st = tile_ptr(stage, i_out) + c;
+                    if (vec4) {
+                        for (uint32_t jj = r0; jj < n; jj += rpp) *reinterpret_cast<float4*>(dstg + (size_t)jj * V) = *reinterpret_cast<const float4*>(st + jj * RV);
+                    } else {
+                        for (uint32_t jj = r0; jj < n; jj += rpp) dstg[(size_t)jj * V] = st[jj * RV];
+                    }
+                }
+            } else if (valid) {
+                float* dstv = a.out + (size_t)f0 * V + v;
+                for (uint32_t mk = painted_mask; mk != 0; mk &= mk - 1) {
+                    const uint32_t jj = __ffs(mk) - 1;
+                    dstv[(size_t)jj * V] = so_t[jj * RV];
+                }
+            }
+            return;
         }
         // the finished output tile goes back to HBM as full rows (skipped when nobody in the CTA painted in it)
         if (__syncthreads_or(painted) && c_valid) {
