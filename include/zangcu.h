@@ -161,6 +161,11 @@ const char* zcu_last_error(zcu_ctx* ctx); /* never NULL */
 void* zcu_ctx_stream(zcu_ctx* ctx);       /* the cudaStream_t every call is enqueued on */
 uint64_t zcu_ctx_launch_count(zcu_ctx* ctx); /* kernels launched by this library on this ctx so far */
 
+/* Diagnostic: the branch-free division by a span constant used by the buffer-frequency TriSawOsc (freq[i] / sample_rate,
+ * TriSawOsc.zig:152) against the IEEE quotient, for EVERY f32 numerator.  mismatches must be 0; claimed = numerators for
+ * which the fast sequence is used (the rest take the real division). */
+int zcu_selftest_div_by_const(zcu_ctx* ctx, float divisor, uint64_t* mismatches, uint64_t* claimed);
+
 /* Arithmetic mode of the module paints (zcu_paint_*).
  * ZCU_PAINT_EXACT (default): every module walks each voice's frames in the reference's order; all state-carrying
  *   modules are bit-identical to the sequential paint() loops.

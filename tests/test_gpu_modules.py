@@ -211,3 +211,16 @@ def test_noise_time_segments_bit_exact(ctx, color):
     assert ctx.noise_resync_count() == 0
     d_out.free()
     sp.free()
+
+
+@pytest.mark.parametrize("sr", [48000.0, 44100.0, 96000.0, 22050.0, 8000.0, 192000.0, 44099.99609375])
+def test_div_by_constant_is_exact(ctx, sr):
+    """freq[i] / sample_rate (TriSawOsc.zig:152) is evaluated without the branch of the IEEE division sequence; the result must
+    be the IEEE quotient for every f32 numerator the fast sequence accepts (all 2^32 bit patterns are swept on the device)."""
+    import ctypes as C
+    from zang_b200._lib import lib
+    bad, claimed = C.c_uint64(), C.c_uint64()
+    rc = lib.zcu_selftest_div_by_const(ctx._h, C.c_float(sr), C.byref(bad), C.byref(claimed))
+    assert rc == 0
+    assert bad.value == 0, f"{bad.value} of {claimed.value} quotients differ from x / {sr}"
+    assert claimed.value > 3.3e9  # every finite numerator with a quotient in [1e-30, 1e30] takes the fast sequence

@@ -76,6 +76,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "bank_bench.json"))
     ap.add_argument("--scale", type=float, default=1.0, help="scale the voice counts (smoke runs)")
+    ap.add_argument("--only", default="", help="comma list of config numbers to run (1,2,3,4)")
     ap.add_argument("--exact", action="store_true", help="ZCU_PAINT_EXACT (default here: ZCU_PAINT_TOLERANCE, Filter in verified time segments)")
     args = ap.parse_args()
     peak = 6553.0
@@ -87,29 +88,34 @@ def main():
     ctx.set_paint_mode(L.PAINT_EXACT if args.exact else L.PAINT_TOLERANCE)
     res = []
     sc = args.scale
+    only = set(int(x) for x in args.only.split(",")) if args.only else {1, 2, 3, 4}
     # configs[1] polyphony bank, un-fused: 4096 voices, 64 mix buffers
     V, frames = int(4096 * sc), 64 * 1024
-    wl = synth.polyphony_bank(V, frames, 48000.0)
-    res.append(run(ctx, "configs[1] NiceInstrument (un-fused)", NiceBankAdapter(ctx, wl, 48000.0, frames), frames, 2, 64, peak))
+    if 1 in only:
+        wl = synth.polyphony_bank(V, frames, 48000.0)
+        res.append(run(ctx, "configs[1] NiceInstrument (un-fused)", NiceBankAdapter(ctx, wl, 48000.0, frames), frames, 2, 64, peak))
     # configs[2] fm/detuned: 16384 voices, 16 mix buffers
     V, frames = int(16384 * sc), 16 * 1024
-    wl = synth.fm_bank(V, frames, 48000.0)
-    det, idx = synth.fm_mod_inputs(V, frames)
-    ins = (ctx.buf(frames, V, det), ctx.buf(frames, V, idx))
-    del det, idx
-    res.append(run(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 6, 140, peak, ins=ins))
-    for b in ins:
-        b.free()
+    if 2 in only:
+        wl = synth.fm_bank(V, frames, 48000.0)
+        det, idx = synth.fm_mod_inputs(V, frames)
+        ins = (ctx.buf(frames, V, det), ctx.buf(frames, V, idx))
+        del det, idx
+        res.append(run(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 6, 140, peak, ins=ins))
+        for b in ins:
+            b.free()
     # configs[3] sampler: 2048 voices, 64 mix buffers @44.1 kHz
     V, frames = int(2048 * sc), 64 * 1024
-    wl = synth.sampler_bank(V, frames, 44100.0)
-    pcm = synth.pcm_loop()
-    smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
-    res.append(run(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 2, 48, peak))
+    if 3 in only:
+        wl = synth.sampler_bank(V, frames, 44100.0)
+        pcm = synth.pcm_loop()
+        smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
+        res.append(run(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 2, 48, peak))
     # configs[4] SFX batch: 65536 jobs x 24 mix buffers
     V, frames = int(65536 * sc), 24 * 1024
-    wl = synth.sfx_bank(V, frames)
-    res.append(run(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 3, 100, peak))
+    if 4 in only:
+        wl = synth.sfx_bank(V, frames)
+        res.append(run(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 3, 100, peak))
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(dict(peak_gbs=peak, paint_mode="exact" if args.exact else "tolerance", results=res), open(args.out, "w"), indent=1)
     ctx.close()

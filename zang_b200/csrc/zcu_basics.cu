@@ -93,7 +93,7 @@ int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a,
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
         attr_set = true;
     }
-    k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(pa, p.T, p.seg_frames, p.vec4);
+    k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(pa, p.T, p.seg_frames, p.vec4, p.stages);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;
@@ -276,6 +276,23 @@ __global__ void k_bank_init(int kind, void* state, uint32_t V, uint32_t first_se
     }
 }
 
+// every f32 numerator against one divisor: div_by_const (zcu_modules.cuh) must equal the IEEE quotient wherever it claims to
+__global__ void k_div_probe(float d, unsigned long long* mismatches, unsigned long long* claimed) {
+    const float rd = 1.0f / d;
+    unsigned long long bad = 0, ok_n = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < (1ull << 32); i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float x = __uint_as_float((uint32_t)i);
+        if (!(fabsf(x) <= 3.0e38f)) continue;  // NaN / inf
+        bool ok = true;
+        const float q = div_by_const(x, d, rd, ok);
+        if (!ok) continue;
+        ok_n++;
+        if (__float_as_uint(q) != __float_as_uint(x / d)) bad++;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+    atomicAdd(claimed, ok_n);
+}
+
 // a*b+c with operands chosen so that a fused multiply-add gives a different f32 than mul-then-add
 __global__ void k_fma_probe(float a, float b, float c, float* out) { out[0] = a * b + c; }
 
@@ -316,6 +333,22 @@ int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed) {
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     if (bank->line) ZCU_CUDA(ctx, cudaMemsetAsync(bank->line, 0, (size_t)bank->delay_samples * bank->voices * sizeof(float), ctx->stream));
+    return ZCU_OK;
+}
+
+extern "C" int zcu_selftest_div_by_const(zcu_ctx* ctx, float divisor, uint64_t* mismatches, uint64_t* claimed) {
+    if (!ctx || !mismatches || !claimed) return ZCU_ERR_INVALID;
+    unsigned long long* d = nullptr;
+    int rc = zcu_arena_reserve(ctx, 0, 2 * sizeof(unsigned long long), (void**)&d);
+    if (rc) return rc;
+    ZCU_CUDA(ctx, cudaMemsetAsync(d, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    k_div_probe<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(divisor, d, d + 1);
+    ctx->launches++;
+    unsigned long long h[2] = {0, 0};
+    ZCU_CUDA(ctx, cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *mismatches = h[0];
+    *claimed = h[1];
     return ZCU_OK;
 }
 

@@ -128,7 +128,7 @@ int launch(zcu_ctx* ctx, PaintArgs a) {
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
         attr_set = true;
     }
-    k_paint_lockstep<M><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4);
+    k_paint_lockstep<M><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4, p.stages);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;

@@ -23,6 +23,8 @@
 
 #include <cuda_pipeline.h>
 
+#include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 
 #include "zcu_modules.cuh"
@@ -47,19 +49,48 @@ struct WarmCall { static __device__ __forceinline__ void sample(M&, float, float
 template <class M>
 struct WarmCall<M, true> { static __device__ __forceinline__ void sample(M& m, float x0, float x1, float x2) { m.sample_warm(x0, x1, x2); } };
 
+// four consecutive samples at once for modules that provide sample4() (same results as four sample() calls, arranged so
+// that the independent parts of the four evaluations can overlap); everything else gets the plain sequence
+template <class M, class = void>
+struct Sample4 {
+    static __device__ __forceinline__ void call(M& m, float (&acc)[4], const float (&x0)[4], const float (&x1)[4], const float (&x2)[4]) {
+#pragma unroll
+        for (int q = 0; q < 4; q++) m.sample(acc[q], x0[q], x1[q], x2[q]);
+    }
+};
+template <class M>
+struct Sample4<M, std::enable_if_t<M::HAS_SAMPLE4>> {
+    static __device__ __forceinline__ void call(M& m, float (&acc)[4], const float (&x0)[4], const float (&x1)[4], const float (&x2)[4]) {
+        m.sample4(acc, x0, x1, x2);
+    }
+};
+
 // m.advance_done() for modules whose advance() only accumulates (M::LAZY)
 template <class M, class = void>
 struct LazyCall { static __device__ __forceinline__ void done(M&) {} };
 template <class M>
 struct LazyCall<M, std::enable_if_t<M::LAZY>> { static __device__ __forceinline__ void done(M& m) { m.advance_done(); } };
 
+// cp.async.wait_group takes an immediate: dispatch the ring depths in use
+__device__ __forceinline__ void pipeline_wait_prior_rt(uint32_t n) {
+    switch (n) {
+        case 0: __pipeline_wait_prior(0); break;
+        case 1: __pipeline_wait_prior(1); break;
+        case 2: __pipeline_wait_prior(2); break;
+        case 3: __pipeline_wait_prior(3); break;
+        case 4: __pipeline_wait_prior(4); break;
+        case 5: __pipeline_wait_prior(5); break;
+        default: __pipeline_wait_prior(6); break;
+    }
+}
+
 constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
 constexpr int kPaintStages = 3;   // tiles in the cp.async ring
 
 template <class M>
-__global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames, uint32_t vec4) {
+__global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames, uint32_t vec4, uint32_t S) {
     extern __shared__ __align__(16) float smem[];
-    constexpr uint32_t W = kPaintWarps, S = kPaintStages, RV = 32 * W;
+    constexpr uint32_t W = kPaintWarps, RV = 32 * W;  // S = tiles in the cp.async ring (3..8: deeper when few CTAs share an SM)
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t v0 = blockIdx.x * RV;
     const uint32_t v = v0 + tid;
@@ -231,7 +262,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     // mode, before the segment): the module only advances its state, nothing is read from or written to the output.
     auto do_tile = [&](uint32_t tile, auto wt_tag) {
         constexpr bool WT = decltype(wt_tag)::value;
-        __pipeline_wait_prior(S - 2);
+        pipeline_wait_prior_rt(S - 2);
         __syncthreads();  // tile `tile` has landed for every thread; every thread is done with the stage refilled next
         if (tile + S - 1 < ntiles) issue(tile + S - 1); else __pipeline_commit();
         const uint32_t f0 = tile * T;
@@ -281,8 +312,24 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 } else {
                     painted = 1;
                     if (kWriteOnly) painted_mask |= ((1u << run) - 1u) << j;
-#pragma unroll 4
-                    for (uint32_t r = 0; r < run; r++) {
+                    // batches of 4 frames: all operands are read before the first result is written, so the shared-memory
+                    // loads of a batch overlap instead of queueing behind the previous sample's store (the compiler cannot
+                    // know that the tiles do not alias); the module still sees the samples one by one, in order
+                    uint32_t r = 0;
+                    for (; r + 4 <= run; r += 4) {
+                        float acc[4], x0[4], x1[4], x2[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            acc[q] = kWriteOnly ? 0.0f : so[(r + q) * RV];
+                            x0[q] = i_in0 >= 0 ? s0[(r + q) * RV] : 0.0f;
+                            x1[q] = i_in1 >= 0 ? s1[(r + q) * RV] : 0.0f;
+                            x2[q] = i_in2 >= 0 ? s2[(r + q) * RV] : 0.0f;
+                        }
+                        Sample4<M>::call(m, acc, x0, x1, x2);
+#pragma unroll
+                        for (int q = 0; q < 4; q++) so[(r + q) * RV] = acc[q];
+                    }
+                    for (; r < run; r++) {
                         float acc = kWriteOnly ? 0.0f : so[r * RV];
                         const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
                         const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
@@ -365,9 +412,11 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
 
 // launch geometry shared by the module and span-restricted basics launchers
 struct PaintPlan {
-    uint32_t T, nseg, seg_frames, vec4, grid_x;
+    uint32_t T, nseg, seg_frames, vec4, grid_x, stages;
     size_t smem;
 };
+
+constexpr int kPaintMaxSmem = 200 * 1024;
 
 inline PaintPlan zcu_paint_plan(const zcu_ctx* ctx, const PaintArgs& a, int nb, bool skippable) {
     PaintPlan p;
@@ -375,10 +424,23 @@ inline PaintPlan zcu_paint_plan(const zcu_ctx* ctx, const PaintArgs& a, int nb, 
     auto al16 = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
     p.vec4 = (a.V % 4 == 0 && al16(a.out) && al16(a.in0) && al16(a.in1) && al16(a.in2)) ? 1u : 0u;
     p.grid_x = (a.V + 32 * kPaintWarps - 1) / (32 * kPaintWarps);
-    p.smem = (size_t)kPaintStages * nb * p.T * 32 * kPaintWarps * sizeof(float);
+    // ring depth: when the launch puts only a few CTAs on an SM (banks that cannot be cut in time), each CTA gets a deeper
+    // ring of longer tiles so that enough bytes are in flight per SM to cover the HBM latency
+    const uint32_t ctas = p.grid_x * p.nseg, sms = (uint32_t)ctx->sm_count;
+    const uint32_t per_sm = std::min(8u, std::max(1u, (ctas + sms - 1) / sms));
+    const size_t budget = (size_t)kPaintMaxSmem / per_sm;
+    const size_t row = (size_t)nb * 32 * kPaintWarps * sizeof(float);
+    const char* deep_env = getenv("ZCU_PAINT_DEEP");  // tuning: 0 = the fixed three-stage ring
+    const bool deep = !(deep_env && atoi(deep_env) == 0);
+    if (deep && !getenv("ZCU_PAINT_T") && p.T < 16 && row * 16 * kPaintStages <= budget) {
+        p.T = 16;
+        p.seg_frames = (p.seg_frames + 15) / 16 * 16;
+        p.nseg = (a.frames + p.seg_frames - 1) / p.seg_frames;
+    }
+    p.stages = deep ? (uint32_t)std::min<size_t>(8, std::max<size_t>(kPaintStages, budget / (row * p.T))) : (uint32_t)kPaintStages;
+    if (const char* e = getenv("ZCU_PAINT_STAGES")) p.stages = (uint32_t)std::min(8, std::max(2, atoi(e)));  // tuning
+    p.smem = (size_t)p.stages * row * p.T;
     return p;
 }
-
-constexpr int kPaintMaxSmem = kPaintStages * 4 * 16 * 32 * kPaintWarps * 4;  // 4 buffers, T <= 16
 
 }  // namespace zcu
