@@ -89,6 +89,7 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 4; i++)
         if (ctx->arena[i]) cudaFree(ctx->arena[i]);
+    if (ctx->prefix) cudaFree(ctx->prefix);
     if (ctx->xjump) cudaFree(ctx->xjump);
     if (ctx->xjump_resync) cudaFree(ctx->xjump_resync);
     if (ctx->chain) cudaFree(ctx->chain);

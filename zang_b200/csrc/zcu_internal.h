@@ -27,6 +27,8 @@ struct zcu_ctx {
     uint32_t* chain_flags = nullptr;
     size_t chain_flag_count = 0;
     uint32_t paint_epoch = 0;
+    void* prefix = nullptr;  // M::PREFIX modules: state rows at the segment starts
+    size_t prefix_bytes = 0;
     // Noise skip-ahead: xoshiro256 jump matrices (built on first use) and the device counter of unforeseeable extra draws
     void* xjump = nullptr;
     unsigned long long* xjump_resync = nullptr;

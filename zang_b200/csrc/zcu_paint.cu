@@ -86,7 +86,7 @@ int ensure_xjump(zcu_ctx* ctx) {
 bool overlaps(const float* a, const float* b, size_t n) { return a && b && a < b + n && b < a + n; }
 
 template <class M>
-int launch(zcu_ctx* ctx, PaintArgs a) {
+int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     int nb = 1;
     if (M::NIN >= 1 && a.in0) nb++;
     if (M::NIN >= 2 && a.in1) nb++;
@@ -122,6 +122,25 @@ int launch(zcu_ctx* ctx, PaintArgs a) {
     } else if (!skip) {
         p.nseg = 1;
         p.seg_frames = a.frames;
+    }
+    a.prefix = nullptr;
+    a.prefix_stride = 0;
+    if (PrefixOf<M>::value && p.nseg > 1 && !getenv("ZCU_PAINT_NO_PREFIX")) {
+        // one sequential walk per voice tabulates the state at every segment start (instead of a re-walk per segment)
+        const size_t stride = zcu_bank_state_size(kind), need = (size_t)p.nseg * a.V * stride;
+        if (ctx->prefix_bytes < need) {
+            ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (ctx->prefix) cudaFree(ctx->prefix);
+            ctx->prefix = nullptr;
+            ctx->prefix_bytes = 0;
+            ZCU_CUDA(ctx, cudaMalloc(&ctx->prefix, need));
+            ctx->prefix_bytes = need;
+        }
+        a.prefix = ctx->prefix;
+        a.prefix_stride = (uint32_t)stride;
+        k_paint_prefix<M><<<(a.V + 127) / 128, 128, 0, ctx->stream>>>(a, p.seg_frames, p.nseg);
+        ctx->launches++;
+        ZCU_CUDA(ctx, cudaGetLastError());
     }
     static bool attr_set = false;
     if (!attr_set) {
@@ -188,30 +207,30 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     const bool b0 = pl.in0 != nullptr, b1 = pl.in1 != nullptr, b2 = pl.in2 != nullptr;
     switch (pl.kind) {
         case ZCU_MOD_SINE_OSC:
-            if (b0 && b1) return launch<SineMod<true, true>>(ctx, a);
-            if (b0) return launch<SineMod<true, false>>(ctx, a);
-            if (b1) return launch<SineMod<false, true>>(ctx, a);
-            return launch<SineMod<false, false>>(ctx, a);
+            if (b0 && b1) return launch<SineMod<true, true>>(ctx, a, pl.kind);
+            if (b0) return launch<SineMod<true, false>>(ctx, a, pl.kind);
+            if (b1) return launch<SineMod<false, true>>(ctx, a, pl.kind);
+            return launch<SineMod<false, false>>(ctx, a, pl.kind);
         case ZCU_MOD_PULSE_OSC:
-            return b0 ? launch<PulseMod<true>>(ctx, a) : launch<PulseMod<false>>(ctx, a);
+            return b0 ? launch<PulseMod<true>>(ctx, a, pl.kind) : launch<PulseMod<false>>(ctx, a, pl.kind);
         case ZCU_MOD_TRISAW_OSC:
-            return b0 ? launch<TriSawMod<true>>(ctx, a) : launch<TriSawMod<false>>(ctx, a);
-        case ZCU_MOD_NOISE: return launch<NoiseMod>(ctx, a);
-        case ZCU_MOD_ENVELOPE: return launch<EnvelopeMod>(ctx, a);
-        case ZCU_MOD_GATE: return launch<GateMod>(ctx, a);
+            return b0 ? launch<TriSawMod<true>>(ctx, a, pl.kind) : launch<TriSawMod<false>>(ctx, a, pl.kind);
+        case ZCU_MOD_NOISE: return launch<NoiseMod>(ctx, a, pl.kind);
+        case ZCU_MOD_ENVELOPE: return launch<EnvelopeMod>(ctx, a, pl.kind);
+        case ZCU_MOD_GATE: return launch<GateMod>(ctx, a, pl.kind);
         case ZCU_MOD_FILTER:
-            if (b1 && b2) return launch<FilterMod<true, true>>(ctx, a);
-            if (b1) return launch<FilterMod<true, false>>(ctx, a);
-            if (b2) return launch<FilterMod<false, true>>(ctx, a);
-            return launch<FilterMod<false, false>>(ctx, a);
-        case ZCU_MOD_PORTAMENTO: return launch<PortamentoMod>(ctx, a);
-        case ZCU_MOD_CURVE: return launch<CurveMod>(ctx, a);
-        case ZCU_MOD_SAMPLER: return launch<SamplerMod>(ctx, a);
-        case ZCU_MOD_DECIMATOR: return launch<DecimatorMod>(ctx, a);
-        case ZCU_MOD_DISTORTION: return launch<DistortionMod>(ctx, a);
-        case ZCU_MOD_SIMPLE_DELAY: return launch<SimpleDelayMod>(ctx, a);
-        case ZCU_MOD_FILTERED_ECHOES: return launch<FilteredEchoesMod>(ctx, a);
-        case ZCU_MOD_CYCLE: return b0 ? launch<CycleMod<true>>(ctx, a) : launch<CycleMod<false>>(ctx, a);
+            if (b1 && b2) return launch<FilterMod<true, true>>(ctx, a, pl.kind);
+            if (b1) return launch<FilterMod<true, false>>(ctx, a, pl.kind);
+            if (b2) return launch<FilterMod<false, true>>(ctx, a, pl.kind);
+            return launch<FilterMod<false, false>>(ctx, a, pl.kind);
+        case ZCU_MOD_PORTAMENTO: return launch<PortamentoMod>(ctx, a, pl.kind);
+        case ZCU_MOD_CURVE: return launch<CurveMod>(ctx, a, pl.kind);
+        case ZCU_MOD_SAMPLER: return launch<SamplerMod>(ctx, a, pl.kind);
+        case ZCU_MOD_DECIMATOR: return launch<DecimatorMod>(ctx, a, pl.kind);
+        case ZCU_MOD_DISTORTION: return launch<DistortionMod>(ctx, a, pl.kind);
+        case ZCU_MOD_SIMPLE_DELAY: return launch<SimpleDelayMod>(ctx, a, pl.kind);
+        case ZCU_MOD_FILTERED_ECHOES: return launch<FilteredEchoesMod>(ctx, a, pl.kind);
+        case ZCU_MOD_CYCLE: return b0 ? launch<CycleMod<true>>(ctx, a, pl.kind) : launch<CycleMod<false>>(ctx, a, pl.kind);
         default: return zcu_fail(ctx, ZCU_ERR_INVALID, "unknown module kind %d", pl.kind);
     }
 }

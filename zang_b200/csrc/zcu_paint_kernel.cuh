@@ -71,6 +71,46 @@ struct LazyCall { static __device__ __forceinline__ void done(M&) {} };
 template <class M>
 struct LazyCall<M, std::enable_if_t<M::LAZY>> { static __device__ __forceinline__ void done(M& m) { m.advance_done(); } };
 
+// M::PREFIX: a paint() call may be split at any frame (second half entered with note_id_changed = false) without changing a
+// bit, so the state at every segment start can be tabulated by one walk per voice
+template <class M, class = void>
+struct PrefixOf { static constexpr bool value = false; };
+template <class M>
+struct PrefixOf<M, std::void_t<decltype(M::PREFIX)>> { static constexpr bool value = M::PREFIX; };
+
+// One thread per voice walks all its spans once with M::advance() and stores the module state (bank POD format) at every
+// segment start s * seg_frames, s = 1 .. nseg-1, into a.prefix[s][v].
+template <class M>
+__global__ void __launch_bounds__(128) k_paint_prefix(PaintArgs a, uint32_t seg_frames, uint32_t nseg) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= a.V) return;
+    M m;
+    m.load(a, v);
+    PaintArgs row = a;
+    uint32_t s = 1;
+    uint64_t next_b = seg_frames;
+    auto record = [&]() {
+        row.state = (char*)a.prefix + (size_t)s * a.V * a.prefix_stride;
+        m.store(row, v);
+        s++;
+        next_b += seg_frames;
+    };
+    for (uint32_t k = a.off[v], ke = a.off[v + 1]; k < ke && s < nseg; k++) {
+        const uint4 sp = *reinterpret_cast<const uint4*>(a.spans + k);
+        while (s < nseg && next_b <= sp.x) record();  // boundaries in the gap before this span (or exactly at its start)
+        m.begin_span(a, sp.w, sp.z, sp.y - sp.x);
+        uint32_t pos = sp.x;
+        while (s < nseg && next_b < sp.y) {
+            m.advance(a, v, pos, (uint32_t)next_b - pos);
+            pos = (uint32_t)next_b;
+            record();
+        }
+        m.advance(a, v, pos, sp.y - pos);
+        m.end_span(a);
+    }
+    while (s < nseg) record();
+}
+
 // cp.async.wait_group takes an immediate: dispatch the ring depths in use
 __device__ __forceinline__ void pipeline_wait_prior_rt(uint32_t n) {
     switch (n) {
@@ -236,7 +276,28 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         if (tile_first + s < ntiles) issue(tile_first + s); else __pipeline_commit();
     }
 
-    if (M::SKIP && f_begin > 0) {
+    if (PrefixOf<M>::value && a.prefix != nullptr && f_begin > 0) {
+        // the state at the segment start was tabulated by k_paint_prefix: move the span cursor, load the row, and re-enter
+        // a straddling span as the second half of a split call
+        if (valid) {
+            while (s_end <= f_begin) {
+                k++;
+                if (k < ke) {
+                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                    s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+                } else {
+                    s_start = s_end = 0xFFFFFFFFu;
+                }
+            }
+            PaintArgs row = a;
+            row.state = (char*)a.prefix + (size_t)blockIdx.y * a.V * a.prefix_stride;
+            m.load(row, v);
+            if (s_start < f_begin) {
+                m.begin_span(a, s_param, s_flags & ~(uint32_t)ZCU_SPAN_NOTE_ID_CHANGED, s_end - s_start);
+                active = true;
+            }
+        }
+    } else if (M::SKIP && f_begin > 0) {
         // spans that end before the segment: state only
         while (s_end <= f_begin) {
             m.begin_span(a, s_param, s_flags, s_end - s_start);

@@ -17,6 +17,8 @@
 #include <new>
 #include <vector>
 
+#include <thread>
+#include <algorithm>
 #include "zcu_internal.h"
 #include "zcu_render_kernel.cuh"
 #include "zcu_render_scan.cuh"
@@ -484,29 +486,45 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     // per-call host scalar of modules.zig:231-234 (cos, sqrt): once per event, on the host
     // (a small direct-mapped memo keyed by the bits of freq: a bank plays few distinct pitches, and the memo returns
     // the very value the function would)
+    // Expanded by a few host threads (each with its own memo) straight into the pinned staging buffer: at ~1 M events per
+    // job a single thread costs more than the H2D copy it feeds.
     struct Memo { uint32_t key; float cutoff; bool valid; };
-    static thread_local Memo memo[1024];
-    static thread_local float memo_sr = 0.0f;
-    if (memo_sr != r->cfg.sample_rate) {
-        for (Memo& m : memo) m.valid = false;
-        memo_sr = r->cfg.sample_rate;
-    }
-    for (uint32_t i = 0; i < n; i++) {
-        DevEvent& d = r->h_events[i];
-        d.frame = events_host[i].frame;
-        d.note_id = events_host[i].note_id;
-        d.freq = events_host[i].freq;
-        d.note_on = events_host[i].note_on;
-        uint32_t key;
-        memcpy(&key, &events_host[i].freq, 4);
-        Memo& m = memo[(key * 2654435761u) >> 22];
-        if (!m.valid || m.key != key) {
-            m.key = key;
-            m.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, r->cfg.sample_rate);
-            m.valid = true;
+    const float sr = r->cfg.sample_rate;
+    DevEvent* const staged = r->h_events;
+    auto expand = [events_host, staged, sr](uint32_t i0, uint32_t i1) {
+        std::vector<Memo> memo(1024, Memo{0u, 0.0f, false});
+        for (uint32_t i = i0; i < i1; i++) {
+            DevEvent& d = staged[i];
+            d.frame = events_host[i].frame;
+            d.note_id = events_host[i].note_id;
+            d.freq = events_host[i].freq;
+            d.note_on = events_host[i].note_on;
+            uint32_t key;
+            memcpy(&key, &events_host[i].freq, 4);
+            Memo& m = memo[(key * 2654435761u) >> 22];
+            if (!m.valid || m.key != key) {
+                m.key = key;
+                m.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, sr);
+                m.valid = true;
+            }
+            d.cutoff = m.cutoff;
+            d.cnt0 = d.flags = d.pad = 0;
         }
-        d.cutoff = m.cutoff;
-        d.cnt0 = d.flags = d.pad = 0;
+    };
+    uint32_t nthreads = 1;
+    if (n >= (1u << 16)) nthreads = std::min(4u, std::max(1u, std::thread::hardware_concurrency()));  // measured: 4 is the knee
+    if (const char* e = getenv("ZCU_HOST_THREADS")) nthreads = (uint32_t)std::max(1, atoi(e));
+    if (nthreads <= 1) {
+        expand(0, n);
+    } else {
+        std::vector<std::thread> pool;
+        const uint32_t per = (n + nthreads - 1) / nthreads;
+        for (uint32_t t = 1; t < nthreads; t++) {
+            const uint32_t i0 = std::min(n, t * per), i1 = std::min(n, (t + 1) * per);
+            if (i0 < i1) pool.emplace_back(expand, i0, i1);
+        }
+        expand(0, std::min(n, per));
+        for (auto& th : pool) th.join();
     }
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, r->h_events, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
