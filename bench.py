@@ -344,10 +344,11 @@ def main():
                 from zang_b200 import engine as E
                 bf = 64 * BUFFER_FRAMES
                 nb = E.NiceInstrumentBank(ctx, V, 0.3)
-                soff, sspans = BankTrigger(wl["event_off"], wl["events"], total_frames, BUFFER_FRAMES).spans(0, bf)
+                wl64 = synth.polyphony_bank(V, bf, SAMPLE_RATE)  # the same generator and seed, cut to the block (params rows = its events)
+                soff, sspans = BankTrigger(wl64["event_off"], wl64["events"], bf, BUFFER_FRAMES).spans(0, bf)
                 sp = ctx.spans(V, bf, soff, sspans)
-                rows = np.zeros(wl["events"].size, dtype=E.NiceInstrumentBank.Params)
-                rows["sample_rate"], rows["freq"], rows["note_on"] = SAMPLE_RATE, wl["events"]["freq"], wl["events"]["note_on"]
+                rows = np.zeros(wl64["events"].size, dtype=E.NiceInstrumentBank.Params)
+                rows["sample_rate"], rows["freq"], rows["note_on"] = SAMPLE_RATE, wl64["events"]["freq"], wl64["events"]["note_on"]
                 bufs = [ctx.buf(bf, V) for _ in range(3)]
                 dp = {}
                 for pm, pname in ((L.PAINT_TOLERANCE, "tolerance"), (L.PAINT_EXACT, "exact")):

@@ -90,7 +90,7 @@ int zcu_fail(zcu_ctx* ctx, int code, const char* fmt, ...);
 // as many segments as fill the chip's resident one-warp CTAs exactly once (each at least 256 frames, a multiple of T);
 // the others get one segment.  nbufs = staged buffers (output + inputs).  ZCU_PAINT_SEGMENTS overrides (tests).
 void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, int nbufs, bool skippable, uint32_t* T, uint32_t* nseg,
-                        uint32_t* seg_frames);
+                        uint32_t* seg_frames, uint32_t max_resident = 8);
 
 // copies `bytes` of host memory into arena slot `slot` (stream ordered) and returns the device ptr
 int zcu_arena_upload(zcu_ctx* ctx, int slot, const void* host, size_t bytes, void** dev_out);

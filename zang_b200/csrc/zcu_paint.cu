@@ -107,7 +107,8 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         a.xjump = skip ? (const ulonglong2*)ctx->xjump : nullptr;
         a.xjump_resync = skip ? ctx->xjump_resync : nullptr;
     }
-    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm);
+    // tolerance-mode segments pay a warm-up window each: half as many, twice as long (measured best at 4 CTAs per SM)
+    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm, warm ? 4u : 8u);
     a.chain = nullptr;
     a.chain_flags = nullptr;
     a.epoch = 0;
@@ -156,7 +157,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
 }  // namespace
 
 void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, int nbufs, bool skippable, uint32_t* T_out, uint32_t* nseg_out,
-                        uint32_t* seg_frames_out) {
+                        uint32_t* seg_frames_out, uint32_t max_resident) {
     const uint32_t rv = 32u * kPaintWarps;
     const uint32_t grid = std::max(1u, (voices + rv - 1) / rv);
     const uint32_t sms = (uint32_t)ctx->sm_count;
@@ -167,7 +168,7 @@ void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, in
     if (skippable && frames > 0) {
         // resident CTAs per SM: 8 by registers (128 threads x <= 64 registers), or what the staging ring leaves of ~220 KB
         const uint32_t per_cta = (uint32_t)kPaintStages * (uint32_t)nbufs * T * rv * 4u + 1024u;
-        const uint32_t resident = std::min(8u, (220u * 1024u) / per_cta) * sms;
+        const uint32_t resident = std::min(max_resident, (220u * 1024u) / per_cta) * sms;
         // one full wave: a second, partly filled wave would cost as much as the first
         nseg = std::max(1u, resident / grid);
         if (const char* e = getenv("ZCU_PAINT_SEGMENTS")) nseg = (uint32_t)std::max(1, atoi(e));  // tuning / tests

@@ -479,9 +479,9 @@ struct PaintPlan {
 
 constexpr int kPaintMaxSmem = 200 * 1024;
 
-inline PaintPlan zcu_paint_plan(const zcu_ctx* ctx, const PaintArgs& a, int nb, bool skippable) {
+inline PaintPlan zcu_paint_plan(const zcu_ctx* ctx, const PaintArgs& a, int nb, bool skippable, uint32_t max_resident = 8) {
     PaintPlan p;
-    zcu_paint_segments(ctx, a.V, a.frames, nb, skippable, &p.T, &p.nseg, &p.seg_frames);
+    zcu_paint_segments(ctx, a.V, a.frames, nb, skippable, &p.T, &p.nseg, &p.seg_frames, max_resident);
     auto al16 = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
     p.vec4 = (a.V % 4 == 0 && al16(a.out) && al16(a.in0) && al16(a.in1) && al16(a.in2)) ? 1u : 0u;
     p.grid_x = (a.V + 32 * kPaintWarps - 1) / (32 * kPaintWarps);
