@@ -23,6 +23,10 @@ mixes are summed with ONE NCCL reduce to rank 0 inside the timed region.
 import argparse
 import json
 import os
+
+# NCCL prints its version banner on STDOUT when NCCL_DEBUG is VERSION/INFO; the driver reads one JSON line from stdout
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
+    os.environ["NCCL_DEBUG"] = "WARN"
 import statistics
 import subprocess
 import sys

@@ -41,7 +41,63 @@ pub const Context = struct {
     pub fn sync(self: Context) Error!void {
         try check(c.zcu_ctx_sync(self.h));
     }
+    /// ZCU_PAINT_EXACT (default) or ZCU_PAINT_TOLERANCE (Filter.paint in device-verified time segments, <= 1e-5)
+    pub fn setPaintMode(self: Context, mode: c_int) Error!void {
+        try check(c.zcu_ctx_set_paint_mode(self.h, mode));
+    }
+    /// 0 = every time-segmented Noise paint so far is bit-identical to the sequential loop
+    pub fn noiseResyncCount(self: Context) Error!u64 {
+        var n: u64 = 0;
+        try check(c.zcu_ctx_noise_resync_count(self.h, &n));
+        return n;
+    }
 };
+
+/// zang.Delay(DELAY_SAMPLES) for every voice (src/zang/delay.zig:7-17) + SimpleDelay.paint (examples/modules.zig:341-388).
+/// The comptime delay length becomes a run-time argument of the bank; the module contract is unchanged.
+pub fn SimpleDelayBank(comptime DELAY_SAMPLES: u32) type {
+    return struct {
+        pub const num_outputs = 1;
+        pub const num_temps = 0;
+        ctx: Context,
+        bank: *c.zcu_bank,
+
+        pub fn init(ctx: Context, voices: u32) Error!@This() {
+            var b: ?*c.zcu_bank = null;
+            try check(c.zcu_delay_bank_create(ctx.h, c.ZCU_MOD_SIMPLE_DELAY, voices, DELAY_SAMPLES, &b));
+            return .{ .ctx = ctx, .bank = b.? };
+        }
+        pub fn reset(self: *@This()) Error!void {
+            try check(c.zcu_bank_reset(self.ctx.h, self.bank, 0));
+        }
+        pub fn paint(self: *@This(), spans: *const c.zcu_spans, outputs: [1]Buffer, temps: [0]Buffer, input: Buffer) Error!void {
+            _ = temps;
+            try check(c.zcu_paint_simple_delay(self.ctx.h, self.bank, spans, outputs[0].h, input.h));
+        }
+    };
+}
+
+/// FilteredEchoes(DELAY_SAMPLES) (examples/modules.zig:392-460): Params{input, feedback_volume, cutoff}; the reference's two
+/// temps are not needed (the device module keeps them in registers).
+pub fn FilteredEchoesBank(comptime DELAY_SAMPLES: u32) type {
+    return struct {
+        pub const num_outputs = 1;
+        pub const num_temps = 0;
+        pub const Params = c.zcu_echoes_params;
+        ctx: Context,
+        bank: *c.zcu_bank,
+
+        pub fn init(ctx: Context, voices: u32) Error!@This() {
+            var b: ?*c.zcu_bank = null;
+            try check(c.zcu_delay_bank_create(ctx.h, c.ZCU_MOD_FILTERED_ECHOES, voices, DELAY_SAMPLES, &b));
+            return .{ .ctx = ctx, .bank = b.? };
+        }
+        pub fn paint(self: *@This(), spans: *const c.zcu_spans, outputs: [1]Buffer, temps: [0]Buffer, params: []const Params, input: Buffer) Error!void {
+            _ = temps;
+            try check(c.zcu_paint_filtered_echoes(self.ctx.h, self.bank, spans, params.ptr, @intCast(params.len), outputs[0].h, input.h));
+        }
+    };
+}
 
 /// [frames][voices] f32 device buffer: the batched form of the caller-owned []f32
 pub const Buffer = struct {
