@@ -108,12 +108,15 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         a.xjump_resync = skip ? ctx->xjump_resync : nullptr;
     }
     // tolerance-mode segments pay a warm-up window each: half as many, twice as long (measured best at 4 CTAs per SM)
-    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm, warm ? 4u : 8u);
+    // exact chained prefix sum (M::SCAN): no aliasing either, the scan pass reads inputs while earlier segments paint
+    const bool scan = ScanOf<M>::value && !getenv("ZCU_PAINT_NO_SCAN") && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
+                      !overlaps(a.out, a.in2, n);
+    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, warm ? 4u : 8u);
     a.chain = nullptr;
     a.chain_flags = nullptr;
     a.epoch = 0;
     a.warm_cap = 0;
-    if (warm && p.nseg > 1) {
+    if ((warm || scan) && p.nseg > 1) {
         int rc = ensure_chain(ctx, (size_t)p.nseg * a.V, (size_t)p.nseg * p.grid_x);
         if (rc) return rc;
         a.chain = (float2*)ctx->chain;

@@ -65,6 +65,18 @@ struct Sample4<M, std::enable_if_t<M::HAS_SAMPLE4>> {
     }
 };
 
+// M::SCAN: the carried state is an integer sum over the inputs (PulseOsc's phase with a frequency buffer), so time segments
+// can be chained exactly: every segment first sums its own inputs (scan tiles), takes its start state from the predecessor's
+// published inclusive prefix, publishes its own, then paints
+template <class M, class = void>
+struct ScanOf { static constexpr bool value = false; };
+template <class M>
+struct ScanOf<M, std::void_t<decltype(M::SCAN)>> { static constexpr bool value = M::SCAN; };
+template <class M, bool = ScanOf<M>::value>
+struct ScanCall { static __device__ __forceinline__ void sample(M&, float, float, float) {} };
+template <class M>
+struct ScanCall<M, true> { static __device__ __forceinline__ void sample(M& m, float x0, float x1, float x2) { m.scan_sample(x0, x1, x2); } };
+
 // m.advance_done() for modules whose advance() only accumulates (M::LAZY)
 template <class M, class = void>
 struct LazyCall { static __device__ __forceinline__ void done(M&) {} };
@@ -151,8 +163,10 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     // this CTA's segment of the frame axis (seg_frames is a multiple of T)
     constexpr bool kWarm = WarmOf<M>::value;
     constexpr bool kWriteOnly = WriteOnlyOf<M>::value;
+    constexpr bool kScan = ScanOf<M>::value;
     const bool warm = kWarm && a.chain != nullptr;  // tolerance mode: segments start from a verified warm-up or the chain
-    const bool segmented = M::SKIP || warm;
+    const bool scan = kScan && a.chain != nullptr;  // exact chained prefix sum: segments pass their integer state along
+    const bool segmented = M::SKIP || warm || scan;
     const uint32_t f_begin = segmented ? blockIdx.y * seg_frames : 0u;
     const uint32_t f_end = segmented ? min(a.frames, f_begin + seg_frames) : a.frames;
     if (f_begin >= f_end) return;  // uniform over the CTA
@@ -164,6 +178,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const uint32_t c = (tid % cpr) * cw, r0 = tid / cpr;
     const bool c_valid = v0 + c < a.V;
 
+    bool inputs_only = false;  // scan pass: the refill skips the output buffer
     auto copy_rows = [&](const float* buf, int slot, uint32_t stage, uint32_t f0, uint32_t n) {
         const float* src = buf + (size_t)f0 * V + v0 + c;
         float* dst = tile_ptr(stage, slot) + c;
@@ -179,7 +194,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         const uint32_t stage = tile % S;
         if (c_valid) {
             // warm-up tiles (before the segment) only read the inputs: the output rows there belong to the previous segment
-            if (!kWriteOnly && !(kWarm && f0 < f_begin)) copy_rows(a.out, i_out, stage, f0, n);
+            if (!kWriteOnly && !(kWarm && f0 < f_begin) && !(kScan && inputs_only)) copy_rows(a.out, i_out, stage, f0, n);
             if (M::NIN >= 1 && i_in0 >= 0) copy_rows(a.in0, i_in0, stage, f0, n);
             if (M::NIN >= 2 && i_in1 >= 0) copy_rows(a.in1, i_in1, stage, f0, n);
             if (M::NIN >= 3 && i_in2 >= 0) copy_rows(a.in2, i_in2, stage, f0, n);
@@ -204,125 +219,12 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     uint32_t tile_first = tile0;
     bool active = false;
     bool pristine = false;
-    if constexpr (kWarm) {
-        if (warm && f_begin > 0) {
-            // Tolerance mode.  The state at f_begin is approximated by running the module from zero state over the Wf frames
-            // before the segment; the error is (homogeneous map of the window) x (true state at the window start), and the
-            // module tracks that map (warm_ok).  Wf: the largest per-voice estimate in the CTA, from the constants of the span
-            // at f_begin; no warm-up at all if that exceeds warm_cap (then the segment waits for its predecessor's end state).
-            __shared__ uint32_t s_w;
-            if (tid == 0) s_w = 0;
-            __syncthreads();
-            const uint32_t f_lo = f_begin > a.warm_cap ? f_begin - a.warm_cap : 0u;
-            uint32_t kk = k;
-            uint32_t p_start = s_start, p_end = s_end, p_flags = s_flags, p_param = s_param;
-            uint32_t est = 0;
-            pristine = s_start >= f_begin;  // nothing painted before the segment: the loaded state is the start state
-            if (valid && !pristine) {
-                // first span that reaches into [f_lo, ...): everything before it cannot matter
-                while (p_end <= f_lo) {
-                    kk++;
-                    if (kk < ke) {
-                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
-                        p_start = s.x; p_end = s.y; p_flags = s.z; p_param = s.w;
-                    } else {
-                        p_start = p_end = 0xFFFFFFFFu;
-                    }
-                }
-                k = kk; s_start = p_start; s_end = p_end; s_flags = p_flags; s_param = p_param;
-                // the span painting at f_begin (or the last one before it) provides the constants of the estimate
-                uint32_t q_param = 0xFFFFFFFFu, q_flags = 0, q_len = 0;
-                while (p_start < f_begin) {
-                    q_param = p_param; q_flags = p_flags; q_len = p_end - p_start;
-                    kk++;
-                    if (kk >= ke) break;
-                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
-                    p_start = s.x; p_end = s.y; p_flags = s.z; p_param = s.w;
-                }
-                est = 0xFFFFFFFFu;  // painted before, but not inside the longest window: only the chain knows the state
-                if (q_param != 0xFFFFFFFFu) {
-                    m.begin_span(a, q_param, q_flags, q_len);
-                    est = m.warm_estimate(a.warm_cap);
-                }
-                atomicMax(&s_w, est);
-            }
-            __syncthreads();
-            uint32_t Wf = s_w;
-            if (Wf > a.warm_cap) Wf = 0;  // hopeless: chain
-            Wf = min((Wf + T - 1) / T * T, f_begin / T * T);
-            if (Wf == f_begin) Wf = 0;    // a window back to frame 0 is the sequential walk: chain instead
-            const uint32_t f_w = f_begin - Wf;
-            tile_first = f_w / T;
-            if (valid && !pristine) {
-                m.warm_begin();
-                while (s_end <= f_w) {
-                    k++;
-                    if (k < ke) {
-                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
-                        s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
-                    } else {
-                        s_start = s_end = 0xFFFFFFFFu;
-                    }
-                }
-                if (s_start < f_w) {  // entered in the middle: only the span's constants are needed
-                    m.begin_span(a, s_param, s_flags, s_end - s_start);
-                    active = true;
-                }
-            }
-        }
-    }
-    // the ring is primed before the skip-ahead so that its latency hides behind it
-    for (uint32_t s = 0; s + 1 < S; s++) {
-        if (tile_first + s < ntiles) issue(tile_first + s); else __pipeline_commit();
-    }
-
-    if (PrefixOf<M>::value && a.prefix != nullptr && f_begin > 0) {
-        // the state at the segment start was tabulated by k_paint_prefix: move the span cursor, load the row, and re-enter
-        // a straddling span as the second half of a split call
-        if (valid) {
-            while (s_end <= f_begin) {
-                k++;
-                if (k < ke) {
-                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
-                    s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
-                } else {
-                    s_start = s_end = 0xFFFFFFFFu;
-                }
-            }
-            PaintArgs row = a;
-            row.state = (char*)a.prefix + (size_t)blockIdx.y * a.V * a.prefix_stride;
-            m.load(row, v);
-            if (s_start < f_begin) {
-                m.begin_span(a, s_param, s_flags & ~(uint32_t)ZCU_SPAN_NOTE_ID_CHANGED, s_end - s_start);
-                active = true;
-            }
-        }
-    } else if (M::SKIP && f_begin > 0) {
-        // spans that end before the segment: state only
-        while (s_end <= f_begin) {
-            m.begin_span(a, s_param, s_flags, s_end - s_start);
-            m.advance(a, v, s_start, s_end - s_start);
-            m.end_span(a);
-            k++;
-            if (k < ke) {
-                const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
-                s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
-            } else {
-                s_start = s_end = 0xFFFFFFFFu;
-            }
-        }
-        if (s_start < f_begin) {  // the span that straddles the segment start
-            m.begin_span(a, s_param, s_flags, s_end - s_start);
-            m.advance(a, v, s_start, f_begin - s_start);
-            active = true;
-        }
-        LazyCall<M>::done(m);
-    }
-
-    // one tile of the ring: wait, refill, walk the frames in runs, write the output tile back.  WT = warm-up tile (tolerance
-    // mode, before the segment): the module only advances its state, nothing is read from or written to the output.
-    auto do_tile = [&](uint32_t tile, auto wt_tag) {
-        constexpr bool WT = decltype(wt_tag)::value;
+    // one tile of the ring: wait, refill, walk the frames in runs, write the output tile back.  Warm-up tiles (tolerance
+    // mode, before the segment) and scan tiles (first pass of an exact chained prefix sum) only advance module state from the
+    // inputs: nothing is read from or written to the output.
+    auto do_tile = [&](uint32_t tile, auto kind_tag) {
+        constexpr int KIND = decltype(kind_tag)::value;  // 0 paint, 1 warm-up tile, 2 scan tile (kScan pass 1)
+        constexpr bool WT = KIND != 0;
         pipeline_wait_prior_rt(S - 2);
         __syncthreads();  // tile `tile` has landed for every thread; every thread is done with the stage refilled next
         if (tile + S - 1 < ntiles) issue(tile + S - 1); else __pipeline_commit();
@@ -368,7 +270,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                         const float x0 = i_in0 >= 0 ? s0[r * RV] : 0.0f;
                         const float x1 = i_in1 >= 0 ? s1[r * RV] : 0.0f;
                         const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
-                        WarmCall<M>::sample(m, x0, x1, x2);
+                        if constexpr (KIND == 1) WarmCall<M>::sample(m, x0, x1, x2); else ScanCall<M>::sample(m, x0, x1, x2);
                     }
                 } else {
                     painted = 1;
@@ -439,7 +341,172 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
 
     if constexpr (kWarm) {
         if (warm && f_begin > 0) {
-            for (uint32_t tile = tile_first; tile < tile0; tile++) do_tile(tile, std::true_type{});
+            // Tolerance mode.  The state at f_begin is approximated by running the module from zero state over the Wf frames
+            // before the segment; the error is (homogeneous map of the window) x (true state at the window start), and the
+            // module tracks that map (warm_ok).  Wf: the largest per-voice estimate in the CTA, from the constants of the span
+            // at f_begin; no warm-up at all if that exceeds warm_cap (then the segment waits for its predecessor's end state).
+            __shared__ uint32_t s_w;
+            if (tid == 0) s_w = 0;
+            __syncthreads();
+            const uint32_t f_lo = f_begin > a.warm_cap ? f_begin - a.warm_cap : 0u;
+            uint32_t kk = k;
+            uint32_t p_start = s_start, p_end = s_end, p_flags = s_flags, p_param = s_param;
+            uint32_t est = 0;
+            pristine = s_start >= f_begin;  // nothing painted before the segment: the loaded state is the start state
+            if (valid && !pristine) {
+                // first span that reaches into [f_lo, ...): everything before it cannot matter
+                while (p_end <= f_lo) {
+                    kk++;
+                    if (kk < ke) {
+                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
+                        p_start = s.x; p_end = s.y; p_flags = s.z; p_param = s.w;
+                    } else {
+                        p_start = p_end = 0xFFFFFFFFu;
+                    }
+                }
+                k = kk; s_start = p_start; s_end = p_end; s_flags = p_flags; s_param = p_param;
+                // the span painting at f_begin (or the last one before it) provides the constants of the estimate
+                uint32_t q_param = 0xFFFFFFFFu, q_flags = 0, q_len = 0;
+                while (p_start < f_begin) {
+                    q_param = p_param; q_flags = p_flags; q_len = p_end - p_start;
+                    kk++;
+                    if (kk >= ke) break;
+                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
+                    p_start = s.x; p_end = s.y; p_flags = s.z; p_param = s.w;
+                }
+                est = 0xFFFFFFFFu;  // painted before, but not inside the longest window: only the chain knows the state
+                if (q_param != 0xFFFFFFFFu) {
+                    m.begin_span(a, q_param, q_flags, q_len);
+                    est = m.warm_estimate(a.warm_cap);
+                }
+                atomicMax(&s_w, est);
+            }
+            __syncthreads();
+            uint32_t Wf = s_w;
+            if (Wf > a.warm_cap) Wf = 0;  // hopeless: chain
+            Wf = min((Wf + T - 1) / T * T, f_begin / T * T);
+            if (Wf == f_begin) Wf = 0;    // a window back to frame 0 is the sequential walk: chain instead
+            const uint32_t f_w = f_begin - Wf;
+            tile_first = f_w / T;
+            if (valid && !pristine) {
+                m.warm_begin();
+                while (s_end <= f_w) {
+                    k++;
+                    if (k < ke) {
+                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                        s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+                    } else {
+                        s_start = s_end = 0xFFFFFFFFu;
+                    }
+                }
+                if (s_start < f_w) {  // entered in the middle: only the span's constants are needed
+                    m.begin_span(a, s_param, s_flags, s_end - s_start);
+                    active = true;
+                }
+            }
+        }
+    }
+    if constexpr (kScan) {
+        if (scan) {
+            // pass 1: position the span cursor at the segment start, then sum this segment's inputs (inputs only)
+            if (f_begin > 0 && valid) {
+                while (s_end <= f_begin) {
+                    k++;
+                    if (k < ke) {
+                        const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                        s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+                    } else {
+                        s_start = s_end = 0xFFFFFFFFu;
+                    }
+                }
+                if (s_start < f_begin) {
+                    m.begin_span(a, s_param, s_flags, s_end - s_start);
+                    active = true;
+                }
+            }
+            const uint32_t k_0 = k, ss_0 = s_start, se_0 = s_end, sf_0 = s_flags, sp_0 = s_param;
+            const bool act_0 = active;
+            m.scan_begin();
+            inputs_only = true;
+            for (uint32_t s = 0; s + 1 < S; s++) {
+                if (tile0 + s < ntiles) issue(tile0 + s); else __pipeline_commit();
+            }
+            for (uint32_t tile = tile0; tile < ntiles; tile++) do_tile(tile, std::integral_constant<int, 2>{});
+            __pipeline_wait_prior(0);
+            __syncthreads();
+            inputs_only = false;
+            // look-back: the predecessor's inclusive prefix is this segment's start state (segment 0 keeps the loaded state)
+            if (blockIdx.y > 0) {
+                if (tid == 0) {
+                    const volatile uint32_t* fl = a.chain_flags + (size_t)(blockIdx.y - 1) * gridDim.x + blockIdx.x;
+                    while (*fl != a.epoch) __nanosleep(128);
+                    __threadfence();
+                }
+                __syncthreads();
+                if (valid) m.scan_load(a.chain + (size_t)(blockIdx.y - 1) * V + v);
+            }
+            if (f_end < a.frames) {
+                if (valid) m.scan_store(a.chain + (size_t)blockIdx.y * V + v);
+                __threadfence();
+                __syncthreads();
+                if (tid == 0) atomicExch(a.chain_flags + (size_t)blockIdx.y * gridDim.x + blockIdx.x, a.epoch);
+            }
+            // pass 2 starts where pass 1 started
+            k = k_0; s_start = ss_0; s_end = se_0; s_flags = sf_0; s_param = sp_0; active = act_0;
+            if (active) m.begin_span(a, s_param, s_flags, s_end - s_start);
+        }
+    }
+    // the ring is primed before the skip-ahead so that its latency hides behind it
+    for (uint32_t s = 0; s + 1 < S; s++) {
+        if (tile_first + s < ntiles) issue(tile_first + s); else __pipeline_commit();
+    }
+
+    if (PrefixOf<M>::value && a.prefix != nullptr && f_begin > 0) {
+        // the state at the segment start was tabulated by k_paint_prefix: move the span cursor, load the row, and re-enter
+        // a straddling span as the second half of a split call
+        if (valid) {
+            while (s_end <= f_begin) {
+                k++;
+                if (k < ke) {
+                    const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                    s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+                } else {
+                    s_start = s_end = 0xFFFFFFFFu;
+                }
+            }
+            PaintArgs row = a;
+            row.state = (char*)a.prefix + (size_t)blockIdx.y * a.V * a.prefix_stride;
+            m.load(row, v);
+            if (s_start < f_begin) {
+                m.begin_span(a, s_param, s_flags & ~(uint32_t)ZCU_SPAN_NOTE_ID_CHANGED, s_end - s_start);
+                active = true;
+            }
+        }
+    } else if (M::SKIP && f_begin > 0) {
+        // spans that end before the segment: state only
+        while (s_end <= f_begin) {
+            m.begin_span(a, s_param, s_flags, s_end - s_start);
+            m.advance(a, v, s_start, s_end - s_start);
+            m.end_span(a);
+            k++;
+            if (k < ke) {
+                const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+                s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+            } else {
+                s_start = s_end = 0xFFFFFFFFu;
+            }
+        }
+        if (s_start < f_begin) {  // the span that straddles the segment start
+            m.begin_span(a, s_param, s_flags, s_end - s_start);
+            m.advance(a, v, s_start, f_begin - s_start);
+            active = true;
+        }
+        LazyCall<M>::done(m);
+    }
+
+    if constexpr (kWarm) {
+        if (warm && f_begin > 0) {
+            for (uint32_t tile = tile_first; tile < tile0; tile++) do_tile(tile, std::integral_constant<int, 1>{});
             // end of the warm-up: keep the warmed state if every voice of the CTA verified its window, otherwise wait for the
             // end state the previous segment publishes (CTAs are dispatched in blockIdx order, so the predecessor is resident
             // or done: no deadlock; an undamped filter degenerates to the sequential walk)
@@ -455,7 +522,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             }
         }
     }
-    for (uint32_t tile = tile0; tile < ntiles; tile++) do_tile(tile, std::false_type{});
+    for (uint32_t tile = tile0; tile < ntiles; tile++) do_tile(tile, std::integral_constant<int, 0>{});
 
     if constexpr (kWarm) {
         if (warm && f_end < a.frames) {  // publish the end state for a successor that could not verify its warm-up
