@@ -165,6 +165,9 @@ uint64_t zcu_ctx_launch_count(zcu_ctx* ctx); /* kernels launched by this library
  * TriSawOsc.zig:152) against the IEEE quotient, for EVERY f32 numerator.  mismatches must be 0; claimed = numerators for
  * which the fast sequence is used (the rest take the real division). */
 int zcu_selftest_div_by_const(zcu_ctx* ctx, float divisor, uint64_t* mismatches, uint64_t* claimed);
+/* The same for numerator / utof23(ifreq) of the buffer-frequency PulseOsc (PulseOsc.zig:138): every one of the 2^23 - 1
+ * denominators the phase increment can produce. */
+int zcu_selftest_div_numerator(zcu_ctx* ctx, float numerator, uint64_t* mismatches, uint64_t* claimed);
 
 /* Arithmetic mode of the module paints (zcu_paint_*).
  * ZCU_PAINT_EXACT (default): every module walks each voice's frames in the reference's order; all state-carrying

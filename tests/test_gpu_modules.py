@@ -224,3 +224,14 @@ def test_div_by_constant_is_exact(ctx, sr):
     assert rc == 0
     assert bad.value == 0, f"{bad.value} of {claimed.value} quotients differ from x / {sr}"
     assert claimed.value > 3.3e9  # every finite numerator with a quotient in [1e-30, 1e30] takes the fast sequence
+
+
+def test_pulse_gain_division_is_exact(ctx):
+    """gain / utof23(ifreq) (PulseOsc.zig:138) is evaluated per sample without the branch of the IEEE division sequence; it
+    must be the IEEE quotient for every denominator the 32-bit phase increment can produce."""
+    import ctypes as C
+    from zang_b200._lib import lib
+    bad, claimed = C.c_uint64(), C.c_uint64()
+    assert lib.zcu_selftest_div_numerator(ctx._h, C.c_float(0.7), C.byref(bad), C.byref(claimed)) == 0
+    assert bad.value == 0, f"{bad.value} of {claimed.value} quotients differ"
+    assert claimed.value == (1 << 23) - 1

@@ -293,6 +293,22 @@ __global__ void k_div_probe(float d, unsigned long long* mismatches, unsigned lo
     atomicAdd(claimed, ok_n);
 }
 
+// every denominator utof23(ifreq) can produce (k * 2^-23, k = 1 .. 2^23-1) against one numerator
+__global__ void k_div_numerator_probe(float num, unsigned long long* mismatches, unsigned long long* claimed) {
+    unsigned long long bad = 0, ok_n = 0;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < (1u << 23); k += gridDim.x * blockDim.x) {
+        const float b = utof23(k << 9);
+        if (b == 0.0f) continue;
+        bool ok = true;
+        const float q = div_nobranch(num, b, ok);
+        if (!ok) continue;
+        ok_n++;
+        if (__float_as_uint(q) != __float_as_uint(num / b)) bad++;
+    }
+    if (bad) atomicAdd(mismatches, bad);
+    atomicAdd(claimed, ok_n);
+}
+
 // a*b+c with operands chosen so that a fused multiply-add gives a different f32 than mul-then-add
 __global__ void k_fma_probe(float a, float b, float c, float* out) { out[0] = a * b + c; }
 
@@ -343,6 +359,22 @@ extern "C" int zcu_selftest_div_by_const(zcu_ctx* ctx, float divisor, uint64_t* 
     if (rc) return rc;
     ZCU_CUDA(ctx, cudaMemsetAsync(d, 0, 2 * sizeof(unsigned long long), ctx->stream));
     k_div_probe<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(divisor, d, d + 1);
+    ctx->launches++;
+    unsigned long long h[2] = {0, 0};
+    ZCU_CUDA(ctx, cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *mismatches = h[0];
+    *claimed = h[1];
+    return ZCU_OK;
+}
+
+extern "C" int zcu_selftest_div_numerator(zcu_ctx* ctx, float numerator, uint64_t* mismatches, uint64_t* claimed) {
+    if (!ctx || !mismatches || !claimed) return ZCU_ERR_INVALID;
+    unsigned long long* d = nullptr;
+    int rc = zcu_arena_reserve(ctx, 0, 2 * sizeof(unsigned long long), (void**)&d);
+    if (rc) return rc;
+    ZCU_CUDA(ctx, cudaMemsetAsync(d, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    k_div_numerator_probe<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(numerator, d, d + 1);
     ctx->launches++;
     unsigned long long h[2] = {0, 0};
     ZCU_CUDA(ctx, cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
