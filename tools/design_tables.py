@@ -12,7 +12,7 @@ a = P(f"{tag}_module_bw_4096.json")["results"]
 b = {r["module"]: r for r in P(f"{tag}_module_bw_65536.json")["results"]}
 o = {r["module"]: r for r in P(f"{old}_module_bw_65536.json")["results"]}
 TP = {"SineOsc const": "exact skip-ahead", "PulseOsc const": "exact skip-ahead", "TriSawOsc const": "exact skip-ahead",
-      "Noise white": "exact GF(2) jump", "Noise pink": "exact GF(2) jump + filter replay", "Envelope": "exact skip-ahead",
+      "PulseOsc freq buf": "exact chained integer scan", "Noise white": "exact GF(2) jump", "Noise pink": "exact GF(2) jump + filter replay", "Envelope": "exact skip-ahead",
       "Gate": "stateless", "Filter const": "tolerance: verified warm-up / chain", "Filter cutoff+res buf": "tolerance: verified warm-up / chain",
       "Portamento": "exact skip-ahead", "Decimator": "exact (prefix table of one counter replay per voice)", "Distortion overdrive": "stateless",
       "Distortion clip": "stateless", "Cycle const": "exact skip-ahead"}
