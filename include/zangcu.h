@@ -185,6 +185,9 @@ int zcu_ctx_paint_mode(const zcu_ctx* ctx);
  * sequential loop.  This counter (since context creation; synchronises the stream) tells how often it happened: 0 means
  * every Noise paint so far is bit-identical to the reference loop.  Expected once per 2.2e12 noise samples. */
 int zcu_ctx_noise_resync_count(zcu_ctx* ctx, uint64_t* out);
+/* Host-only (no device): the same jump applied on the CPU, state <- T^n state of xoshiro256 (n < 2^24), for checking the
+ * matrices against n plain steps of the generator. */
+int zcu_xoshiro_jump_host(uint64_t state[4], uint32_t n);
 
 /* device-side timing (CUDA events on the context stream) */
 int zcu_timer_start(zcu_ctx* ctx);

@@ -74,3 +74,21 @@ def test_noise_seed_counter():
     st = oracle.state_init(L.MOD_NOISE, 5, first_seed=10)
     for v in range(5):
         assert [int(x) for x in st["s"][v]] == splitmix(10 + v, 4)
+
+
+def test_jump_matrices_equal_plain_stepping():
+    """The Noise skip-ahead multiplies the xoshiro256 state by T^n (hex-digit matrices built in libzangcu, zcu_paint.cu); the
+    host copy of that product must equal n plain next() calls of the oracle's generator, for n across all digit positions."""
+    import ctypes as C
+    from zang_b200._lib import lib
+    rng = np.random.default_rng(2024)
+    for n in [1, 2, 15, 16, 17, 255, 256, 4095, 4096, 65535, 65536, 99991, (1 << 20) + 12345] + [int(x) for x in rng.integers(1, 1 << 21, size=6)]:
+        s = np.zeros(4, dtype=np.uint64)
+        oracle.orc.orc_xoshiro_seed(int(rng.integers(0, 1 << 32)), L.ptr(s))
+        jumped = s.copy()
+        assert lib.zcu_xoshiro_jump_host(L.ptr(jumped), n) == 0
+        out = np.zeros(n, dtype=np.uint64)
+        oracle.orc.orc_xoshiro_next(L.ptr(s), L.ptr(out), n)  # advances s by n draws
+        assert np.array_equal(jumped, s), n
+    bad = np.zeros(4, dtype=np.uint64)
+    assert lib.zcu_xoshiro_jump_host(L.ptr(bad), 1 << 24) != 0  # beyond the table

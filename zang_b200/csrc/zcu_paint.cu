@@ -57,10 +57,10 @@ void xm_apply(const XMat& m, const uint64_t x[4], uint64_t y[4]) {
 void xm_mul(const XMat& a, const XMat& b, XMat& out) {  // out = a * b (b first)
     for (int j = 0; j < 256; j++) xm_apply(a, b.c[j], out.c[j]);
 }
-int ensure_xjump(zcu_ctx* ctx) {
-    if (ctx->xjump) return ZCU_OK;
-    constexpr int LEVELS = 6, DIGITS = 15;
-    std::vector<XMat> tab((size_t)LEVELS * DIGITS);
+constexpr int kJumpLevels = 6, kJumpDigits = 15;
+void build_xjump(std::vector<XMat>& tab) {
+    constexpr int LEVELS = kJumpLevels, DIGITS = kJumpDigits;
+    tab.resize((size_t)LEVELS * DIGITS);
     XMat p;  // T^(16^k)
     for (int j = 0; j < 256; j++) {
         uint64_t e[4] = {0, 0, 0, 0};
@@ -75,6 +75,11 @@ int ensure_xjump(zcu_ctx* ctx) {
         xm_mul(p, tab[(size_t)k * DIGITS + DIGITS - 1], next);
         p = next;
     }
+}
+int ensure_xjump(zcu_ctx* ctx) {
+    if (ctx->xjump) return ZCU_OK;
+    std::vector<XMat> tab;
+    build_xjump(tab);
     ZCU_CUDA(ctx, cudaMalloc(&ctx->xjump, tab.size() * sizeof(XMat)));
     ZCU_CUDA(ctx, cudaMemcpyAsync(ctx->xjump, tab.data(), tab.size() * sizeof(XMat), cudaMemcpyHostToDevice, ctx->stream));
     ZCU_CUDA(ctx, cudaMalloc((void**)&ctx->xjump_resync, sizeof(unsigned long long)));
@@ -82,6 +87,25 @@ int ensure_xjump(zcu_ctx* ctx) {
     ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // tab is a host temporary
     return ZCU_OK;
 }
+
+}  // namespace
+
+// Host-only check of the jump table (no device needed): state <- T^n state, exactly as NoiseMod::advance_done applies it.
+extern "C" int zcu_xoshiro_jump_host(uint64_t state[4], uint32_t n) {
+    if (!state || n >= (1u << (4 * kJumpLevels))) return ZCU_ERR_INVALID;
+    static std::vector<XMat> tab;
+    if (tab.empty()) build_xjump(tab);
+    for (int k = 0; n != 0; k++, n >>= 4) {
+        const uint32_t d = n & 15u;
+        if (!d) continue;
+        uint64_t y[4];
+        xm_apply(tab[(size_t)k * kJumpDigits + (d - 1)], state, y);
+        for (int q = 0; q < 4; q++) state[q] = y[q];
+    }
+    return ZCU_OK;
+}
+
+namespace {
 
 bool overlaps(const float* a, const float* b, size_t n) { return a && b && a < b + n && b < a + n; }
 

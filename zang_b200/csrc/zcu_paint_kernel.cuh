@@ -143,7 +143,7 @@ template <class M>
 __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames, uint32_t vec4, uint32_t S) {
     extern __shared__ __align__(16) float smem[];
     constexpr uint32_t W = kPaintWarps, RV = 32 * W;  // S = tiles in the cp.async ring (3..8: deeper when few CTAs share an SM)
-    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t tid = threadIdx.x;
     const uint32_t v0 = blockIdx.x * RV;
     const uint32_t v = v0 + tid;
     const bool valid = v < a.V;
