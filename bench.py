@@ -24,9 +24,16 @@ import argparse
 import json
 import os
 
-# NCCL prints its version banner on STDOUT when NCCL_DEBUG is VERSION/INFO; the driver reads one JSON line from stdout
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
-    os.environ["NCCL_DEBUG"] = "WARN"
+# The driver reads ONE JSON line from stdout.  NCCL prints its version banner on stdout (NCCL_DEBUG=VERSION and WARN both do),
+# and other libraries may chat too: file descriptor 1 is pointed at stderr for the whole run and the result line is written
+# to the saved descriptor by emit().
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
 import statistics
 import subprocess
 import sys
@@ -179,7 +186,7 @@ def main():
                            "voices_per_gpu": VOICES_PER_GPU, "note": "CPU reference arm renders a bounded sample of the same workload"},
                 "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": res["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import numpy as np
@@ -375,7 +382,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_reference_run(1, 0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
