@@ -59,7 +59,8 @@ enum {
     /* the delay line and the echo modules built on it (next-row scope) */
     ZCU_MOD_SIMPLE_DELAY = 13,    /* examples/modules.zig:341-388 over src/zang/delay.zig:7-91 */
     ZCU_MOD_FILTERED_ECHOES = 14, /* examples/modules.zig:392-460 */
-    ZCU_MOD_COUNT = 15
+    ZCU_MOD_FM_OSCILLATOR = 15,   /* examples/example_fmsynth.zig:26-89: sine with two-sample feedback */
+    ZCU_MOD_COUNT = 16
 };
 
 /* ---- opaque handles ----------------------------------------------------------------------- */
@@ -101,6 +102,7 @@ typedef struct { float dval, dcount; } zcu_decimator_state;     /* Decimator.zig
 typedef struct { float t; } zcu_cycle_state;                    /* Cycle.zig:14 */
 /* zang.Delay (delay.zig:9-10): the index; the delay_buffer itself lives in the bank ([delay_samples][voices] f32) */
 typedef struct { uint32_t index; } zcu_delay_state;
+typedef struct { float t, feedback1, feedback2; } zcu_fm_oscillator_state; /* example_fmsynth.zig:37-39 */
 typedef struct { uint32_t index; float l, b; } zcu_echoes_state; /* FilteredEchoes: Delay + Filter (modules.zig:403-404) */
 
 enum { ZCU_ENV_IDLE = 0, ZCU_ENV_ATTACK = 1, ZCU_ENV_DECAY = 2, ZCU_ENV_SUSTAIN = 3, ZCU_ENV_RELEASE = 4 };
@@ -146,6 +148,7 @@ typedef struct { float sample_rate, fake_sample_rate; } zcu_decimator_params;   
 enum { ZCU_DIST_OVERDRIVE = 0, ZCU_DIST_CLIP = 1 };
 typedef struct { int32_t type; float ingain, outgain, offset; } zcu_distortion_params;   /* Distortion.zig:13-19 */
 typedef struct { float sample_rate, speed; } zcu_cycle_params;                            /* Cycle.zig:9-12 */
+typedef struct { float sample_rate; uint32_t waveform; float feedback; } zcu_fm_oscillator_params; /* example_fmsynth.zig:29-35 (freq, phase = buffer args) */
 typedef struct { float feedback_volume, cutoff; } zcu_echoes_params;                      /* modules.zig:396-400 (input = buffer arg) */
 
 /* ---- library / context --------------------------------------------------------------------- */
@@ -289,6 +292,12 @@ int zcu_paint_simple_delay(zcu_ctx*, zcu_bank*, const zcu_spans*, zcu_buf* out, 
  * back into the delay line.  The reference's temps never exist: one pass, one read of input, one read-modify-write of out. */
 int zcu_paint_filtered_echoes(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_echoes_params*, uint32_t nparams,
                               zcu_buf* out, const zcu_buf* input);
+
+/* fmsynth Oscillator.paint (examples/example_fmsynth.zig:49-88): out += wave(sin((t + phase) * pi * 2 + (fb1 + fb2) * feedback)),
+ * t += freq[i] / sample_rate, the last two output samples fed back.  A nonlinear recurrence: one thread per voice, sequential
+ * in time.  freq is required (a slice in the reference), phase may be NULL (= 0).  waveform 0..3 as :71-76. */
+int zcu_paint_fm_oscillator(zcu_ctx*, zcu_bank*, const zcu_spans*, const zcu_fm_oscillator_params*, uint32_t nparams,
+                            zcu_buf* out, const zcu_buf* freq, const zcu_buf* phase);
 
 /* Filter.cutoffFromFrequency (Filter.zig:20-23): host scalar, f32 arithmetic */
 float zcu_filter_cutoff_from_frequency(float frequency, float sample_rate);

@@ -115,4 +115,40 @@ struct StereoEchoes {
     }
 };
 
+// examples/example_fmsynth.zig:26-89 (Oscillator): parity unpinned like every paint(); `sin` = glibc sinf
+struct FmOscillator {
+    struct Params {
+        float sample_rate;
+        unsigned waveform;  // u2
+        const float* freq;
+        const float* phase;  // may be null
+        float feedback;
+    };
+    float t = 0.0f, feedback1 = 0.0f, feedback2 = 0.0f;
+    void paint(Span span, float* out0, bool, const Params& p) {
+        float* output = out0 + span.start;
+        const size_t len = span.end - span.start;
+        float tt = t;
+        const float inv_sample_rate = 1.0f / p.sample_rate;  // :66
+        for (size_t i = 0; i < len; i++) {
+            const float phase = p.phase ? p.phase[span.start + i] : 0.0f;
+            const float feedback = (feedback1 + feedback2) * p.feedback;  // :70
+            const float pp = (tt + phase) * kPi * 2.0f + feedback;        // :72
+            const float s = sinf(pp);
+            float sample;
+            switch (p.waveform & 3u) {  // :74-79
+                case 0: sample = s; break;
+                case 1: sample = s > 0.0f ? s : 0.0f; break;
+                case 2: sample = fabsf(s); break;
+                default: sample = sinf(pp * 2.0f) >= 0.0f ? fabsf(s) : 0.0f; break;
+            }
+            output[i] += sample;
+            tt += p.freq[span.start + i] * inv_sample_rate;  // :83
+            feedback2 = feedback1;
+            feedback1 = sample;
+        }
+        t = tt - truncf(tt);  // :63 (defer)
+    }
+};
+
 }  // namespace zo

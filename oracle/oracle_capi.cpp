@@ -256,6 +256,19 @@ int orc_paint(int kind, uint32_t V, uint32_t frames, const uint32_t* off, const 
                     m.paint(sp, o.data(), nic, {p.sample_rate, in0 ? buffer(i0.data()) : constant(p.speed)});
                     st.t = m.t;
                 } break;
+                case ZCU_MOD_FM_OSCILLATOR: {
+                    auto& st = ((zcu_fm_oscillator_state*)state)[v];
+                    const auto& p = ((const zcu_fm_oscillator_params*)params)[zs.param];
+                    if (!in0) return 3;
+                    FmOscillator m;
+                    m.t = st.t;
+                    m.feedback1 = st.feedback1;
+                    m.feedback2 = st.feedback2;
+                    m.paint(sp, o.data(), nic, {p.sample_rate, p.waveform, i0.data(), in1 ? i1.data() : nullptr, p.feedback});
+                    st.t = m.t;
+                    st.feedback1 = m.feedback1;
+                    st.feedback2 = m.feedback2;
+                } break;
                 default: return 1;
             }
             co.scatter(s, e, o.data());
@@ -363,6 +376,7 @@ int orc_state_init(int kind, uint32_t V, uint32_t first_seed, void* state) {
             case ZCU_MOD_SAMPLER: ((zcu_sampler_state*)state)[v] = {0.0f}; break;
             case ZCU_MOD_DECIMATOR: ((zcu_decimator_state*)state)[v] = {0.0f, 1.0f}; break;
             case ZCU_MOD_CYCLE: ((zcu_cycle_state*)state)[v] = {0.0f}; break;
+            case ZCU_MOD_FM_OSCILLATOR: ((zcu_fm_oscillator_state*)state)[v] = {0.0f, 0.0f, 0.0f}; break;
             case ZCU_MOD_GATE:
             case ZCU_MOD_DISTORTION: break;
             default: return 1;

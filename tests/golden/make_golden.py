@@ -121,6 +121,15 @@ def delay_cases():
     o = np.zeros((8, 1), dtype=np.float32)
     oracle.paint_delay(L.MOD_SIMPLE_DELAY, off, spans, None, st, line, o, np.arange(1, 9, dtype=np.float32).reshape(8, 1))
     out["simple_delay_3_literal"] = [float(v) for v in o[:, 0]]
+    # fmsynth Oscillator (examples/example_fmsynth.zig:26-89): libm sinf per sample, hashed after rounding to 1e-5
+    V, NB, BF = 4, 3, 64
+    off, spans = random_spans(rng, V, NB, BF, 4)
+    params = np.array([(48000.0, w, 0.1 * w) for w in range(4)], dtype=L.param_dtypes[L.MOD_FM_OSCILLATOR])
+    st = oracle.state_init(L.MOD_FM_OSCILLATOR, V)
+    o = np.zeros((NB * BF, V), dtype=np.float32)
+    freq = np.full((NB * BF, V), 440.0, dtype=np.float32) * np.arange(1, V + 1, dtype=np.float32)
+    oracle.paint(L.MOD_FM_OSCILLATOR, off, spans, params, st, o, freq, None)
+    out["fm_oscillator"] = digest(np.round(o.astype(np.float64), 5).astype(np.float32), st["t"])
     return out
 
 

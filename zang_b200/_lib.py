@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("ZANGCU_LIB", os.path.join(_HERE, "libzangcu.so"))  # 
 # ---- error codes / enums (zangcu.h) ---------------------------------------------------------------
 OK, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_OOM, ERR_UNSUPPORTED, ERR_NCCL = range(7)
 (MOD_SINE_OSC, MOD_PULSE_OSC, MOD_TRISAW_OSC, MOD_NOISE, MOD_ENVELOPE, MOD_GATE, MOD_FILTER, MOD_PORTAMENTO,
- MOD_CURVE, MOD_SAMPLER, MOD_DECIMATOR, MOD_DISTORTION, MOD_CYCLE, MOD_SIMPLE_DELAY, MOD_FILTERED_ECHOES) = range(15)
+ MOD_CURVE, MOD_SAMPLER, MOD_DECIMATOR, MOD_DISTORTION, MOD_CYCLE, MOD_SIMPLE_DELAY, MOD_FILTERED_ECHOES, MOD_FM_OSCILLATOR) = range(16)
 SPAN_NOTE_ID_CHANGED = 1
 ENV_IDLE, ENV_ATTACK, ENV_DECAY, ENV_SUSTAIN, ENV_RELEASE = range(5)
 CURVE_INSTANTANEOUS, CURVE_LINEAR, CURVE_SQUARED, CURVE_CUBED = range(4)
@@ -46,6 +46,7 @@ state_dtypes = {
     MOD_SAMPLER: np.dtype([("t", "<f4")]),
     MOD_DECIMATOR: np.dtype([("dval", "<f4"), ("dcount", "<f4")]),
     MOD_CYCLE: np.dtype([("t", "<f4")]),
+    MOD_FM_OSCILLATOR: np.dtype([("t", "<f4"), ("feedback1", "<f4"), ("feedback2", "<f4")]),
     MOD_SIMPLE_DELAY: np.dtype([("index", "<u4")]),
     MOD_FILTERED_ECHOES: np.dtype([("index", "<u4"), ("l", "<f4"), ("b", "<f4")]),
     MOD_GATE: None,
@@ -67,6 +68,7 @@ param_dtypes = {
     MOD_DECIMATOR: np.dtype([("sample_rate", "<f4"), ("fake_sample_rate", "<f4")]),
     MOD_DISTORTION: np.dtype([("type", "<i4"), ("ingain", "<f4"), ("outgain", "<f4"), ("offset", "<f4")]),
     MOD_CYCLE: np.dtype([("sample_rate", "<f4"), ("speed", "<f4")]),
+    MOD_FM_OSCILLATOR: np.dtype([("sample_rate", "<f4"), ("waveform", "<u4"), ("feedback", "<f4")]),
     MOD_SIMPLE_DELAY: np.dtype([("unused", "<u4")]),
     MOD_FILTERED_ECHOES: np.dtype([("feedback_volume", "<f4"), ("cutoff", "<f4")]),
 }
@@ -186,6 +188,7 @@ PROTOTYPES = {
     "zcu_paint_decimator": (_I, [_P, _P, _P, _P, _U, _P, _P]),
     "zcu_paint_distortion": (_I, [_P, _P, _P, _U, _P, _P]),
     "zcu_paint_cycle": (_I, [_P, _P, _P, _P, _U, _P, _P]),
+    "zcu_paint_fm_oscillator": (_I, [_P, _P, _P, _P, _U, _P, _P, _P]),
     "zcu_paint_simple_delay": (_I, [_P, _P, _P, _P, _P]),
     "zcu_paint_filtered_echoes": (_I, [_P, _P, _P, _P, _U, _P, _P]),
     "zcu_filter_cutoff_from_frequency": (_F, [_F, _F]),

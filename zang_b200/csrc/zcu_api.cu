@@ -198,6 +198,7 @@ size_t zcu_bank_state_size(int kind) {
         case ZCU_MOD_SAMPLER: return sizeof(zcu_sampler_state);
         case ZCU_MOD_DECIMATOR: return sizeof(zcu_decimator_state);
         case ZCU_MOD_CYCLE: return sizeof(zcu_cycle_state);
+        case ZCU_MOD_FM_OSCILLATOR: return sizeof(zcu_fm_oscillator_state);
         case ZCU_MOD_SIMPLE_DELAY: return sizeof(zcu_delay_state);
         case ZCU_MOD_FILTERED_ECHOES: return sizeof(zcu_echoes_state);
         default: return 0;  // Gate, Distortion: stateless
@@ -491,6 +492,10 @@ int zcu_paint_cycle(zcu_ctx* c, zcu_bank* b, const zcu_spans* s, const zcu_cycle
     return paint_call(c, ZCU_MOD_CYCLE, b, s, p, sizeof *p, n, out, speed, nullptr, nullptr, false, nullptr, 0, nullptr);
 }
 
+int zcu_paint_fm_oscillator(zcu_ctx* c, zcu_bank* b, const zcu_spans* s, const zcu_fm_oscillator_params* p, uint32_t n, zcu_buf* out,
+                            const zcu_buf* freq, const zcu_buf* phase) {
+    return paint_call(c, ZCU_MOD_FM_OSCILLATOR, b, s, p, sizeof *p, n, out, freq, phase, nullptr, true, nullptr, 0, nullptr);
+}
 int zcu_paint_simple_delay(zcu_ctx* c, zcu_bank* b, const zcu_spans* s, zcu_buf* out, const zcu_buf* input) {
     // SimpleDelay.Params holds nothing but the input slice (modules.zig:345-347): whatever rows the spans name are empty
     const std::vector<uint32_t> rows(s ? (size_t)s->max_param + 1 : 1, 0u);

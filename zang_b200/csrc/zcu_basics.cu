@@ -265,6 +265,11 @@ __global__ void k_bank_init(int kind, void* state, uint32_t V, uint32_t first_se
             ((zcu_decimator_state*)state)[v] = s;
         } break;
         case ZCU_MOD_CYCLE: ((zcu_cycle_state*)state)[v].t = 0.0f; break;
+        case ZCU_MOD_FM_OSCILLATOR: {
+            zcu_fm_oscillator_state s;
+            s.t = s.feedback1 = s.feedback2 = 0.0f;
+            ((zcu_fm_oscillator_state*)state)[v] = s;
+        } break;
         case ZCU_MOD_SIMPLE_DELAY: ((zcu_delay_state*)state)[v].index = 0; break;  // delay.zig:12-17
         case ZCU_MOD_FILTERED_ECHOES: {
             zcu_echoes_state s;

@@ -256,6 +256,7 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
         case ZCU_MOD_SAMPLER: return launch<SamplerMod>(ctx, a, pl.kind);
         case ZCU_MOD_DECIMATOR: return launch<DecimatorMod>(ctx, a, pl.kind);
         case ZCU_MOD_DISTORTION: return launch<DistortionMod>(ctx, a, pl.kind);
+        case ZCU_MOD_FM_OSCILLATOR: return b1 ? launch<FmOscMod<true>>(ctx, a, pl.kind) : launch<FmOscMod<false>>(ctx, a, pl.kind);
         case ZCU_MOD_SIMPLE_DELAY: return launch<SimpleDelayMod>(ctx, a, pl.kind);
         case ZCU_MOD_FILTERED_ECHOES: return launch<FilteredEchoesMod>(ctx, a, pl.kind);
         case ZCU_MOD_CYCLE: return b0 ? launch<CycleMod<true>>(ctx, a, pl.kind) : launch<CycleMod<false>>(ctx, a, pl.kind);

@@ -403,6 +403,15 @@ class Cycle(_Module):
         _check(self.ctx, lib.zcu_paint_cycle(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(speed)))
 
 
+class FmOscillator(_Module):
+    """examples/example_fmsynth.zig:26-89: Params = {sample_rate, waveform, freq (buffer), phase (buffer or None), feedback}."""
+    kind = L.MOD_FM_OSCILLATOR
+
+    def paint(self, spans, outputs, temps, params, freq, phase=None):
+        p = _params(self.kind, params)
+        _check(self.ctx, lib.zcu_paint_fm_oscillator(self.ctx._h, self._bh(), spans._h, ptr(p), p.size, outputs[0]._h, _h(freq), _h(phase)))
+
+
 class DelayBank(Bank):
     """zang.Delay(delay_samples).init() for every voice (src/zang/delay.zig:7-17): index POD + a zeroed delay line per voice."""
 
