@@ -58,7 +58,7 @@ def main():
     ap.add_argument("--voices", default="4096,65536")
     ap.add_argument("--buffers", type=int, default=8)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--only", default="", help="substring filter on the module name")
+    ap.add_argument("--only", default="", help="comma-separated substring filters on the module name")
     ap.add_argument("--tolerance", action="store_true", help="ZCU_PAINT_TOLERANCE: Filter cut into verified time segments")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "module_bw.json"))
     args = ap.parse_args()
@@ -88,7 +88,7 @@ def main():
         del host
         smp = None
         for name, kind, bps, prow, inputs in module_cases():
-            if args.only and args.only not in name:
+            if args.only and not any(o in name for o in args.only.split(",")):
                 continue
             mod = E.MODULE_CLASSES[kind](ctx, V)
             kw = {k: ins[k] for k in inputs}
@@ -98,6 +98,46 @@ def main():
                 ctx.zero(None, out)
                 ctx.timer_start()
                 mod.paint(sp, [out], [], prow, **kw)
+                ms = ctx.timer_stop_ms()
+                if rep > 0:
+                    ms_best = min(ms_best, ms)
+            vs = V * frames / (ms_best * 1e-3)
+            gbs = vs * bps / 1e9
+            results.append(dict(module=name, voices=V, frames=frames, ms=ms_best, voice_samples_per_s=vs, bytes_per_voice_sample=bps, gbs=gbs, frac_of_peak=gbs / peak))
+            print(f"V={V:6d} {name:26s} {ms_best:9.3f} ms  {vs:10.3e} vs/s  {gbs:8.1f} GB/s  {gbs / peak:6.3f} of {peak:.0f}", flush=True)
+        # modules with extra arguments (nodes, PCM table, delay lines): same timing, explicit calls
+        from zang_b200 import synth
+        pcm = ctx.sample(synth.pcm_loop(), 1, 44100, L.FMT_SIGNED16_LSB)
+        nodes = np.array([(1000.0, 0.0), (200.0, 0.1), (100.0, 0.2), (400.0, 5.0)], dtype=L.curve_node_dtype)
+        curve = E.Curve(ctx, V)
+        smp = E.Sampler(ctx, V)
+        sdel = E.SimpleDelay(ctx, V, 7500)
+        fecho = E.FilteredEchoes(ctx, V, 15000)
+        sdel2 = E.SimpleDelay(ctx, V, 15000) if "SimpleDelay 15000" in args.only else None
+        fmo = E.FmOscillator(ctx, V)
+
+        def prow(kind, **kw):
+            p = np.zeros(1, dtype=L.param_dtypes[kind])
+            for k, v in kw.items():
+                p[k] = v
+            return p
+        custom = [
+            ("Curve smoothstep", 8, lambda: curve.paint(sp, [out], [], prow(L.MOD_CURVE, sample_rate=SR, function=L.INTERP_SMOOTHSTEP, node_start=0, node_count=4), nodes)),
+            ("Sampler resample x0.73", 8, lambda: smp.paint(sp, [out], [], prow(L.MOD_SAMPLER, sample_rate=44100.0 / 0.73, channel=0, loop=1), pcm)),
+            ("SimpleDelay 7500", 20, lambda: sdel.paint(sp, [out], [], ins["input"])),
+            ("SimpleDelay 15000", 20, (lambda: sdel2.paint(sp, [out], [], ins["input"])) if sdel2 else None),
+            ("FilteredEchoes 15000", 20, lambda: fecho.paint(sp, [out], [], prow(L.MOD_FILTERED_ECHOES, feedback_volume=0.6, cutoff=0.1), ins["input"])),
+            ("FmOscillator freq buf", 12, lambda: fmo.paint(sp, [out], [], prow(L.MOD_FM_OSCILLATOR, sample_rate=SR, waveform=0, feedback=0.2), ins["freq"], None)),
+        ]
+        for name, bps, fn in custom:
+            if fn is None or (args.only and not any(o in name for o in args.only.split(","))):
+                continue
+            ms_best = 1e30
+            for rep in range(args.reps + 1):
+                ctx.zero(None, flush)
+                ctx.zero(None, out)
+                ctx.timer_start()
+                fn()
                 ms = ctx.timer_stop_ms()
                 if rep > 0:
                     ms_best = min(ms_best, ms)

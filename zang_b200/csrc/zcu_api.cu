@@ -230,7 +230,7 @@ int zcu_delay_bank_create(zcu_ctx* ctx, int kind, uint32_t voices, uint32_t dela
     if (!ctx || !out) return ZCU_ERR_INVALID;
     *out = nullptr;
     ZCU_REQUIRE(ctx, kind == ZCU_MOD_SIMPLE_DELAY || kind == ZCU_MOD_FILTERED_ECHOES, "not a delay module kind");
-    ZCU_REQUIRE(ctx, delay_samples > 0, "delay_samples must be > 0");
+    ZCU_REQUIRE(ctx, delay_samples > 0 && delay_samples < 0x80000000u, "delay_samples must be in 1 .. 2^31-1");
     zcu_bank* b = new zcu_bank{ctx, kind, voices, nullptr, zcu_bank_state_size(kind)};
     b->delay_samples = delay_samples;
     const size_t bytes = b->stride * voices, lbytes = (size_t)delay_samples * voices * sizeof(float);
