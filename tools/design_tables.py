@@ -15,7 +15,9 @@ TP = {"SineOsc const": "exact skip-ahead", "PulseOsc const": "exact skip-ahead",
       "PulseOsc freq buf": "exact chained integer scan", "Noise white": "exact GF(2) jump", "Noise pink": "exact GF(2) jump + filter replay", "Envelope": "exact skip-ahead",
       "Gate": "stateless", "Filter const": "tolerance: verified warm-up / chain", "Filter cutoff+res buf": "tolerance: verified warm-up / chain",
       "Portamento": "exact skip-ahead", "Decimator": "exact (prefix table of one counter replay per voice)", "Distortion overdrive": "stateless",
-      "Distortion clip": "stateless", "Cycle const": "exact skip-ahead"}
+      "Distortion clip": "stateless", "Cycle const": "exact skip-ahead", "Curve smoothstep": "no (per-call node bookkeeping)",
+      "Sampler resample x0.73": "exact skip-ahead", "SimpleDelay 7500": "no (the line is carried state)",
+      "FilteredEchoes 15000": "no (feedback through the line)", "FmOscillator freq buf": "no (nonlinear feedback recurrence)"}
 print(f"| module (variant) | B / voice-sample | 4096 voices x 64 buffers: GB/s (of peak) | 65536 voices x 8 buffers: GB/s (of peak) | {old} | time-parallel |")
 print("|---|---|---|---|---|---|")
 for r in a:
@@ -23,7 +25,7 @@ for r in a:
     if m.startswith("basics"):
         continue
     x = b[m]
-    print(f"| {m} | {r['bytes_per_voice_sample']} | {r['gbs']:.0f} ({r['frac_of_peak']:.2f}) | {x['gbs']:.0f} ({x['frac_of_peak']:.2f}) | {o[m]['frac_of_peak']:.2f} | {TP.get(m, 'no (one segment)')} |")
+    print(f"| {m} | {r['bytes_per_voice_sample']} | {r['gbs']:.0f} ({r['frac_of_peak']:.2f}) | {x['gbs']:.0f} ({x['frac_of_peak']:.2f}) | {(f"{o[m]['frac_of_peak']:.2f}" if m in o else "-")} | {TP.get(m, 'no (one segment)')} |")
 print()
 print("basics @65536:", ", ".join(f"{m.split('.')[1]} {r['gbs']:.0f}" for m, r in b.items() if m.startswith("basics")))
 print()
