@@ -55,7 +55,9 @@ ZCU_HD float ea_add(float a, float b) {
 //   STOP   stop after the add that makes t >= 1 (*finished = true); CLAMP additionally sets t = 1 then
 //          (painter.zig:102-106).  Without STOP every one of the n adds is performed (SineOsc.zig:49-62, Sampler.zig:130).
 // Returns the number of adds performed.
-template <bool STOP, bool CLAMP>
+//   ONE    return after the first piece (one in-binade jump or one real add): the table builder of the bank render's
+//          pre-pass walks a ramp piece by piece with it (zcu_render_scan.cuh, RampTab).
+template <bool STOP, bool CLAMP, bool ONE = false>
 ZCU_HD uint32_t accum_core(float& t, float step, uint32_t n, bool& finished) {
     finished = false;
     uint32_t done = 0;
@@ -108,12 +110,16 @@ ZCU_HD uint32_t accum_core(float& t, float step, uint32_t n, bool& finished) {
                 return done;
             }
         }
+        if (ONE) return done;
     }
     return done;
 }
 
 // Painter's ramp clock: `t += step; if (t >= 1) { t = 1; finished }` up to n times, stopping after the add that finishes.
 ZCU_HD uint32_t ramp_advance(float& t, float step, uint32_t n, bool& finished) { return accum_core<true, true>(t, step, n, finished); }
+
+// the first piece of the same walk: up to n adds inside t's binade in one jump, or one real add
+ZCU_HD uint32_t ramp_advance_piece(float& t, float step, uint32_t n, bool& finished) { return accum_core<true, true, true>(t, step, n, finished); }
 
 // n plain adds (SineOsc's and Sampler's phase between the wraps at the end of a paint call)
 ZCU_HD void accum_advance(float& t, float step, uint32_t n) {

@@ -538,8 +538,9 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
         p.events = r->d_events;
         p.snaps = r->d_snaps;
         p.cursor = r->d_cursor;
+        k_nice_cursor<<<(V + 3) / 4, 128, 0, ctx->stream>>>(p);
         k_nice_prepass<<<(V + 63) / 64, 64, 0, ctx->stream>>>(p);
-        ctx->launches++;
+        ctx->launches += 2;
         ZCU_CUDA(ctx, cudaGetLastError());
     }
     return ZCU_OK;
