@@ -168,6 +168,39 @@ def test_envelope_named_edges(ctx):
     assert state_equal(mod.bank.get_state(), ostate)
 
 
+def test_envelope_time_segments_ramp_tables(ctx):
+    """A long block is painted as time segments whose skip-ahead over the earlier spans reads the Painter's exact ramp clock
+    from per-step tables (zcu_modules.cuh RampTab, built on the host by zcu_envelope_ramp_tabs): ramps caught in the middle
+    by a segment start, by a continued span (same note, no new curve) and by a retrigger; six distinct ramp steps, so two of
+    them have no table and take the binade walk.  Bit-exact against the sequential loop, carried state included."""
+    Vn, NB, bf = 150, 64, 1024
+    frames = NB * bf
+    rng = np.random.default_rng(77)
+    rows = np.zeros(8, dtype=L.param_dtypes[L.MOD_ENVELOPE])
+    rows["sample_rate"] = SR
+    rows["attack"] = (L.CURVE_CUBED, 0.01)
+    rows["decay"] = (L.CURVE_CUBED, 0.1)
+    rows["release"] = (L.CURVE_CUBED, 0.5)
+    rows["sustain_volume"] = 0.8
+    rows["note_on"] = [1, 0, 1, 0, 1, 0, 1, 0]
+    rows[2]["attack"] = rows[3]["attack"] = (L.CURVE_SQUARED, 0.3)    # a slow attack: segment starts land inside it
+    rows[4]["decay"] = rows[5]["decay"] = (L.CURVE_LINEAR, 0.9)
+    rows[6]["release"] = rows[7]["release"] = (L.CURVE_LINEAR, 2.0)  # fifth and sixth distinct steps: no table
+    rows[6]["attack"] = rows[7]["attack"] = (L.CURVE_LINEAR, 0.07)
+    off, spans = random_spans(rng, Vn, NB, bf, 8, max_cuts=2, p_empty=0.15, p_gap=0.3)
+    want = np.zeros((frames, Vn), dtype=np.float32)
+    ostate = oracle.state_init(L.MOD_ENVELOPE, Vn)
+    oracle.paint(L.MOD_ENVELOPE, off, spans, rows, ostate, want)
+    assert want.max() > 0.7
+    mod = E.Envelope(ctx, Vn)
+    d_out = ctx.buf(frames, Vn)
+    sp = ctx.spans(Vn, frames, off, spans)
+    mod.paint(sp, [d_out], [], rows)
+    assert_bit_exact(d_out.download(), want, "envelope in time segments")
+    assert state_equal(mod.bank.get_state(), ostate)
+    d_out.free()
+
+
 def test_paint_argument_errors(ctx):
     """Error behaviour of the boundary: int codes, never an abort."""
     from zang_b200._lib import lib, ptr

@@ -411,6 +411,10 @@ static int paint_call(zcu_ctx* ctx, int kind, zcu_bank* bank, const zcu_spans* s
     pl.off = sp->d_off;
     pl.spans = sp->d_spans;
     pl.params = dparams;
+    if (kind == ZCU_MOD_ENVELOPE && out->frames >= 8192) {  // long blocks run as time segments that skip ahead
+        rc = zcu_envelope_ramp_tabs(ctx, (const zcu_envelope_params*)params, nparams, &pl.ramp_tabs, &pl.n_ramp_tabs);
+        if (rc) return rc;
+    }
     pl.state = bank ? bank->d : nullptr;
     pl.out = out->d;
     pl.in0 = in0 ? in0->d : nullptr;

@@ -103,6 +103,8 @@ struct PaintLaunch {
     const uint32_t* off;
     const zcu_span* spans;
     const void* params;
+    const void* ramp_tabs;  // Envelope (zcu_envelope_ramp_tabs)
+    uint32_t n_ramp_tabs;
     void* state;
     float* out;
     const float* in0;
@@ -116,6 +118,9 @@ struct PaintLaunch {
     uint32_t delay_samples;
 };
 int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl);
+// Envelope: exact ramp-clock tables (RampTab, zcu_modules.cuh) of up to 4 distinct Painter steps named by the first rows,
+// built once per step value (process-wide cache), uploaded stream-ordered; *dev stays null when no row has a ramp
+int zcu_envelope_ramp_tabs(zcu_ctx* ctx, const zcu_envelope_params* rows, uint32_t nrows, const void** dev, uint32_t* count);
 int zcu_launch_basic(zcu_ctx* ctx, int op, const zcu_spans* spans, zcu_buf* dest, const zcu_buf* a, const zcu_buf* b, float scalar);
 int zcu_launch_basic_rows(zcu_ctx* ctx, int op, const zcu_spans* spans, zcu_buf* dest, const zcu_buf* a, const float* rows, uint32_t nrows);
 int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed);

@@ -1,6 +1,9 @@
 // zcu_paint.cu — instantiation and launch of the lockstep paint kernel for every module variant.
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
+#include <map>
+#include <mutex>
 #include <type_traits>
 #include <vector>
 
@@ -209,6 +212,48 @@ void zcu_paint_segments(const zcu_ctx* ctx, uint32_t voices, uint32_t frames, in
     *seg_frames_out = seg_frames;
 }
 
+int zcu_envelope_ramp_tabs(zcu_ctx* ctx, const zcu_envelope_params* rows, uint32_t nrows, const void** dev, uint32_t* count) {
+    static std::mutex mu;
+    static std::map<uint32_t, RampTab> cache;  // a table depends on the bits of its step alone
+    *dev = nullptr;
+    *count = 0;
+    uint32_t steps[4];
+    uint32_t ns = 0;
+    for (uint32_t r = 0; r < std::min(nrows, 64u); r++) {
+        const zcu_painter_curve cv[3] = {rows[r].attack, rows[r].decay, rows[r].release};
+        for (const zcu_painter_curve& c : cv) {
+            if (c.kind == ZCU_CURVE_INSTANTANEOUS) continue;
+            volatile float prod = c.duration * rows[r].sample_rate;  // PainterDev::try_ramp, two roundings
+            const float step = 1.0f / prod;
+            const uint32_t sb = ea_bits(step);
+            if (!(step > 0.0f) || !std::isfinite(step)) continue;
+            if (std::find(steps, steps + ns, sb) != steps + ns) continue;
+            if (ns < 4) steps[ns++] = sb;
+        }
+    }
+    if (ns == 0) return ZCU_OK;
+    std::vector<RampTab> host(ns);
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        for (uint32_t i = 0; i < ns; i++) {
+            auto it = cache.find(steps[i]);
+            if (it == cache.end()) {
+                if (cache.size() > 4096) cache.clear();
+                RampTab t;
+                t.build(ea_float(steps[i]));
+                it = cache.emplace(steps[i], t).first;
+            }
+            host[i] = it->second;
+        }
+    }
+    void* d = nullptr;
+    int rc = zcu_arena_upload(ctx, 3, host.data(), ns * sizeof(RampTab), &d);
+    if (rc) return rc;
+    *dev = d;
+    *count = ns;
+    return ZCU_OK;
+}
+
 int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     PaintArgs a;
     a.V = pl.V;
@@ -216,6 +261,8 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     a.off = pl.off;
     a.spans = pl.spans;
     a.params = pl.params;
+    a.ramp_tabs = (const RampTab*)pl.ramp_tabs;
+    a.n_ramp_tabs = pl.n_ramp_tabs;
     a.state = pl.state;
     a.out = pl.out;
     a.in0 = pl.in0;

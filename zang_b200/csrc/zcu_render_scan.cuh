@@ -106,84 +106,6 @@ struct PrepassArgs {
     uint32_t* cursor;
 };
 
-// A Painter ramp always starts at t = 0 (painter.zig:47-50) and NiceInstrument's three ramps have fixed steps, so the exact
-// clock after i adds is a function of (step, i) alone.  The pre-pass builds that function once per step as the list of pieces
-// the exact walk takes (zcu_exact_accum.cuh: in-binade jumps with a constant significand increment, single real adds) and
-// then advances a ramp by a table lookup instead of re-walking ~30 binades per note event (ncu: the walk and the cursor
-// loop were 3500 warp instructions per event on a one-warp-per-SM critical path, 2.4 ms per job).
-constexpr int kRampSegs = 96;
-struct RampTab {
-    uint32_t step_bits;
-    uint32_t nseg;  // 0: no table (the walk did not fit or never finishes): callers fall back to ramp_advance
-    uint32_t N;     // adds from t = 0 until the ramp finishes (t clamped to 1)
-    uint32_t i0[kRampSegs], tb[kRampSegs], d[kRampSegs];  // adds done / bits of t at the piece start, bits increment per add
-    __device__ void build(float step) {
-        step_bits = __float_as_uint(step);
-        nseg = 0;
-        N = 0;
-        float t = 0.0f;
-        uint32_t i = 0;
-        for (int s = 0; s < kRampSegs; s++) {
-            const uint32_t b0 = __float_as_uint(t);
-            bool fin = false;
-            const uint32_t room = 0x7FFFFFFFu - i;
-            const uint32_t k = ramp_advance_piece(t, step, room, fin);
-            if (k == 0 || k >= room) return;  // never finishes
-            i0[s] = i;
-            tb[s] = b0;
-            d[s] = (!fin && k > 1) ? (__float_as_uint(t) - b0) / k : 0u;
-            i += k;
-            if (fin) {
-                N = i;
-                nseg = (uint32_t)s + 1;
-                return;
-            }
-        }
-    }
-    // t after i adds from 0, 0 < i < N
-    __device__ __forceinline__ float at(uint32_t i) const {
-        uint32_t lo = 0, hi = nseg;  // last piece with i0 <= i
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (i0[mid] <= i)
-                lo = mid;
-            else
-                hi = mid;
-        }
-        return __uint_as_float(tb[lo] + (i - i0[lo]) * d[lo]);
-    }
-};
-
-// env_advance (zcu_modules.cuh) with the ramp clock read from the tables; ri = adds done on the current curve
-__device__ inline void env_advance_tab(EnvelopeCore& e, uint32_t& ri, uint32_t n, const RampTab* tabs) {
-    while (n > 0) {
-        if (e.mode != EnvelopeCore::M_RAMP_ON && e.mode != EnvelopeCore::M_RAMP_OFF) return;
-        if (e.painter.t == 0.0f) ri = 0;
-        const uint32_t sb = __float_as_uint(e.painter.t_step);
-        const RampTab* T = nullptr;
-#pragma unroll
-        for (int j = 0; j < 3; j++)
-            if (tabs[j].nseg != 0 && tabs[j].step_bits == sb) T = &tabs[j];
-        bool finished = false;
-        uint32_t k;
-        if (T == nullptr || ri >= T->N) {
-            k = ramp_advance(e.painter.t, e.painter.t_step, n, finished);
-            ri += k;
-        } else if (n >= T->N - ri) {
-            k = T->N - ri;
-            e.painter.t = 1.0f;
-            finished = true;
-        } else {
-            k = n;
-            ri += n;
-            e.painter.t = T->at(ri);
-        }
-        painter_value_at_t(e.painter);
-        n -= k;
-        if (finished) e.on_ramp_finished();
-    }
-}
-
 // cursor[c][v] = index of the voice's first event at or after the start of mix buffer c: one warp per voice, one lane per event
 __global__ void __launch_bounds__(128) k_nice_cursor(PrepassArgs a) {
     const uint32_t v = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
@@ -196,6 +118,8 @@ __global__ void __launch_bounds__(128) k_nice_cursor(PrepassArgs a) {
     }
 }
 
+// The envelope state at every event comes from the ramp tables of zcu_modules.cuh (RampTab): the walk over ~30 binades per
+// event and the cursor loop were 3500 warp instructions per event on a one-warp-per-SM critical path (ncu, 2.4 ms per job).
 __global__ void __launch_bounds__(64) k_nice_prepass(PrepassArgs a) {
     __shared__ RampTab tabs[3];
     if (threadIdx.x < 3) {
@@ -209,7 +133,7 @@ __global__ void __launch_bounds__(64) k_nice_prepass(PrepassArgs a) {
     const uint32_t k0 = a.event_off[v], k1 = a.event_off[v + 1];
     EnvelopeCore e;
     env_reset(e, a.sample_rate);
-    uint32_t cnt = 0, ifreq = 0, note_id = 0, prev_frame = 0, ri = 0;
+    uint32_t cnt = 0, ifreq = 0, note_id = 0, prev_frame = 0;
     bool has_note = false;
     uint4 raw = k0 < k1 ? *reinterpret_cast<const uint4*>(a.events + k0) : make_uint4(0, 0, 0, 0);
     for (uint32_t k = k0; k < k1; k++) {
@@ -220,7 +144,7 @@ __global__ void __launch_bounds__(64) k_nice_prepass(PrepassArgs a) {
         const uint32_t n = frame - prev_frame;
         if (has_note) {
             cnt += n * ifreq;
-            env_advance_tab(e, ri, n, tabs);
+            env_advance_tab(e, n, tabs, 3);
         }
         const bool superseded = (k + 1 < k1) && nxt.x == frame;  // trigger.zig:173-178
         const bool changed = has_note ? (id != note_id) : true;  // trigger.zig:96-100
