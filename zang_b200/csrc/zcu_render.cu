@@ -36,8 +36,12 @@ struct zcu_render {
     NiceVoiceState* d_state;
     uint32_t* d_event_off; // [V+1]
     DevEvent* d_events;    // per event, with Filter.cutoffFromFrequency(freq*8, sr) evaluated on the host
-    DevEvent* h_events;    // pinned staging for the H2D copy
-    uint32_t nevents;
+    DevEvent* h_events[2]; // pinned staging for the H2D copy, double buffered: the host expands the next job's events while
+                           // the device still renders the previous one (only a buffer's own last copy is waited for)
+    cudaEvent_t h_done[2]; // recorded after the copy out of h_events[i]
+    bool h_busy[2];
+    int h_flip;
+    uint32_t nevents, cap_events;
     float* d_partial;      // [nwarps][block_frames][C]
     uint32_t debug_skip_mask;
     unsigned long long* d_debug_cycles;  // [nwarps][4][2], only with ZCU_RENDER_DEBUG_CYCLES=1
@@ -351,11 +355,15 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     zcu_render* r = new (std::nothrow) zcu_render();
     if (!r) return ZCU_ERR_OOM;
     r->d_color = r->d_gains = r->d_partial = nullptr;
-    r->h_events = nullptr;
+    r->h_events[0] = r->h_events[1] = nullptr;
+    r->h_done[0] = r->h_done[1] = nullptr;
+    r->h_busy[0] = r->h_busy[1] = false;
+    r->h_flip = 0;
     r->d_state = nullptr;
     r->d_event_off = nullptr;
     r->d_events = nullptr;
     r->nevents = 0;
+    r->cap_events = 0;
     r->profiling = false;
     r->ev_used = 0;
     r->ev_aux_used = 0;
@@ -444,7 +452,10 @@ void zcu_render_free(zcu_render* r) {
     cudaFree(r->d_state);
     cudaFree(r->d_event_off);
     cudaFree(r->d_events);
-    cudaFreeHost(r->h_events);
+    for (int i = 0; i < 2; i++) {
+        cudaFreeHost(r->h_events[i]);
+        if (r->h_done[i]) cudaEventDestroy(r->h_done[i]);
+    }
     cudaFree(r->d_partial);
     cudaFree(r->d_snaps);
     cudaFree(r->d_cursor);
@@ -468,20 +479,26 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     const uint32_t V = r->cfg.voices;
     const uint32_t n = event_off_host[V];
     ZCU_REQUIRE(ctx, n == 0 || events_host, "null events");
-    if (n > r->nevents || !r->d_events) {
+    if (n > r->cap_events || !r->d_events) {
         ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         cudaFree(r->d_events);
-        cudaFreeHost(r->h_events);
         cudaFree(r->d_snaps);
         r->d_events = nullptr;
-        r->h_events = nullptr;
         r->d_snaps = nullptr;
+        for (int i = 0; i < 2; i++) {
+            cudaFreeHost(r->h_events[i]);
+            r->h_events[i] = nullptr;
+            r->h_busy[i] = false;
+            if (!r->h_done[i]) ZCU_CUDA(ctx, cudaEventCreateWithFlags(&r->h_done[i], cudaEventDisableTiming));
+        }
         if (r->cfg.mode != ZCU_RENDER_EXACT) ZCU_CUDA(ctx, cudaMalloc(&r->d_snaps, (size_t)(n ? n : 1) * sizeof(EnvSnap)));
         ZCU_CUDA(ctx, cudaMalloc(&r->d_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
-        ZCU_CUDA(ctx, cudaMallocHost(&r->h_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
-    } else {
-        ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the staging buffer may still be in flight
+        for (int i = 0; i < 2; i++) ZCU_CUDA(ctx, cudaMallocHost(&r->h_events[i], (size_t)(n ? n : 1) * sizeof(DevEvent)));
+        r->cap_events = n;
     }
+    r->h_flip ^= 1;
+    const int hb = r->h_flip;
+    if (r->h_busy[hb]) ZCU_CUDA(ctx, cudaEventSynchronize(r->h_done[hb]));  // this buffer's copy of two calls ago
     r->nevents = n;
     // per-call host scalar of modules.zig:231-234 (cos, sqrt): once per event, on the host
     // (a small direct-mapped memo keyed by the bits of freq: a bank plays few distinct pitches, and the memo returns
@@ -490,7 +507,7 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     // job a single thread costs more than the H2D copy it feeds.
     struct Memo { uint32_t key; float cutoff; bool valid; };
     const float sr = r->cfg.sample_rate;
-    DevEvent* const staged = r->h_events;
+    DevEvent* const staged = r->h_events[hb];
     auto expand = [events_host, staged, sr](uint32_t i0, uint32_t i1) {
         std::vector<Memo> memo(1024, Memo{0u, 0.0f, false});
         for (uint32_t i = i0; i < i1; i++) {
@@ -527,7 +544,11 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
         for (auto& th : pool) th.join();
     }
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, r->h_events, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
+    if (n) {
+        ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, staged, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
+        ZCU_CUDA(ctx, cudaEventRecord(r->h_done[hb], ctx->stream));
+        r->h_busy[hb] = true;
+    }
     if (r->cfg.mode != ZCU_RENDER_EXACT) {
         PrepassArgs p;
         p.V = V;
