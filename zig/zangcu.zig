@@ -99,6 +99,26 @@ pub fn FilteredEchoesBank(comptime DELAY_SAMPLES: u32) type {
     };
 }
 
+/// The fmsynth example's feedback Oscillator (examples/example_fmsynth.zig:26-89): Params{sample_rate, waveform, freq, phase,
+/// feedback}; freq is a buffer argument (a slice in the reference), phase null stands for the reference's zero phase.
+pub const FmOscillatorBank = struct {
+    pub const num_outputs = 1;
+    pub const num_temps = 0;
+    pub const Params = c.zcu_fm_oscillator_params;
+    ctx: Context,
+    bank: *c.zcu_bank,
+
+    pub fn init(ctx: Context, voices: u32) Error!FmOscillatorBank {
+        var b: ?*c.zcu_bank = null;
+        try check(c.zcu_bank_create(ctx.h, c.ZCU_MOD_FM_OSCILLATOR, voices, 0, &b));
+        return .{ .ctx = ctx, .bank = b.? };
+    }
+    pub fn paint(self: *FmOscillatorBank, spans: *const c.zcu_spans, outputs: [1]Buffer, temps: [0]Buffer, rows: []const Params, freq: Buffer, phase: ?Buffer) Error!void {
+        _ = temps;
+        try check(c.zcu_paint_fm_oscillator(self.ctx.h, self.bank, spans, rows.ptr, @intCast(rows.len), outputs[0].h, freq.h, if (phase) |p| p.h else null));
+    }
+};
+
 /// [frames][voices] f32 device buffer: the batched form of the caller-owned []f32
 pub const Buffer = struct {
     h: *c.zcu_buf,
