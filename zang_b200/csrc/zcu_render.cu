@@ -38,9 +38,23 @@ struct zcu_render {
     DevEvent* d_events;    // per event, with Filter.cutoffFromFrequency(freq*8, sr) evaluated on the host
     DevEvent* h_events[2]; // pinned staging for the H2D copy, double buffered: the host expands the next job's events while
                            // the device still renders the previous one (only a buffer's own last copy is waited for)
-    cudaEvent_t h_done[2]; // recorded after the copy out of h_events[i]
+    uint32_t* h_off[2];    // pinned copy of the caller's event_off (nothing of the caller's is read after the call returns)
+    cudaEvent_t h_done[2]; // recorded after the copies out of h_events[i] / h_off[i]
     bool h_busy[2];
     int h_flip;
+    // The device tables of a job (event_off, events, snaps, cursor) exist twice, and a job's upload and pre-pass run on a
+    // stream of their own: zcu_render_set_events for job i+1 proceeds while zcu_render_run of job i still executes; the run
+    // waits for its set's `ready`, the next upload into a set waits for the `released` of the last run that read it.
+    struct TabSet {
+        uint32_t* off;
+        DevEvent* events;
+        EnvSnap* snaps;
+        uint32_t* cursor;
+        cudaEvent_t ready, released;
+        bool has_ready, has_released;
+    } ts[2];
+    int ts_cur;
+    cudaStream_t up_stream;
     uint32_t nevents, cap_events;
     float* d_partial;      // [nwarps][block_frames][C]
     uint32_t debug_skip_mask;
@@ -271,7 +285,17 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint
     return ZCU_OK;
 }
 
+int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame);
 int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+    zcu_render::TabSet& T = r->ts[r->ts_cur];
+    if (T.has_ready) ZCU_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, T.ready, 0));  // this job's upload and pre-pass
+    const int rc = render_blocks_mode(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
+    if (rc != ZCU_OK) return rc;
+    ZCU_CUDA(ctx, cudaEventRecord(T.released, ctx->stream));
+    T.has_released = true;
+    return ZCU_OK;
+}
+int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
     if (r->cfg.mode == ZCU_RENDER_SEGMENTS) return render_blocks_seg(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
     if (r->cfg.mode == ZCU_RENDER_SCAN) return render_blocks_scan(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
     const zcu_render_config& c = r->cfg;
@@ -356,6 +380,10 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     if (!r) return ZCU_ERR_OOM;
     r->d_color = r->d_gains = r->d_partial = nullptr;
     r->h_events[0] = r->h_events[1] = nullptr;
+    r->h_off[0] = r->h_off[1] = nullptr;
+    for (auto& t : r->ts) t = zcu_render::TabSet{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, false, false};
+    r->ts_cur = 0;
+    r->up_stream = nullptr;
     r->h_done[0] = r->h_done[1] = nullptr;
     r->h_busy[0] = r->h_busy[1] = false;
     r->h_flip = 0;
@@ -398,11 +426,20 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     cudaError_t e = cudaMalloc(&r->d_color, (size_t)V * 4);
     if (e == cudaSuccess) e = cudaMalloc(&r->d_gains, (size_t)V * C * 4);
     if (e == cudaSuccess) e = cudaMalloc(&r->d_state, (size_t)V * sizeof(NiceVoiceState));
-    if (e == cudaSuccess) e = cudaMalloc(&r->d_event_off, (size_t)(V + 1) * 4);
+    for (auto& t : r->ts) {
+        if (e == cudaSuccess) e = cudaMalloc(&t.off, (size_t)(V + 1) * 4);
+        if (e == cudaSuccess) e = cudaMallocHost(&r->h_off[&t - r->ts], (size_t)(V + 1) * 4);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t.ready, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t.released, cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->up_stream, cudaStreamNonBlocking);
+    r->d_event_off = r->ts[0].off;
     if (e == cudaSuccess) e = cudaMalloc(&r->d_partial, (size_t)r->nwarps * r->block_frames * C * 4);
     if (segm) {
         r->nchunks_total = (cfg->total_frames + cfg->buffer_frames - 1) / cfg->buffer_frames;
-        if (e == cudaSuccess) e = cudaMalloc(&r->d_cursor, (size_t)r->nchunks_total * V * 4);
+        for (auto& t : r->ts)
+            if (e == cudaSuccess) e = cudaMalloc(&t.cursor, (size_t)r->nchunks_total * V * 4);
+        r->d_cursor = r->ts[0].cursor;
         if (e == cudaSuccess) e = cudaMalloc(&r->d_carry[0], (size_t)V * sizeof(float2));
         if (e == cudaSuccess) e = cudaMalloc(&r->d_carry[1], (size_t)V * sizeof(float2));
         if (e == cudaSuccess) e = cudaMalloc(&r->d_warm_stats, 2 * sizeof(uint32_t));
@@ -410,7 +447,9 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     if (scan) {
         r->nchunks_total = (cfg->total_frames + cfg->buffer_frames - 1) / cfg->buffer_frames;
         const size_t bc = (size_t)bb * V;
-        if (e == cudaSuccess) e = cudaMalloc(&r->d_cursor, (size_t)r->nchunks_total * V * 4);
+        for (auto& t : r->ts)
+            if (e == cudaSuccess) e = cudaMalloc(&t.cursor, (size_t)r->nchunks_total * V * 4);
+        r->d_cursor = r->ts[0].cursor;
         if (e == cudaSuccess) e = cudaMalloc(&r->d_zs, bc * sizeof(float2));
         if (e == cudaSuccess) e = cudaMalloc(&r->d_M, bc * sizeof(Mat2));
         if (e == cudaSuccess) e = cudaMalloc(&r->d_sstart, bc * sizeof(float2));
@@ -422,7 +461,7 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     }
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_color, voice_color_host, (size_t)V * 4, cudaMemcpyHostToDevice, ctx->stream));
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_gains, gains_host, (size_t)V * C * 4, cudaMemcpyHostToDevice, ctx->stream));
-    ZCU_CUDA(ctx, cudaMemsetAsync(r->d_event_off, 0, (size_t)(V + 1) * 4, ctx->stream));
+    for (auto& t : r->ts) ZCU_CUDA(ctx, cudaMemsetAsync(t.off, 0, (size_t)(V + 1) * 4, ctx->stream));
     if (getenv("ZCU_RENDER_DEBUG_CYCLES")) {  // profiling aid: per-stage busy/total cycles, printed at zcu_render_free
         ZCU_CUDA(ctx, cudaMalloc(&r->d_debug_cycles, (size_t)r->nwarps * 8 * sizeof(unsigned long long)));
         ZCU_CUDA(ctx, cudaMemsetAsync(r->d_debug_cycles, 0, (size_t)r->nwarps * 8 * sizeof(unsigned long long), ctx->stream));
@@ -450,15 +489,22 @@ void zcu_render_free(zcu_render* r) {
     cudaFree(r->d_color);
     cudaFree(r->d_gains);
     cudaFree(r->d_state);
-    cudaFree(r->d_event_off);
-    cudaFree(r->d_events);
+    if (r->up_stream) {
+        cudaStreamSynchronize(r->up_stream);
+        cudaStreamDestroy(r->up_stream);
+    }
     for (int i = 0; i < 2; i++) {
         cudaFreeHost(r->h_events[i]);
+        cudaFreeHost(r->h_off[i]);
         if (r->h_done[i]) cudaEventDestroy(r->h_done[i]);
+        cudaFree(r->ts[i].off);
+        cudaFree(r->ts[i].events);
+        cudaFree(r->ts[i].snaps);
+        cudaFree(r->ts[i].cursor);
+        if (r->ts[i].ready) cudaEventDestroy(r->ts[i].ready);
+        if (r->ts[i].released) cudaEventDestroy(r->ts[i].released);
     }
     cudaFree(r->d_partial);
-    cudaFree(r->d_snaps);
-    cudaFree(r->d_cursor);
     cudaFree(r->d_zs);
     cudaFree(r->d_M);
     cudaFree(r->d_sstart);
@@ -479,21 +525,27 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     const uint32_t V = r->cfg.voices;
     const uint32_t n = event_off_host[V];
     ZCU_REQUIRE(ctx, n == 0 || events_host, "null events");
-    if (n > r->cap_events || !r->d_events) {
+    if (n > r->cap_events || !r->ts[0].events) {
         ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        cudaFree(r->d_events);
-        cudaFree(r->d_snaps);
+        ZCU_CUDA(ctx, cudaStreamSynchronize(r->up_stream));
         r->d_events = nullptr;
         r->d_snaps = nullptr;
         for (int i = 0; i < 2; i++) {
+            cudaFree(r->ts[i].events);
+            cudaFree(r->ts[i].snaps);
+            r->ts[i].events = nullptr;
+            r->ts[i].snaps = nullptr;
             cudaFreeHost(r->h_events[i]);
             r->h_events[i] = nullptr;
             r->h_busy[i] = false;
             if (!r->h_done[i]) ZCU_CUDA(ctx, cudaEventCreateWithFlags(&r->h_done[i], cudaEventDisableTiming));
         }
-        if (r->cfg.mode != ZCU_RENDER_EXACT) ZCU_CUDA(ctx, cudaMalloc(&r->d_snaps, (size_t)(n ? n : 1) * sizeof(EnvSnap)));
-        ZCU_CUDA(ctx, cudaMalloc(&r->d_events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
-        for (int i = 0; i < 2; i++) ZCU_CUDA(ctx, cudaMallocHost(&r->h_events[i], (size_t)(n ? n : 1) * sizeof(DevEvent)));
+        r->cap_events = 0;
+        for (int i = 0; i < 2; i++) {
+            if (r->cfg.mode != ZCU_RENDER_EXACT) ZCU_CUDA(ctx, cudaMalloc(&r->ts[i].snaps, (size_t)(n ? n : 1) * sizeof(EnvSnap)));
+            ZCU_CUDA(ctx, cudaMalloc(&r->ts[i].events, (size_t)(n ? n : 1) * sizeof(DevEvent)));
+            ZCU_CUDA(ctx, cudaMallocHost(&r->h_events[i], (size_t)(n ? n : 1) * sizeof(DevEvent)));
+        }
         r->cap_events = n;
     }
     r->h_flip ^= 1;
@@ -543,27 +595,38 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
         expand(0, std::min(n, per));
         for (auto& th : pool) th.join();
     }
-    ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_event_off, event_off_host, (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    if (n) {
-        ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_events, staged, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, ctx->stream));
-        ZCU_CUDA(ctx, cudaEventRecord(r->h_done[hb], ctx->stream));
-        r->h_busy[hb] = true;
-    }
+    // upload and pre-pass of this job on the upload stream, into the table set the current run is not reading
+    const int nx = r->ts_cur ^ 1;
+    zcu_render::TabSet& T = r->ts[nx];
+    cudaStream_t us = r->up_stream;
+    if (T.has_released) ZCU_CUDA(ctx, cudaStreamWaitEvent(us, T.released, 0));
+    memcpy(r->h_off[hb], event_off_host, (size_t)(V + 1) * 4);
+    ZCU_CUDA(ctx, cudaMemcpyAsync(T.off, r->h_off[hb], (size_t)(V + 1) * 4, cudaMemcpyHostToDevice, us));
+    if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(T.events, staged, (size_t)n * sizeof(DevEvent), cudaMemcpyHostToDevice, us));
+    ZCU_CUDA(ctx, cudaEventRecord(r->h_done[hb], us));
+    r->h_busy[hb] = true;
     if (r->cfg.mode != ZCU_RENDER_EXACT) {
         PrepassArgs p;
         p.V = V;
         p.L = r->cfg.buffer_frames;
         p.nchunks_total = r->nchunks_total;
         p.sample_rate = r->cfg.sample_rate;
-        p.event_off = r->d_event_off;
-        p.events = r->d_events;
-        p.snaps = r->d_snaps;
-        p.cursor = r->d_cursor;
-        k_nice_cursor<<<(V + 3) / 4, 128, 0, ctx->stream>>>(p);
-        k_nice_prepass<<<(V + 63) / 64, 64, 0, ctx->stream>>>(p);
+        p.event_off = T.off;
+        p.events = T.events;
+        p.snaps = T.snaps;
+        p.cursor = T.cursor;
+        k_nice_cursor<<<(V + 3) / 4, 128, 0, us>>>(p);
+        k_nice_prepass<<<(V + 63) / 64, 64, 0, us>>>(p);
         ctx->launches += 2;
         ZCU_CUDA(ctx, cudaGetLastError());
     }
+    ZCU_CUDA(ctx, cudaEventRecord(T.ready, us));
+    T.has_ready = true;
+    r->ts_cur = nx;
+    r->d_event_off = T.off;
+    r->d_events = T.events;
+    r->d_snaps = T.snaps;
+    r->d_cursor = T.cursor;
     return ZCU_OK;
 }
 
