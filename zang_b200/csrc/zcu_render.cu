@@ -432,7 +432,11 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t.ready, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t.released, cudaEventDisableTiming);
     }
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->up_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) {  // highest priority: the small pre-pass kernels must not queue behind a render's CTAs
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        e = cudaStreamCreateWithPriority(&r->up_stream, cudaStreamNonBlocking, hi);
+    }
     r->d_event_off = r->ts[0].off;
     if (e == cudaSuccess) e = cudaMalloc(&r->d_partial, (size_t)r->nwarps * r->block_frames * C * 4);
     if (segm) {
