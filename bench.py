@@ -338,7 +338,9 @@ def main():
                        "render_mode": mode_desc,
                        "l2": "flushed between timed steps (256 MiB memset, untimed)"},
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": ms_e2e_step},
+                    "ms_per_step": ms_e2e_step,
+                    "note": "jobs submitted back to back: a job's H2D + pre-pass (upload stream) and the previous job's D2H (copy stream) "
+                            "overlap the render; every step copies its events in and its mix out"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": kernel_desc,
