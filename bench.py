@@ -19,6 +19,12 @@ mixes are summed with ONE NCCL reduce to rank 0 inside the timed region.
   cpu_baseline: the oracle (C++ restatement of the reference loops; no Zig toolchain exists here) on the
            host cores, on a bounded sample of the same workload.  Reported, not the target.
 
+  parity : the benched job checked, untimed, against the oracle on rank 0 (tests/bench_parity.py: per-voice windows at
+           every segment start + random windows + the first 64 voices x 8 s + the stereo mix)
+  strong : the same 4096-voice job split V/N per GPU (strong scaling), one reduce of the mix
+  sfx    : BASELINE.json configs[4]: 65536 SFX jobs x 24576 frames split over the GPUs, one reduce of the mix
+  other_configs : configs[2], configs[3] through the drop-in module path (N = 1 only), for a driver clock record
+
 `--impl reference` times that CPU path alone (rank 0 only).
 """
 import argparse
@@ -63,6 +69,12 @@ def parse_args():
     ap.add_argument("--block-buffers", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-modes", action="store_true", help="skip the comparison runs of the other render modes")
+    ap.add_argument("--no-parity", action="store_true", help="skip the untimed oracle check of the benched job")
+    ap.add_argument("--no-extra", action="store_true", help="skip the strong-scaling, SFX and other-config legs")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default, the driver's line): 4096 voices per GPU; strong: 4096 voices in total, V/N per GPU")
+    ap.add_argument("--config", default="polyphony", choices=["polyphony", "sfx"],
+                    help="sfx: BASELINE.json configs[4] as the headline line (65536 jobs x 24576 frames split over the GPUs)")
     ap.add_argument("--mode", default="segments", choices=["exact", "scan", "segments"],
                     help="exact: sequential-in-time kernel, bit-exact per voice; scan: time-parallel chunks (exact PulseOsc/Envelope, "
                          "filter start states from a 2x2 f64 scan; per-voice error <= 1e-5, the north-star tolerance)")
@@ -169,6 +181,116 @@ def cpu_reference_run(steps, warmup, quiet=False):
             "note": "C++ restatement of the reference's Zig paint loops (oracle/); the Zig ReleaseFast build cannot be produced here"}
 
 
+def sfx_leg(ctx, torch, dist, timed, rank, world, peak, jobs_total=65536, job_frames=24 * 1024):
+    """BASELINE.json configs[4]: jobs_total SFX jobs (Noise -> Curve -> Filter(cutoff buffer) -> Envelope -> multiply;
+    example_stereo.zig:71-98, example_laser.zig:77-115) split jobs/N per GPU, per-job pan gains, one reduce of the stereo
+    mix.  Device timed: module chain + voice sum + reduce; span tables and params resident."""
+    from zang_b200 import banks, synth
+    wl_all = synth.sfx_bank(jobs_total, job_frames)
+    a, b = jobs_total * rank // world, jobs_total * (rank + 1) // world
+    wl = {"event_off": (wl_all["event_off"][a:b + 1] - wl_all["event_off"][a]).astype("uint32"),
+          "events": wl_all["events"][wl_all["event_off"][a]:wl_all["event_off"][b]], "filter_type": wl_all["filter_type"][a:b],
+          "nodes": wl_all["nodes"].reshape(jobs_total, 3)[a:b].reshape(-1), "gains": wl_all["gains"][a:b]}
+    V = b - a
+    bank = banks.SfxBank(ctx, wl, SAMPLE_RATE, job_frames, first_seed=a)
+    out = ctx.buf(job_frames, V)
+    temps = [ctx.buf(job_frames, V) for _ in range(3)]
+    mix_t = torch.zeros((job_frames, 2), dtype=torch.float32, device="cuda")
+    mix = ctx.wrap(mix_t.data_ptr(), job_frames, 2)
+    prepared = bank.prepare_block(0, job_frames)
+    from zang_b200 import _lib as L
+    ctx.set_paint_mode(L.PAINT_TOLERANCE)
+
+    def step():
+        bank.noise.bank.reset(a)  # every step renders the same jobs from init()
+        for m in (bank.curve, bank.filter, bank.env):
+            m.bank.reset()
+        ctx.zero(None, out)
+        bank.paint_block(0, job_frames, out, temps, prepared=prepared)
+        mix_t.zero_()
+        ctx.mix_reduce(out, wl["gains"], 2, mix)
+        if dist is not None:
+            dist.reduce(mix_t, dst=0)
+    l0 = ctx.launch_count
+    step()
+    launches = ctx.launch_count - l0
+    ms = timed(step, 3)
+    ctx.set_paint_mode(L.PAINT_EXACT)
+    t = torch.tensor([sum(ms) / len(ms)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t[0])
+    for x in [out] + temps + list(prepared):
+        x.free()
+    vs = float(jobs_total) * job_frames / (ms_step * 1e-3)
+    gbs = vs * 100 / 1e9
+    return {"workload": "BASELINE.json configs[4]: SFX jobs (Noise -> Curve -> Filter with cutoff buffer -> x Envelope), drop-in module path "
+                        "(ZCU_PAINT_TOLERANCE), pan + voice sum, one NCCL reduce of the mix",
+            "jobs_total": jobs_total, "jobs_per_gpu": V, "job_frames": job_frames, "n_gpus": world, "scaling": "strong",
+            "ms_per_step": ms_step, "value": vs, "unit": METRIC, "steps": 3, "gpu_launches_per_step": int(launches),
+            "algorithmic_bytes_per_voice_sample": 100, "algorithmic_gbs_all_gpus": gbs, "frac_of_hbm_peak_per_gpu": gbs / world / peak}
+
+
+def other_configs_leg(ctx, torch, timed, peak):
+    """configs[2] (FmDetuned, 16384 voices) and configs[3] (SamplerVoice, 2048 voices) through the drop-in module path,
+    one block each, device timed with the span tables resident (N = 1 only).  tools/bank_bench.py is the long form."""
+    import numpy as np
+    from zang_b200 import _lib as L
+    from zang_b200 import banks, synth
+    res = {}
+    ctx.set_paint_mode(L.PAINT_TOLERANCE)
+    try:
+        # configs[2]
+        V, frames = 16384, 16 * 1024
+        wl = synth.fm_bank(V, frames, SAMPLE_RATE)
+        f = torch.arange(frames, dtype=torch.float64, device="cuda")[:, None]
+        v = torch.arange(V, dtype=torch.float64, device="cuda")[None, :]
+        det = (1.0 + 0.02 * torch.sin(2 * np.pi * (0.37 + 0.013 * (v % 17)) * f / 48000.0 + 0.7 * v)).float().contiguous()
+        idx = (1.0 + torch.sin(2 * np.pi * (0.11 + 0.007 * (v % 23)) * f / 48000.0 + 1.3 * v)).float().contiguous()
+        ins = (ctx.wrap(det.data_ptr(), frames, V), ctx.wrap(idx.data_ptr(), frames, V))
+        bank = banks.FmDetunedBank(ctx, wl, SAMPLE_RATE, frames)
+        out = ctx.buf(frames, V)
+        temps = [ctx.buf(frames, V) for _ in range(6)]
+        prepared = bank.prepare_block(0, frames)
+
+        def step_fm():
+            bank.paint_block(0, frames, out, temps, *ins, prepared=prepared)
+        step_fm()
+        ms = timed(step_fm, 3)
+        m = sum(ms) / len(ms)
+        gbs = V * frames * 140 / (m * 1e-3) / 1e9
+        res["configs[2] FmDetuned 16384 voices x 16384 frames"] = {"ms_per_block": m, "value": V * frames / (m * 1e-3), "bytes_per_voice_sample": 140,
+                                                                  "algorithmic_gbs": gbs, "frac_of_hbm_peak": gbs / peak}
+        for x in [out] + temps + list(prepared):
+            x.free()
+        del det, idx
+        # configs[3]
+        V, frames = 2048, 64 * 1024
+        wl = synth.sampler_bank(V, frames, 44100.0)
+        pcm, pcm_name = synth.drumloop_pcm()
+        smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
+        bank = banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames)
+        out = ctx.buf(frames, V)
+        temps = [ctx.buf(frames, V) for _ in range(2)]
+        prepared = bank.prepare_block(0, frames)
+
+        def step_smp():
+            bank.paint_block(0, frames, out, temps, prepared=prepared)
+        step_smp()
+        ms = timed(step_smp, 3)
+        m = sum(ms) / len(ms)
+        gbs = V * frames * 48 / (m * 1e-3) / 1e9
+        res[f"configs[3] SamplerVoice 2048 voices x 65536 frames ({pcm_name})"] = {"ms_per_block": m, "value": V * frames / (m * 1e-3),
+                                                                                 "bytes_per_voice_sample": 48, "algorithmic_gbs": gbs,
+                                                                                 "frac_of_hbm_peak": gbs / peak}
+        for x in [out] + temps + list(prepared):
+            x.free()
+    except Exception as e:  # never at the expense of the headline
+        res["error"] = repr(e)
+    ctx.set_paint_mode(L.PAINT_EXACT)
+    return res
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -207,15 +329,48 @@ def main():
 
     stream = torch.cuda.current_stream()
     ctx = Context(local_rank, stream=stream.cuda_stream)  # every kernel, copy, event and the NCCL reduce share one stream
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    peak, peak_src = measured_peak()
 
-    # ---- workload: the global bank has voices*world voices; this rank owns a contiguous shard ----
-    V = args.voices
-    wl_all = synth.polyphony_bank(V * world, total_frames, SAMPLE_RATE)
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """K steps between barrier+synchronize; per-step device time from CUDA events on the launch stream;
+        L2 flushed (untimed) between steps."""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        for a, b in evs:
+            flush.zero_()
+            a.record(stream)
+            fn()
+            b.record(stream)
+        barrier()
+        return [a.elapsed_time(b) for a, b in evs]
+
+    if args.config == "sfx":  # configs[4] as the line itself
+        sfx = sfx_leg(ctx, torch, dist, timed, rank, world, peak)
+        if rank == 0:
+            emit({"metric": METRIC, "value": sfx["value"], "unit": METRIC, "n_gpus": world, "steps": 3, "warmup": 1, "ms_per_step": sfx["ms_per_step"],
+                  "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": sfx,
+                  "gpu_launches": sfx["gpu_launches_per_step"] * 3})
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    # ---- workload: weak = the global bank has voices*world voices, strong = `voices` in total; a rank owns a contiguous shard
+    strong_line = args.scaling == "strong"
+    V_global = args.voices if strong_line else args.voices * world
+    wl_all = synth.polyphony_bank(V_global, total_frames, SAMPLE_RATE)
     wl = synth.shard_voices(wl_all, rank, world)
+    V = int(wl["color"].size)
     n_events = int(wl["event_off"][-1])
     # pinned host buffers for the end-to-end leg
-    ev_pinned = torch.empty(n_events * L.note_event_dtype.itemsize, dtype=torch.uint8).pin_memory()
-    ev_host = ev_pinned.numpy().view(L.note_event_dtype)
+    ev_pinned = torch.empty(max(n_events, 1) * L.note_event_dtype.itemsize, dtype=torch.uint8).pin_memory()
+    ev_host = ev_pinned.numpy().view(L.note_event_dtype)[:n_events]
     ev_host[:] = wl["events"]
     off_pinned = torch.empty(V + 1, dtype=torch.int32).pin_memory()
     off_host = off_pinned.numpy().view(np.uint32)
@@ -224,15 +379,10 @@ def main():
 
     mix_t = torch.zeros((total_frames, 2), dtype=torch.float32, device="cuda")
     mix = ctx.wrap(mix_t.data_ptr(), total_frames, 2)
+    mode_id = {"exact": L.RENDER_EXACT, "scan": L.RENDER_SCAN, "segments": L.RENDER_SEGMENTS}[args.mode]
     r = Render(ctx, V, total_frames, wl["color"], wl["gains"], channels=2, sample_rate=SAMPLE_RATE, buffer_frames=BUFFER_FRAMES,
-               block_buffers=args.block_buffers, mode={"exact": L.RENDER_EXACT, "scan": L.RENDER_SCAN, "segments": L.RENDER_SEGMENTS}[args.mode])
+               block_buffers=args.block_buffers, mode=mode_id)
     r.set_events(off_host, ev_host)
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     def step_resident():
         mix_t.zero_()
@@ -271,20 +421,6 @@ def main():
         if prev is not None:
             stream.wait_event(prev)  # the other mix buffer is free again, and the interval includes that copy
 
-    def timed(fn, steps, profile=False):
-        """K steps between barrier+synchronize; per-step device time from CUDA events on the launch stream;
-        L2 flushed (untimed) between steps."""
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
-        barrier()
-        for a, b in evs:
-            flush.zero_()
-            a.record(stream)
-            fn()
-            b.record(stream)
-        barrier()
-        ms = [a.elapsed_time(b) for a, b in evs]
-        return ms
-
     for _ in range(max(args.warmup, 0)):
         step_resident()
     barrier()
@@ -304,22 +440,118 @@ def main():
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
 
+    # wall-clock cross-checks of the end-to-end number (host clock, not stream events):
+    #   pipelined: K back-to-back jobs between two synchronizes, no flush inside (the flush is what the event-timed leg leaves out);
+    #   latency:   one job alone, set_events -> run -> (reduce) -> D2H -> synchronize, nothing to overlap with.
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    wall_pipelined_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    lat = []
+    for _ in range(3):
+        barrier()
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r.set_events(off_host, ev_host, sync=False)
+        mix_t.zero_()
+        r.run(mix)
+        if dist is not None:
+            dist.reduce(mix_t, dst=0)
+        if rank == 0:
+            mix_host.copy_(mix_t, non_blocking=True)
+        torch.cuda.synchronize()
+        lat.append((time.perf_counter() - t0) * 1e3)
+    e2e_state["copy_done"] = None
+
     # max over ranks of the mean step time
-    t_res = torch.tensor([sum(ms_steps) / len(ms_steps), sum(ms_e2e) / len(ms_e2e)], dtype=torch.float64, device="cuda")
+    t_res = torch.tensor([sum(ms_steps) / len(ms_steps), sum(ms_e2e) / len(ms_e2e), wall_pipelined_ms, min(lat)], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t_res, op=dist.ReduceOp.MAX)
-    ms_per_step, ms_e2e_step = float(t_res[0]), float(t_res[1])
+    ms_per_step, ms_e2e_step, wall_pipelined_ms, wall_latency_ms = (float(x) for x in t_res)
+
+    # ---- parity of the benched job, untimed: a clean run, the reduced mix read back on rank 0, then the oracle ----
+    parity = None
+    if not args.no_parity and args.mode == "segments":
+        mix_t.zero_()
+        r.run(mix)
+        if dist is not None:
+            dist.reduce(mix_t, dst=0)
+        torch.cuda.synchronize()
+        if rank == 0:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            try:
+                import bench_parity  # executes oracle/ as the checker (allowed: never inside a timed region)
+                nthreads = max(1, min(32, len(os.sched_getaffinity(0))))
+                got = mix_t.cpu().numpy()
+                # with N ranks the mix holds N x 4096 voices: the oracle then renders the first 1/N of the job of all of them
+                parity = bench_parity.check_bench_job(ctx, r, wl, total_frames, SAMPLE_RATE, BUFFER_FRAMES, mix_got=got, mix_wl=wl_all,
+                                                      mix_frames=total_frames // world, nthreads=nthreads)
+            except AssertionError as e:
+                parity = {"ok": False, "error": str(e)}
+        barrier()
+
+    # ---- strong scaling: the SAME 4096-voice job split V/N per GPU (at N = 1 it is the main line) ----
+    strong = None
+    if not args.no_extra and not strong_line and args.mode == "segments":
+        if world == 1:
+            strong = {"voices_total": V, "voices_per_gpu": V, "n_gpus": 1, "ms_per_step": ms_per_step, "value": float(V) * total_frames / (ms_per_step * 1e-3),
+                      "unit": METRIC, "scaling": "strong", "note": "N = 1: identical to the main line"}
+        else:
+            wl_s = synth.shard_voices(synth.polyphony_bank(args.voices, total_frames, SAMPLE_RATE), rank, world)
+            Vs = int(wl_s["color"].size)
+            rs = Render(ctx, Vs, total_frames, wl_s["color"], wl_s["gains"], channels=2, sample_rate=SAMPLE_RATE, buffer_frames=BUFFER_FRAMES, mode=mode_id)
+            rs.set_events(wl_s["event_off"], wl_s["events"])
+
+            def step_strong():
+                mix_t.zero_()
+                rs.run(mix)
+                if dist is not None:
+                    dist.reduce(mix_t, dst=0)
+            for _ in range(3):
+                step_strong()
+            rs.set_profiling(True)
+            ms_s = timed(step_strong, args.steps)
+            ks_ms, ks_n = rs.kernel_ms()
+            rs.set_profiling(False)
+            seg_s = rs.segment_info()
+
+            def step_strong_e2e():
+                rs.set_events(wl_s["event_off"], wl_s["events"], sync=False)
+                step_strong()
+                if rank == 0:
+                    mix_host.copy_(mix_t, non_blocking=True)
+            step_strong_e2e()
+            ms_se = timed(step_strong_e2e, args.steps)
+            ts = torch.tensor([sum(ms_s) / len(ms_s), sum(ms_se) / len(ms_se), ks_ms / max(ks_n, 1)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+            strong = {"voices_total": args.voices, "voices_per_gpu": Vs, "n_gpus": world, "ms_per_step": float(ts[0]),
+                      "value": float(args.voices) * total_frames / (float(ts[0]) * 1e-3), "unit": METRIC, "scaling": "strong", "steps": args.steps,
+                      "render_kernel_ms": float(ts[2]), "segments": seg_s,
+                      "e2e_ms_per_step": float(ts[1]), "e2e_value": float(args.voices) * total_frames / (float(ts[1]) * 1e-3),
+                      "note": "fixed costs per job that do not shrink with N: mix memset + k_partial_reduce over the 23 MB mix, the NCCL reduce of "
+                              "23 MB, launch latencies, and the Filter warm-up (2 buffers per segment, segments get shorter as N grows)"}
+            rs.free()
+
+    sfx = None
+    if not args.no_extra and args.mode == "segments":
+        try:
+            sfx = sfx_leg(ctx, torch, dist, timed, rank, world, peak)
+        except Exception as e:
+            sfx = {"error": repr(e)}
 
     if rank == 0:
-        voice_samples = float(V) * world * total_frames
+        voice_samples = float(V_global) * total_frames
         value = voice_samples / (ms_per_step * 1e-3)
         e2e_value = voice_samples / (ms_e2e_step * 1e-3)
-        peak, peak_src = measured_peak()
         kernel_key, kernel_desc, mode_desc = MODE_INFO[args.mode]
-        frames_per_launch_cfg = total_frames * args.steps / max(kern_launches, 1)
-        block_frames = int(round(frames_per_launch_cfg))
         avg_launch_ms = kern_ms / max(kern_launches, 1)
         frames_per_launch = total_frames * args.steps / max(kern_launches, 1)
+        block_frames = int(round(frames_per_launch))
         algo_bytes_per_launch = ALGO_BYTES_PER_VOICE_SAMPLE * V * frames_per_launch
         achieved = algo_bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9
         traffic = ncu_traffic_bytes_per_launch()
@@ -329,30 +561,46 @@ def main():
         d2h = total_frames * 2 * 4
         line = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if strong_line else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": "polyphony bank: NiceInstrument (PulseOsc+Envelope+Filter lowpass res 0.7) x Trigger note streams, "
                                    f"{args.seconds:g} s @48 kHz in 1024-frame buffers, stereo mix (BASELINE.json configs[1])",
-                       "voices_per_gpu": V, "voices_total": V * world, "frames": total_frames, "block_frames": block_frames,
+                       "voices_per_gpu": V, "voices_total": V_global, "frames": total_frames, "block_frames": block_frames,
                        "parallelism": f"voices sharded over {world} GPU(s); one NCCL reduce of the stereo mix per job" if world > 1 else "1 GPU",
                        "render_mode": mode_desc,
                        "l2": "flushed between timed steps (256 MiB memset, untimed)"},
             "e2e": {"value": e2e_value, "unit": METRIC, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": ms_e2e_step,
+                    "ms_per_step": ms_e2e_step, "kind": "pipelined throughput (stream events)",
+                    "wall_clock_ms_per_step_pipelined": wall_pipelined_ms, "wall_clock_value_pipelined": voice_samples / (wall_pipelined_ms * 1e-3),
+                    "wall_clock_ms_single_job_latency": wall_latency_ms, "wall_clock_value_single_job": voice_samples / (wall_latency_ms * 1e-3),
                     "note": "jobs submitted back to back: a job's H2D + pre-pass (upload stream) and the previous job's D2H (copy stream) "
-                            "overlap the render; every step copies its events in and its mix out"},
+                            "overlap the render; every step copies its events in and its mix out.  wall_clock_*: host perf_counter over the same "
+                            "K jobs without the L2 flush (pipelined) and of ONE job alone, set_events -> run -> D2H -> synchronize (latency)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": kernel_desc,
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
+                         "traffic_source": traffic.get("source") if traffic else None,
                          "algorithmic_bytes_per_launch": algo_bytes_per_launch, "avg_launch_ms": avg_launch_ms,
                          "launches_timed": int(kern_launches), "kernel_share_of_step": kern_ms / sum(ms_steps), "peak_source": peak_src,
-                         "note": "algorithmic bytes = 64 B/voice-sample of the un-fused module chain; the fused kernel keeps them in registers, so the "
-                                 "kernel is issue-bound (ncu: >90% issue slots busy), not HBM-bound; frac > 1 is the fusion"},
+                         "limiter": "instruction issue, not HBM",
+                         "dram_gbs_measured": (traffic["dram_bytes_per_launch"] / (avg_launch_ms * 1e-3) / 1e9) if traffic else None,
+                         "dram_frac_of_peak": (traffic["dram_bytes_per_launch"] / (avg_launch_ms * 1e-3) / 1e9 / peak) if traffic else None,
+                         "issue": traffic.get("issue") if traffic else None,
+                         "note": "achieved/frac follow the contract (algorithmic bytes of the reference's UN-FUSED module chain, 64 B per voice-sample, "
+                                 "over the fused kernel's time), so frac > 1 is the fusion, not a bandwidth: the kernel keeps the chain in registers, moves "
+                                 "dram_gbs_measured through HBM and is bound by instruction issue (`issue`, from the committed ncu capture).  The HBM-bound "
+                                 "form of the same workload is dropin_module_path below, whose frac_of_hbm_peak is a true roofline fraction"},
         }
         if args.mode == "segments":
             line["config"]["segments"] = r.segment_info()
+        if parity is not None:
+            line["parity"] = parity
+        if strong is not None:
+            line["strong"] = strong
+        if sfx is not None:
+            line["sfx"] = sfx
         if world == 1 and not args.no_other_modes:
             # the same job through the other render modes (device timed, inputs resident, L2 flushed), for comparison
             others = {}
@@ -404,6 +652,8 @@ def main():
                     b.free()
             except Exception as e:  # the headline number must not depend on the comparison leg
                 line["dropin_module_path"] = {"error": repr(e)}
+            if not args.no_extra:
+                line["other_configs"] = other_configs_leg(ctx, torch, timed, peak)
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_reference_run(1, 0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -462,12 +462,17 @@ enum { ZCU_RENDER_EXACT = 0, ZCU_RENDER_SCAN = 1, ZCU_RENDER_SEGMENTS = 2 };
 int zcu_render_create(zcu_ctx*, const zcu_render_config* cfg, const float* voice_color_host,
                       const float* gains_host, zcu_render** out);
 void zcu_render_free(zcu_render*);
-/* host events -> device (H2D), resets all voice state */
+/* host events -> device (H2D), resets all voice state.  ZCU_ERR_INVALID if event_off is not monotone from 0 or a voice's
+ * events are not chronological inside [0, total_frames). */
 int zcu_render_set_events(zcu_ctx*, zcu_render*, const uint32_t* event_off_host, const zcu_note_event* events_host);
 /* renders the whole job into mix ([total_frames][channels], accumulating, like every zang paint) */
 int zcu_render_run(zcu_ctx*, zcu_render*, zcu_buf* mix);
 /* optional: per-voice output (before mixing) of frames [first_frame, first_frame+out->frames) for parity tests */
 int zcu_render_run_voices(zcu_ctx*, zcu_render*, uint32_t first_frame, zcu_buf* out_voices);
+/* the same for voices [first_voice, first_voice + out->voices) only: out is [frames][out->voices].  The window is rendered
+ * with the launches and time segments of the whole job (what zcu_render_run executes), so it is the parity probe for a
+ * job too large to read back whole (per-voice windows at the benchmark configuration). */
+int zcu_render_run_voice_window(zcu_ctx*, zcu_render*, uint32_t first_voice, uint32_t first_frame, zcu_buf* out_voices);
 uint64_t zcu_render_launches_per_run(const zcu_render*);
 /* per-launch CUDA-event timing of the render kernel (the dominant kernel): after enabling, every
  * zcu_render_run records an event pair around each render-kernel launch; zcu_render_kernel_ms
@@ -479,6 +484,9 @@ int zcu_render_aux_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* l
 
 /* ZCU_RENDER_SEGMENTS diagnostics of the last run: segments per launch, mix buffers per segment, and the sum / max
  * over all (voice group, segment) warp tasks of the warm-up length in mix buffers */
+/* ZCU_RENDER_SEGMENTS: time segments per launch; 0 (default) = as many as fill the GPU's resident warps once, each at
+ * least 8 mix buffers long.  Any value renders within the mode's tolerance; 1 is the exact sequential render. */
+int zcu_render_set_segments(zcu_render*, uint32_t segments_per_launch);
 int zcu_render_segment_info(zcu_ctx*, zcu_render*, uint32_t* segments, uint32_t* buffers_per_segment, uint32_t* warm_sum,
                             uint32_t* warm_max);
 

@@ -5,7 +5,7 @@ import subprocess
 
 import numpy as np
 
-from zang_b200 import _lib as L
+from zang_b200 import abi as L  # dtypes / enums only: the oracle never touches libzangcu.so
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ODIR = os.path.join(ROOT, "oracle")

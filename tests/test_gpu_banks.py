@@ -47,6 +47,26 @@ def test_sampler_bank(ctx, voices, total, block):
     assert_close(got, want, TRANSCENDENTAL_TOL, "sampler bank (atanf per sample)")
 
 
+def test_sampler_bank_on_the_reference_drumloop(ctx):
+    """configs[3] on the reference's own asset (examples/example_sampler.zig:66, examples/drumloop.wav as the fixture
+    tests/golden/drumloop.wav): 8 s at 44.1 kHz with rare retriggers, so that some voices play through the whole
+    192 437-frame loop and the position check against the BYTE length (Sampler.zig:133-135) happens on the real length."""
+    sr = 44100.0
+    pcm, name = synth.drumloop_pcm()
+    assert name == "examples/drumloop.wav" and pcm.size == 384874
+    voices, total, block = 40, 344 * 1024 + 77, 64 * 1024
+    wl = synth.sampler_bank(voices, total, sr, seed=19, mean_gap=6.0)
+    _, want, _ = oracle.render_bank(oracle.BANK_SAMPLER, wl, total, sr, pcm=pcm, pcm_meta=(1, 44100, L.FMT_SIGNED16_LSB))
+    smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
+    bank = banks.SamplerVoiceBank(ctx, wl, smp, sr, total)
+    got = render_blocks(ctx, bank, total, block, 2)
+    assert np.abs(want).max() > 0.2
+    assert_close(got, want, TRANSCENDENTAL_TOL, "sampler bank on drumloop.wav (atanf per sample)")
+    # the Sampler position of at least one voice passed the end of the loop (192 437 frames) without a retrigger
+    st = bank.sampler.bank.get_state()
+    assert float(st["t"].max()) > 192437.0, float(st["t"].max())
+
+
 @pytest.mark.parametrize("jobs,job_frames,block", [(70, 6 * 1024, 2 * 1024), (32, 24576, 8 * 1024)])
 def test_sfx_bank(ctx, jobs, job_frames, block):
     sr = 48000.0

@@ -194,3 +194,37 @@ def test_render_config_errors(ctx):
     mix = ctx.buf(4096, 2)
     assert lib.zcu_render_run(ctx._h, h, mix._h) == L.ERR_INVALID  # no events yet
     lib.zcu_render_free(h)
+
+
+def test_set_events_rejects_malformed_tables(ctx):
+    """zcu_render_set_events validates what the device kernels will index with: offsets monotone from 0,
+    a voice's frames chronological and inside the render.  A bad table is ZCU_ERR_INVALID, not a GPU fault."""
+    voices, total = 8, 4 * 1024
+    wl = small_workload(voices, total, seed=3)
+    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, mode=L.RENDER_SEGMENTS)
+    off, ev = wl["event_off"].copy(), wl["events"].copy()
+    bad_off = off.copy()
+    bad_off[3], bad_off[4] = off[4], off[3]  # not monotone
+    with pytest.raises(E.ZangCuError):
+        r.set_events(bad_off, ev)
+    bad_ev = ev.copy()
+    bad_ev["frame"][off[2]] = total  # outside the render
+    with pytest.raises(E.ZangCuError):
+        r.set_events(off, bad_ev)
+    bad_ev = ev.copy()
+    k = int(off[5])
+    assert off[6] - off[5] >= 2
+    bad_ev["frame"][k], bad_ev["frame"][k + 1] = ev["frame"][k + 1] + 1, ev["frame"][k]  # out of order inside a voice
+    with pytest.raises(E.ZangCuError):
+        r.set_events(off, bad_ev)
+    shifted = off.copy()
+    shifted[0] = 1
+    with pytest.raises(E.ZangCuError):
+        r.set_events(shifted, ev)
+    # and the object still works after the rejections
+    r.set_events(off, ev)
+    _, want, _ = oracle.render_nice(wl, total, SR, want_mix=False, window=(0, total))
+    vo = ctx.buf(total, voices)
+    r.run_voices(0, vo)
+    assert_close(vo.download(), want, SCAN_TOL, "render after rejected tables")
+    r.free()

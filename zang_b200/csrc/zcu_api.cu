@@ -87,6 +87,7 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->nccl_comm) zcu_nccl_finalize(ctx);
     for (int i = 0; i < 4; i++)
         if (ctx->arena[i]) cudaFree(ctx->arena[i]);
     if (ctx->prefix) cudaFree(ctx->prefix);
@@ -94,6 +95,7 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
     if (ctx->xjump_resync) cudaFree(ctx->xjump_resync);
     if (ctx->chain) cudaFree(ctx->chain);
     if (ctx->chain_flags) cudaFree(ctx->chain_flags);
+    if (ctx->paint_ticket) cudaFree(ctx->paint_ticket);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->stream && ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -103,6 +105,14 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
 int zcu_ctx_sync(zcu_ctx* ctx) {
     if (!ctx) return ZCU_ERR_INVALID;
     ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->paint_ticket) {  // a chained paint launch whose wait for a predecessor segment timed out (zcu_paint_kernel.cuh)
+        uint32_t err = 0;
+        ZCU_CUDA(ctx, cudaMemcpy(&err, ctx->paint_ticket + 1, sizeof err, cudaMemcpyDeviceToHost));
+        if (err) {
+            cudaMemset(ctx->paint_ticket + 1, 0, sizeof err);
+            return zcu_fail(ctx, ZCU_ERR_CUDA, "a chained paint segment timed out waiting for its predecessor; the painted block is invalid");
+        }
+    }
     return ZCU_OK;
 }
 const char* zcu_last_error(zcu_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
@@ -303,16 +313,21 @@ int zcu_spans_upload(zcu_ctx* ctx, uint32_t voices, uint32_t frames, const uint3
     const uint32_t n = voice_off[voices];
     ZCU_REQUIRE(ctx, n == 0 || spans != nullptr, "null spans");
     uint32_t max_param = 0;
-    for (uint32_t v = 0; v < voices; v++) {
-        ZCU_REQUIRE(ctx, voice_off[v] <= voice_off[v + 1], "voice_off must be non-decreasing");
+    const char* bad = nullptr;
+    for (uint32_t v = 0; v < voices && !bad; v++) {
+        if (voice_off[v] > voice_off[v + 1] || voice_off[v + 1] > n) {
+            bad = "voice_off must be non-decreasing";
+            break;
+        }
         uint32_t prev_end = 0;
         for (uint32_t k = voice_off[v]; k < voice_off[v + 1]; k++) {
-            ZCU_REQUIRE(ctx, spans[k].start < spans[k].end && spans[k].end <= frames, "span outside the block or empty");
-            ZCU_REQUIRE(ctx, spans[k].start >= prev_end, "spans of a voice must be sorted and disjoint");
+            if (!(spans[k].start < spans[k].end && spans[k].end <= frames)) bad = "span outside the block or empty";
+            if (spans[k].start < prev_end) bad = "spans of a voice must be sorted and disjoint";
             prev_end = spans[k].end;
             if (spans[k].param > max_param) max_param = spans[k].param;
         }
     }
+    ZCU_REQUIRE(ctx, bad == nullptr, bad);
     zcu_spans* s = new zcu_spans{ctx, voices, frames, n, nullptr, nullptr, max_param};
     cudaError_t e = cudaMalloc(&s->d_off, (size_t)(voices + 1) * sizeof(uint32_t));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_spans, (size_t)(n ? n : 1) * sizeof(zcu_span));
@@ -320,13 +335,18 @@ int zcu_spans_upload(zcu_ctx* ctx, uint32_t voices, uint32_t frames, const uint3
         zcu_spans_free(s);
         return zcu_fail(ctx, ZCU_ERR_OOM, "span table allocation failed: %s", cudaGetErrorString(e));
     }
-    ZCU_CUDA(ctx, cudaMemcpyAsync(s->d_off, voice_off, (size_t)(voices + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
-    if (n) ZCU_CUDA(ctx, cudaMemcpyAsync(s->d_spans, spans, (size_t)n * sizeof(zcu_span), cudaMemcpyHostToDevice, ctx->stream));
+    e = cudaMemcpyAsync(s->d_off, voice_off, (size_t)(voices + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && n) e = cudaMemcpyAsync(s->d_spans, spans, (size_t)n * sizeof(zcu_span), cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) {
+        zcu_spans_free(s);
+        return zcu_fail(ctx, ZCU_ERR_CUDA, "span table upload failed: %s", cudaGetErrorString(e));
+    }
     *out = s;
     return ZCU_OK;
 }
 int zcu_spans_full(zcu_ctx* ctx, uint32_t voices, uint32_t num_buffers, uint32_t buffer_frames, zcu_spans** out) {
     if (!ctx || !out) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, (uint64_t)voices * num_buffers < (1ull << 32) && (uint64_t)num_buffers * buffer_frames < (1ull << 32), "table too large");
     std::vector<uint32_t> off(voices + 1);
     std::vector<zcu_span> sp((size_t)voices * num_buffers);
     for (uint32_t v = 0; v <= voices; v++) off[v] = v * num_buffers;
@@ -527,7 +547,11 @@ int zcu_sample_create(zcu_ctx* ctx, const uint8_t* data, size_t len, uint32_t nu
     ZCU_REQUIRE(ctx, format >= ZCU_FMT_UNSIGNED8 && format <= ZCU_FMT_SIGNED32_LSB, "unknown sample format");
     uint8_t* d = nullptr;
     ZCU_CUDA(ctx, cudaMalloc(&d, len));
-    ZCU_CUDA(ctx, cudaMemcpyAsync(d, data, len, cudaMemcpyHostToDevice, ctx->stream));
+    const cudaError_t e = cudaMemcpyAsync(d, data, len, cudaMemcpyHostToDevice, ctx->stream);
+    if (e != cudaSuccess) {
+        cudaFree(d);
+        return zcu_fail(ctx, ZCU_ERR_CUDA, "sample upload failed: %s", cudaGetErrorString(e));
+    }
     *out = new zcu_sample{ctx, d, len, num_channels, sample_rate, format};
     return ZCU_OK;
 }

@@ -88,10 +88,9 @@ int launch_spans(zcu_ctx* ctx, const zcu_spans* sp, float* dest, const float* a,
     if (pa.V == 0 || pa.frames == 0) return ZCU_OK;
     int nb = 1 + (pa.in0 ? 1 : 0) + (pa.in1 ? 1 : 0);
     const PaintPlan p = zcu_paint_plan(ctx, pa, nb, true);
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!ctx->attr_done.count((const void*)k_paint_lockstep<BasicMod<OP, ROWS>>)) {  // per device: tracked per context
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<BasicMod<OP, ROWS>>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
-        attr_set = true;
+        ctx->attr_done.insert((const void*)k_paint_lockstep<BasicMod<OP, ROWS>>);
     }
     k_paint_lockstep<BasicMod<OP, ROWS>><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(pa, p.T, p.seg_frames, p.vec4, p.stages);
     ctx->launches++;

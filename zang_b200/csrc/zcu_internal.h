@@ -5,6 +5,7 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <set>
 #include <string>
 
 #include "../../include/zangcu.h"
@@ -27,6 +28,9 @@ struct zcu_ctx {
     uint32_t* chain_flags = nullptr;
     size_t chain_flag_count = 0;
     uint32_t paint_epoch = 0;
+    uint32_t* paint_ticket = nullptr;  // [0] ticket counter of chained launches, [1] error flag of a timed-out wait
+    uint32_t paint_ticket_base = 0;    // host shadow of the counter: tickets handed out by the launches enqueued so far
+    std::set<const void*> attr_done;   // kernels whose dynamic shared-memory limit has been raised on this context's device
     void* prefix = nullptr;  // M::PREFIX modules: state rows at the segment starts
     size_t prefix_bytes = 0;
     // Noise skip-ahead: xoshiro256 jump matrices (built on first use) and the device counter of unforeseeable extra draws
@@ -81,8 +85,16 @@ int zcu_fail(zcu_ctx* ctx, int code, const char* fmt, ...);
                             "%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));    \
     } while (0)
 
+// Every ABI entry point validates its arguments with ZCU_REQUIRE first; that is also where the calling thread is switched
+// to the context's device (allocations and launches use the CURRENT device, and a host may hold contexts on several GPUs).
+inline void zcu_use_device(const zcu_ctx* ctx) {
+    int cur = -1;
+    if (ctx && cudaGetDevice(&cur) == cudaSuccess && cur != ctx->device) cudaSetDevice(ctx->device);
+}
+
 #define ZCU_REQUIRE(ctx, cond, msg)                                                         \
     do {                                                                                    \
+        zcu_use_device(ctx);                                                                \
         if (!(cond)) return zcu_fail((ctx), ZCU_ERR_INVALID, "%s: %s", __func__, (msg));    \
     } while (0)
 

@@ -4,7 +4,10 @@
 // collective of the whole path is this reduce of the [frames][channels] partial mix.  NCCL is bound at
 // run time with dlopen so that the library has no link-time dependency on a particular libnccl (the
 // Python harness shares the process with torch's bundled NCCL; a Zig host uses the system one).
+// Types, enum values and prototypes come from NCCL's own header (decltype of the declared functions), so the signatures the
+// function pointers are called through are the library's, not hand-copied ones; only the binding is deferred to dlopen.
 #include <dlfcn.h>
+#include <nccl.h>
 
 #include <cstring>
 
@@ -12,13 +15,14 @@
 
 namespace {
 
-typedef struct { char internal[128]; } ncclUniqueId_t;
-typedef void* ncclComm_p;
-typedef int (*fn_GetUniqueId)(ncclUniqueId_t*);
-typedef int (*fn_CommInitRank)(ncclComm_p*, int, ncclUniqueId_t, int);
-typedef int (*fn_CommDestroy)(ncclComm_p);
-typedef int (*fn_Reduce)(const void*, void*, size_t, int, int, int, ncclComm_p, cudaStream_t);
-typedef const char* (*fn_GetErrorString)(int);
+typedef ncclUniqueId ncclUniqueId_t;
+typedef ncclComm_t ncclComm_p;
+typedef decltype(&ncclGetUniqueId) fn_GetUniqueId;
+typedef decltype(&ncclCommInitRank) fn_CommInitRank;
+typedef decltype(&ncclCommDestroy) fn_CommDestroy;
+typedef decltype(&ncclReduce) fn_Reduce;
+typedef decltype(&ncclGetErrorString) fn_GetErrorString;
+static_assert(sizeof(ncclUniqueId) == 128, "zcu_nccl_unique_id hands out the 128-byte ncclUniqueId");
 
 struct Nccl {
     void* h = nullptr;
@@ -44,8 +48,10 @@ struct Nccl {
     }
 };
 Nccl g_nccl;
-const int kNcclFloat32 = 7;  // ncclFloat32
-const int kNcclSum = 0;      // ncclSum
+const char* dl_error() {
+    const char* e = dlerror();  // NULL when the library loaded but a symbol is missing
+    return e ? e : "a required NCCL symbol is missing";
+}
 
 }  // namespace
 
@@ -55,7 +61,7 @@ int zcu_nccl_unique_id(uint8_t id_out[128]) {
     if (!id_out) return ZCU_ERR_INVALID;
     if (!g_nccl.load()) return ZCU_ERR_NCCL;
     ncclUniqueId_t id;
-    if (g_nccl.GetUniqueId(&id) != 0) return ZCU_ERR_NCCL;
+    if (g_nccl.GetUniqueId(&id) != ncclSuccess) return ZCU_ERR_NCCL;
     std::memcpy(id_out, id.internal, 128);
     return ZCU_OK;
 }
@@ -63,13 +69,14 @@ int zcu_nccl_unique_id(uint8_t id_out[128]) {
 int zcu_nccl_init(zcu_ctx* ctx, int nranks, int rank, const uint8_t id_in[128]) {
     if (!ctx || !id_in) return ZCU_ERR_INVALID;
     ZCU_REQUIRE(ctx, nranks >= 1 && rank >= 0 && rank < nranks, "bad rank / nranks");
-    if (!g_nccl.load()) return zcu_fail(ctx, ZCU_ERR_NCCL, "libnccl.so.2 not found: %s", dlerror());
+    if (!g_nccl.load()) return zcu_fail(ctx, ZCU_ERR_NCCL, "libnccl.so.2 not usable: %s", dl_error());
+    ZCU_REQUIRE(ctx, ctx->nccl_comm == nullptr, "zcu_nccl_init called twice (zcu_nccl_finalize first)");
     ncclUniqueId_t id;
     std::memcpy(id.internal, id_in, 128);
     ZCU_CUDA(ctx, cudaSetDevice(ctx->device));
     ncclComm_p comm = nullptr;
-    const int rc = g_nccl.CommInitRank(&comm, nranks, id, rank);
-    if (rc != 0) return zcu_fail(ctx, ZCU_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error");
+    const ncclResult_t rc = g_nccl.CommInitRank(&comm, nranks, id, rank);
+    if (rc != ncclSuccess) return zcu_fail(ctx, ZCU_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error");
     ctx->nccl_comm = comm;
     ctx->nccl_rank = rank;
     ctx->nccl_nranks = nranks;
@@ -81,8 +88,9 @@ int zcu_nccl_reduce_mix(zcu_ctx* ctx, zcu_buf* mix, int root) {
     ZCU_REQUIRE(ctx, mix != nullptr, "null mix");
     ZCU_REQUIRE(ctx, ctx->nccl_comm != nullptr, "zcu_nccl_init has not been called");
     const size_t count = (size_t)mix->frames * mix->voices;
-    const int rc = g_nccl.Reduce(mix->d, mix->d, count, kNcclFloat32, kNcclSum, root, ctx->nccl_comm, ctx->stream);
-    if (rc != 0) return zcu_fail(ctx, ZCU_ERR_NCCL, "ncclReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error");
+    ZCU_REQUIRE(ctx, root >= 0 && root < ctx->nccl_nranks, "bad root");
+    const ncclResult_t rc = g_nccl.Reduce(mix->d, mix->d, count, ncclFloat32, ncclSum, root, (ncclComm_t)ctx->nccl_comm, ctx->stream);
+    if (rc != ncclSuccess) return zcu_fail(ctx, ZCU_ERR_NCCL, "ncclReduce: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error");
     return ZCU_OK;
 }
 
@@ -90,7 +98,7 @@ int zcu_nccl_finalize(zcu_ctx* ctx) {
     if (!ctx) return ZCU_ERR_INVALID;
     if (ctx->nccl_comm) {
         cudaStreamSynchronize(ctx->stream);
-        g_nccl.CommDestroy(ctx->nccl_comm);
+        g_nccl.CommDestroy((ncclComm_t)ctx->nccl_comm);
         ctx->nccl_comm = nullptr;
     }
     return ZCU_OK;

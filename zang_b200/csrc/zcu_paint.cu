@@ -34,6 +34,11 @@ int ensure_chain(zcu_ctx* ctx, size_t states, size_t flags) {
         ctx->chain_flag_count = flags;
         ctx->paint_epoch = 0;
     }
+    if (!ctx->paint_ticket) {
+        ZCU_CUDA(ctx, cudaMalloc(&ctx->paint_ticket, 2 * sizeof(uint32_t)));
+        ZCU_CUDA(ctx, cudaMemsetAsync(ctx->paint_ticket, 0, 2 * sizeof(uint32_t), ctx->stream));
+        ctx->paint_ticket_base = 0;
+    }
     return ZCU_OK;
 }
 
@@ -143,6 +148,9 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     a.chain_flags = nullptr;
     a.epoch = 0;
     a.warm_cap = 0;
+    a.ticket = nullptr;
+    a.ticket_base = 0;
+    a.chain_err = nullptr;
     if ((warm || scan) && p.nseg > 1) {
         int rc = ensure_chain(ctx, (size_t)p.nseg * a.V, (size_t)p.nseg * p.grid_x);
         if (rc) return rc;
@@ -150,6 +158,10 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         a.chain_flags = ctx->chain_flags;
         a.epoch = ++ctx->paint_epoch;
         a.warm_cap = (uint32_t)std::min<uint64_t>(a.frames, 8ull * p.seg_frames);  // a window longer than this: chain instead
+        a.ticket = ctx->paint_ticket;
+        a.ticket_base = ctx->paint_ticket_base;
+        a.chain_err = ctx->paint_ticket + 1;
+        ctx->paint_ticket_base += p.grid_x * p.nseg;  // one ticket per CTA of this launch (mod 2^32, like the device counter)
     } else if (!skip) {
         p.nseg = 1;
         p.seg_frames = a.frames;
@@ -173,10 +185,9 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         ctx->launches++;
         ZCU_CUDA(ctx, cudaGetLastError());
     }
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!ctx->attr_done.count((const void*)k_paint_lockstep<M>)) {  // the attribute is per device: tracked per context
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
-        attr_set = true;
+        ctx->attr_done.insert((const void*)k_paint_lockstep<M>);
     }
     k_paint_lockstep<M><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4, p.stages);
     ctx->launches++;

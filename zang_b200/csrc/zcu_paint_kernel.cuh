@@ -144,9 +144,31 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     extern __shared__ __align__(16) float smem[];
     constexpr uint32_t W = kPaintWarps, RV = 32 * W;  // S = tiles in the cp.async ring (3..8: deeper when few CTAs share an SM)
     const uint32_t tid = threadIdx.x;
-    const uint32_t v0 = blockIdx.x * RV;
+    // (voice block, segment) of this CTA: blockIdx, or — in launches whose segments wait for each other — a ticket
+    uint32_t bx = blockIdx.x, by = blockIdx.y;
+    if (a.ticket != nullptr) {
+        __shared__ uint32_t s_ticket;
+        if (tid == 0) s_ticket = atomicAdd(a.ticket, 1u) - a.ticket_base;
+        __syncthreads();
+        bx = s_ticket % gridDim.x;
+        by = s_ticket / gridDim.x;
+    }
+    const uint32_t v0 = bx * RV;
     const uint32_t v = v0 + tid;
     const bool valid = v < a.V;
+    // wait for the flag of (bx, by - 1); bounded: ~4 s, then flag the error and go on
+    auto wait_predecessor = [&](uint32_t ns) {
+        const volatile uint32_t* fl = a.chain_flags + (size_t)(by - 1) * gridDim.x + bx;
+        uint32_t spins = 0;
+        while (*fl != a.epoch) {
+            __nanosleep(ns);
+            if (++spins > (1u << 24)) {
+                if (a.chain_err) atomicExch(a.chain_err, 1u);
+                break;
+            }
+        }
+        __threadfence();
+    };
 
     // staged buffers: slot 0 = output, then the inputs that are present (no pointer array: it would live in local memory)
     int nb = 1;
@@ -167,7 +189,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const bool warm = kWarm && a.chain != nullptr;  // tolerance mode: segments start from a verified warm-up or the chain
     const bool scan = kScan && a.chain != nullptr;  // exact chained prefix sum: segments pass their integer state along
     const bool segmented = M::SKIP || warm || scan;
-    const uint32_t f_begin = segmented ? blockIdx.y * seg_frames : 0u;
+    const uint32_t f_begin = segmented ? by * seg_frames : 0u;
     const uint32_t f_end = segmented ? min(a.frames, f_begin + seg_frames) : a.frames;
     if (f_begin >= f_end) return;  // uniform over the CTA
 
@@ -436,20 +458,16 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             __syncthreads();
             inputs_only = false;
             // look-back: the predecessor's inclusive prefix is this segment's start state (segment 0 keeps the loaded state)
-            if (blockIdx.y > 0) {
-                if (tid == 0) {
-                    const volatile uint32_t* fl = a.chain_flags + (size_t)(blockIdx.y - 1) * gridDim.x + blockIdx.x;
-                    while (*fl != a.epoch) __nanosleep(128);
-                    __threadfence();
-                }
+            if (by > 0) {
+                if (tid == 0) wait_predecessor(128);
                 __syncthreads();
-                if (valid) m.scan_load(a.chain + (size_t)(blockIdx.y - 1) * V + v);
+                if (valid) m.scan_load(a.chain + (size_t)(by - 1) * V + v);
             }
             if (f_end < a.frames) {
-                if (valid) m.scan_store(a.chain + (size_t)blockIdx.y * V + v);
+                if (valid) m.scan_store(a.chain + (size_t)by * V + v);
                 __threadfence();
                 __syncthreads();
-                if (tid == 0) atomicExch(a.chain_flags + (size_t)blockIdx.y * gridDim.x + blockIdx.x, a.epoch);
+                if (tid == 0) atomicExch(a.chain_flags + (size_t)by * gridDim.x + bx, a.epoch);
             }
             // pass 2 starts where pass 1 started
             k = k_0; s_start = ss_0; s_end = se_0; s_flags = sf_0; s_param = sp_0; active = act_0;
@@ -475,7 +493,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 }
             }
             PaintArgs row = a;
-            row.state = (char*)a.prefix + (size_t)blockIdx.y * a.V * a.prefix_stride;
+            row.state = (char*)a.prefix + (size_t)by * a.V * a.prefix_stride;
             m.load(row, v);
             if (s_start < f_begin) {
                 m.begin_span(a, s_param, s_flags & ~(uint32_t)ZCU_SPAN_NOTE_ID_CHANGED, s_end - s_start);
@@ -508,17 +526,13 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         if (warm && f_begin > 0) {
             for (uint32_t tile = tile_first; tile < tile0; tile++) do_tile(tile, std::integral_constant<int, 1>{});
             // end of the warm-up: keep the warmed state if every voice of the CTA verified its window, otherwise wait for the
-            // end state the previous segment publishes (CTAs are dispatched in blockIdx order, so the predecessor is resident
-            // or done: no deadlock; an undamped filter degenerates to the sequential walk)
+            // end state the previous segment publishes (segments are handed out by ticket, so the predecessor has started:
+            // no deadlock whatever the dispatch order; an undamped filter degenerates to the sequential walk)
             const bool ok = !valid || pristine || (tile_first < tile0 && m.warm_ok());
             if (!__syncthreads_and(ok)) {
-                if (tid == 0) {
-                    const volatile uint32_t* fl = a.chain_flags + (size_t)(blockIdx.y - 1) * gridDim.x + blockIdx.x;
-                    while (*fl != a.epoch) __nanosleep(256);
-                    __threadfence();
-                }
+                if (tid == 0) wait_predecessor(256);
                 __syncthreads();
-                if (valid && !pristine) m.chain_load(a.chain + (size_t)(blockIdx.y - 1) * V + v);
+                if (valid && !pristine) m.chain_load(a.chain + (size_t)(by - 1) * V + v);
             }
         }
     }
@@ -526,10 +540,10 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
 
     if constexpr (kWarm) {
         if (warm && f_end < a.frames) {  // publish the end state for a successor that could not verify its warm-up
-            if (valid) m.chain_store(a.chain + (size_t)blockIdx.y * V + v);
+            if (valid) m.chain_store(a.chain + (size_t)by * V + v);
             __threadfence();
             __syncthreads();
-            if (tid == 0) atomicExch(a.chain_flags + (size_t)blockIdx.y * gridDim.x + blockIdx.x, a.epoch);
+            if (tid == 0) atomicExch(a.chain_flags + (size_t)by * gridDim.x + bx, a.epoch);
         }
     }
     if (f_end < a.frames) return;  // not the last segment: its state is somebody else's start

@@ -77,9 +77,17 @@ struct zcu_render {
     uint32_t* d_warm_stats;  // [2] sum / max of warm-up buffers over the warp tasks of the last run
     uint32_t seg_slots;    // resident warps of k_nice_seg_render on this device
     uint32_t last_nseg, last_seg_chunks;
+    uint32_t forced_nseg;  // zcu_render_set_segments: segments per launch (0 = as many as fill the resident warps)
+    bool attr_set[3];      // cudaFuncSetAttribute done for the scan / segment / exact kernels on this render's device
 };
 
 namespace {
+
+// un-mixed per-voice output window of a run (parity tests): frames [first, first+frames) x voices [v0, v0+nv), or d == null
+struct VoutReq {
+    float* d;
+    uint32_t first, frames, v0, nv;
+};
 
 // mix[F0+f][c] += sum over warps (fixed order) of partial[w][f][c]
 __global__ void __launch_bounds__(256) k_partial_reduce(const float* __restrict__ partial, float* __restrict__ mix, uint32_t nwarps,
@@ -111,12 +119,12 @@ int record_pair_begin(zcu_ctx* ctx, std::vector<cudaEvent_t>& ev, size_t used) {
 }
 
 // ZCU_RENDER_SCAN: per block of chunks  zero-state pass -> per-voice chain -> render -> ordered partial sum
-int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame) {
     const zcu_render_config& c = r->cfg;
     ZCU_CUDA(ctx, cudaMemsetAsync(r->d_fstate, 0, (size_t)c.voices * sizeof(double2), ctx->stream));
     constexpr int RT = 64;
     const size_t smem = scan_render_smem_bytes<RT>();
-    static bool attr_set = false;
+    bool& attr_set = r->attr_set[0];  // per render object: the attribute is per device, and contexts may live on several
     if (!attr_set) {
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_scan_render<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_scan_render<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -146,12 +154,14 @@ int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uin
         a.sstart = r->d_sstart;
         a.fstate = r->d_fstate;
         a.partial = r->d_partial;
-        a.vout = vout;
-        a.vout_first = vout_first;
-        a.vout_frames = vout_frames;
+        a.vout = vo.d;
+        a.vout_first = vo.first;
+        a.vout_frames = vo.frames;
+        a.vout_v0 = vo.v0;
+        a.vout_nv = vo.nv;
         const uint32_t tasks = a.nvgroups * a.nchunks;
         const uint32_t grid = (tasks + 3) / 4;
-        const bool prof = r->profiling && !vout;
+        const bool prof = r->profiling && !vo.d;
         if (prof) {
             int rc = record_pair_begin(ctx, r->ev_aux, r->ev_aux_used);
             if (rc != ZCU_OK) return rc;
@@ -166,7 +176,7 @@ int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uin
             int rc = record_pair_begin(ctx, r->ev, r->ev_used);
             if (rc != ZCU_OK) return rc;
         }
-        if (vout) {
+        if (vo.d) {
             if (c.channels == 2)
                 k_nice_scan_render<2, true, RT><<<grid, 128, smem, ctx->stream>>>(a);
             else
@@ -191,11 +201,11 @@ int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uin
 }
 
 // ZCU_RENDER_SEGMENTS: one launch per block of mix buffers; (voice groups x segments) fills the resident warps once
-int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame) {
     const zcu_render_config& c = r->cfg;
     constexpr int RT = 64;
     const size_t smem = scan_render_smem_bytes<RT>();
-    static bool attr_set = false;
+    bool& attr_set = r->attr_set[1];
     if (!attr_set) {
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -211,7 +221,12 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint
     ZCU_CUDA(ctx, cudaMemsetAsync(r->d_carry[0], 0, (size_t)c.voices * sizeof(float2), ctx->stream));
     ZCU_CUDA(ctx, cudaMemsetAsync(r->d_warm_stats, 0, 2 * sizeof(uint32_t), ctx->stream));
     int flip = 0;
+    // A voice window is rendered with the launches and segments of the whole job, so that it shows the arithmetic of
+    // zcu_render_run; launches past the window are not issued, warp tasks that cannot touch it return at once.
+    const uint32_t win_end = end_frame;
+    if (vo.d) end_frame = c.total_frames;
     for (uint32_t F0 = 0; F0 < end_frame; F0 += r->block_frames) {
+        if (vo.d && F0 >= win_end) break;
         SegArgs g;
         ScanArgs& a = g.s;
         a.V = c.voices;
@@ -234,13 +249,18 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint
         a.sstart = nullptr;
         a.fstate = nullptr;
         a.partial = r->d_partial;
-        a.vout = vout;
-        a.vout_first = vout_first;
-        a.vout_frames = vout_frames;
+        a.vout = vo.d;
+        a.vout_first = vo.first;
+        a.vout_frames = vo.frames;
+        a.vout_v0 = vo.v0;
+        a.vout_nv = vo.nv;
         // segments: as many as fill the resident warps once, each at least 8 mix buffers long
         uint32_t nseg = std::max(1u, r->seg_slots / a.nvgroups);
         uint32_t min_chunks = 8;
-        if (const char* e = getenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH")) {  // tuning / tests
+        if (r->forced_nseg) {
+            nseg = r->forced_nseg;
+            min_chunks = 1;
+        } else if (const char* e = getenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH")) {  // tuning / tests
             nseg = std::max(1, atoi(e));
             min_chunks = 1;
         }
@@ -250,6 +270,7 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint
         g.seg_chunks = seg_chunks;
         g.carry = nullptr;
         g.warm_stats = r->d_warm_stats;
+        g.need_carry = (vo.d && a.F1 < win_end) ? 1u : 0u;
         r->last_nseg = nseg;
         r->last_seg_chunks = seg_chunks;
         const uint32_t tasks = a.nvgroups * nseg;
@@ -257,7 +278,7 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint
         const float2* cin = r->d_carry[flip];
         float2* cout = r->d_carry[flip ^ 1];
         flip ^= 1;
-        if (vout) {
+        if (vo.d) {
             if (c.channels == 2)
                 k_nice_seg_render<2, true, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
             else
@@ -285,19 +306,19 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint
     return ZCU_OK;
 }
 
-int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame);
-int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
+int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame);
+int render_blocks(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame) {
     zcu_render::TabSet& T = r->ts[r->ts_cur];
     if (T.has_ready) ZCU_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, T.ready, 0));  // this job's upload and pre-pass
-    const int rc = render_blocks_mode(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
+    const int rc = render_blocks_mode(ctx, r, mix, vo, end_frame);
     if (rc != ZCU_OK) return rc;
     ZCU_CUDA(ctx, cudaEventRecord(T.released, ctx->stream));
     T.has_released = true;
     return ZCU_OK;
 }
-int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uint32_t vout_first, uint32_t vout_frames, uint32_t end_frame) {
-    if (r->cfg.mode == ZCU_RENDER_SEGMENTS) return render_blocks_seg(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
-    if (r->cfg.mode == ZCU_RENDER_SCAN) return render_blocks_scan(ctx, r, mix, vout, vout_first, vout_frames, end_frame);
+int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame) {
+    if (r->cfg.mode == ZCU_RENDER_SEGMENTS) return render_blocks_seg(ctx, r, mix, vo, end_frame);
+    if (r->cfg.mode == ZCU_RENDER_SCAN) return render_blocks_scan(ctx, r, mix, vo, end_frame);
     const zcu_render_config& c = r->cfg;
     k_state_reset<<<(c.voices + 127) / 128, 128, 0, ctx->stream>>>(r->d_state, r->d_event_off, c.voices);
     ctx->launches++;
@@ -317,14 +338,16 @@ int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uin
         a.event_off = r->d_event_off;
         a.events = r->d_events;
         a.partial = r->d_partial;
-        a.vout = vout;
-        a.vout_first = vout_first;
-        a.vout_frames = vout_frames;
+        a.vout = vo.d;
+        a.vout_first = vo.first;
+        a.vout_frames = vo.frames;
+        a.vout_v0 = vo.v0;
+        a.vout_nv = vo.nv;
         a.debug_skip_mask = r->debug_skip_mask;
         a.debug_cycles = r->d_debug_cycles;
         constexpr int RT = 128;
         const size_t smem = render_smem_bytes<RT>();
-        static bool attr_set = false;
+        bool& attr_set = r->attr_set[2];
         if (!attr_set) {
             ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -332,7 +355,7 @@ int render_blocks_mode(zcu_ctx* ctx, zcu_render* r, float* mix, float* vout, uin
             ZCU_CUDA(ctx, cudaFuncSetAttribute(k_render_nice<2, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr_set = true;
         }
-        if (vout) {
+        if (vo.d) {
             if (c.channels == 2)
                 k_render_nice<2, true, RT><<<r->nwarps, 128, smem, ctx->stream>>>(a);
             else
@@ -405,9 +428,13 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     r->d_warm_stats = nullptr;
     r->seg_slots = 0;
     r->last_nseg = r->last_seg_chunks = 0;
+    r->attr_set[0] = r->attr_set[1] = r->attr_set[2] = false;
+    r->forced_nseg = 0;
     r->debug_skip_mask = 0;
     r->d_debug_cycles = nullptr;
-    if (const char* m = getenv("ZCU_RENDER_DEBUG_SKIP_MASK")) r->debug_skip_mask = (uint32_t)atoi(m);  // profiling aid, wrong results
+#ifdef ZCU_DEBUG_KNOBS  // profiling aid that produces wrong audio: only in builds that ask for it, never from a stray environment variable
+    if (const char* m = getenv("ZCU_RENDER_DEBUG_SKIP_MASK")) r->debug_skip_mask = (uint32_t)atoi(m);
+#endif
     r->ctx = ctx;
     r->cfg = *cfg;
     const bool scan = cfg->mode == ZCU_RENDER_SCAN;
@@ -466,10 +493,12 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_color, voice_color_host, (size_t)V * 4, cudaMemcpyHostToDevice, ctx->stream));
     ZCU_CUDA(ctx, cudaMemcpyAsync(r->d_gains, gains_host, (size_t)V * C * 4, cudaMemcpyHostToDevice, ctx->stream));
     for (auto& t : r->ts) ZCU_CUDA(ctx, cudaMemsetAsync(t.off, 0, (size_t)(V + 1) * 4, ctx->stream));
+#ifdef ZCU_DEBUG_KNOBS
     if (getenv("ZCU_RENDER_DEBUG_CYCLES")) {  // profiling aid: per-stage busy/total cycles, printed at zcu_render_free
         ZCU_CUDA(ctx, cudaMalloc(&r->d_debug_cycles, (size_t)r->nwarps * 8 * sizeof(unsigned long long)));
         ZCU_CUDA(ctx, cudaMemsetAsync(r->d_debug_cycles, 0, (size_t)r->nwarps * 8 * sizeof(unsigned long long), ctx->stream));
     }
+#endif
     *out = r;
     return ZCU_OK;
 }
@@ -563,41 +592,66 @@ int zcu_render_set_events(zcu_ctx* ctx, zcu_render* r, const uint32_t* event_off
     // job a single thread costs more than the H2D copy it feeds.
     struct Memo { uint32_t key; float cutoff; bool valid; };
     const float sr = r->cfg.sample_rate;
+    const uint32_t total_frames = r->cfg.total_frames;
     DevEvent* const staged = r->h_events[hb];
-    auto expand = [events_host, staged, sr](uint32_t i0, uint32_t i1) {
+    // Each thread takes a range of voices and checks the table while it expands it: offsets monotone from 0, every voice's
+    // frames chronological and inside the render.  A malformed table would make the device kernels walk out of bounds.
+    auto expand = [event_off_host, events_host, staged, sr, total_frames, n](uint32_t v0, uint32_t v1, int* bad) {
         std::vector<Memo> memo(1024, Memo{0u, 0.0f, false});
-        for (uint32_t i = i0; i < i1; i++) {
-            DevEvent& d = staged[i];
-            d.frame = events_host[i].frame;
-            d.note_id = events_host[i].note_id;
-            d.freq = events_host[i].freq;
-            d.note_on = events_host[i].note_on;
-            uint32_t key;
-            memcpy(&key, &events_host[i].freq, 4);
-            Memo& m = memo[(key * 2654435761u) >> 22];
-            if (!m.valid || m.key != key) {
-                m.key = key;
-                m.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, sr);
-                m.valid = true;
+        for (uint32_t v = v0; v < v1; v++) {
+            const uint32_t i0 = event_off_host[v], i1 = event_off_host[v + 1];
+            if (i1 < i0 || i1 > n) {
+                *bad = 1;
+                return;
             }
-            d.cutoff = m.cutoff;
-            d.cnt0 = d.flags = d.pad = 0;
+            uint32_t prev = 0;
+            for (uint32_t i = i0; i < i1; i++) {
+                DevEvent& d = staged[i];
+                d.frame = events_host[i].frame;
+                if (d.frame < prev || d.frame >= total_frames) {
+                    *bad = 2;
+                    return;
+                }
+                prev = d.frame;
+                d.note_id = events_host[i].note_id;
+                d.freq = events_host[i].freq;
+                d.note_on = events_host[i].note_on;
+                uint32_t key;
+                memcpy(&key, &events_host[i].freq, 4);
+                Memo& m = memo[(key * 2654435761u) >> 22];
+                if (!m.valid || m.key != key) {
+                    m.key = key;
+                    m.cutoff = zcu_filter_cutoff_from_frequency(events_host[i].freq * 8.0f, sr);
+                    m.valid = true;
+                }
+                d.cutoff = m.cutoff;
+                d.cnt0 = d.flags = d.pad = 0;
+            }
         }
     };
     uint32_t nthreads = 1;
     if (n >= (1u << 16)) nthreads = std::min(4u, std::max(1u, std::thread::hardware_concurrency()));  // measured: 4 is the knee
     if (const char* e = getenv("ZCU_HOST_THREADS")) nthreads = (uint32_t)std::max(1, atoi(e));
+    nthreads = std::min(nthreads, 64u);
+    int bad[64] = {0};
+    if (event_off_host[0] != 0) bad[0] = 1;
     if (nthreads <= 1) {
-        expand(0, n);
-    } else {
+        if (!bad[0]) expand(0, V, &bad[0]);
+    } else if (!bad[0]) {
         std::vector<std::thread> pool;
-        const uint32_t per = (n + nthreads - 1) / nthreads;
         for (uint32_t t = 1; t < nthreads; t++) {
-            const uint32_t i0 = std::min(n, t * per), i1 = std::min(n, (t + 1) * per);
-            if (i0 < i1) pool.emplace_back(expand, i0, i1);
+            const uint32_t a = (uint32_t)((uint64_t)V * t / nthreads), b = (uint32_t)((uint64_t)V * (t + 1) / nthreads);
+            if (a < b) pool.emplace_back(expand, a, b, &bad[t]);
         }
-        expand(0, std::min(n, per));
+        expand(0, (uint32_t)((uint64_t)V / nthreads), &bad[0]);
         for (auto& th : pool) th.join();
+    }
+    for (uint32_t t = 0; t < nthreads; t++) {
+        if (bad[t]) {
+            r->h_flip ^= 1;  // the staging buffer was not handed to a copy
+            return zcu_fail(ctx, ZCU_ERR_INVALID, bad[t] == 1 ? "event_off must start at 0 and be monotone"
+                                                               : "events of a voice must be chronological with frames inside the render");
+        }
     }
     // upload and pre-pass of this job on the upload stream, into the table set the current run is not reading
     const int nx = r->ts_cur ^ 1;
@@ -639,7 +693,7 @@ int zcu_render_run(zcu_ctx* ctx, zcu_render* r, zcu_buf* mix) {
     ZCU_REQUIRE(ctx, r && mix, "null argument");
     ZCU_REQUIRE(ctx, r->d_events != nullptr, "zcu_render_set_events has not been called");
     ZCU_REQUIRE(ctx, mix->frames == r->cfg.total_frames && mix->voices == r->cfg.channels, "mix must be [total_frames][channels]");
-    return render_blocks(ctx, r, mix->d, nullptr, 0, 0, r->cfg.total_frames);
+    return render_blocks(ctx, r, mix->d, VoutReq{nullptr, 0, 0, 0, 0}, r->cfg.total_frames);
 }
 
 int zcu_render_run_voices(zcu_ctx* ctx, zcu_render* r, uint32_t first_frame, zcu_buf* out_voices) {
@@ -648,7 +702,17 @@ int zcu_render_run_voices(zcu_ctx* ctx, zcu_render* r, uint32_t first_frame, zcu
     ZCU_REQUIRE(ctx, r->d_events != nullptr, "zcu_render_set_events has not been called");
     ZCU_REQUIRE(ctx, out_voices->voices == r->cfg.voices, "out_voices must be [frames][voices]");
     ZCU_REQUIRE(ctx, (uint64_t)first_frame + out_voices->frames <= r->cfg.total_frames, "window beyond the render");
-    return render_blocks(ctx, r, nullptr, out_voices->d, first_frame, out_voices->frames, first_frame + out_voices->frames);
+    return render_blocks(ctx, r, nullptr, VoutReq{out_voices->d, first_frame, out_voices->frames, 0, r->cfg.voices}, first_frame + out_voices->frames);
+}
+
+int zcu_render_run_voice_window(zcu_ctx* ctx, zcu_render* r, uint32_t first_voice, uint32_t first_frame, zcu_buf* out_voices) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, r && out_voices, "null argument");
+    ZCU_REQUIRE(ctx, r->d_events != nullptr, "zcu_render_set_events has not been called");
+    ZCU_REQUIRE(ctx, out_voices->voices > 0 && (uint64_t)first_voice + out_voices->voices <= r->cfg.voices, "voice window beyond the bank");
+    ZCU_REQUIRE(ctx, (uint64_t)first_frame + out_voices->frames <= r->cfg.total_frames, "window beyond the render");
+    return render_blocks(ctx, r, nullptr, VoutReq{out_voices->d, first_frame, out_voices->frames, first_voice, out_voices->voices},
+                         first_frame + out_voices->frames);
 }
 
 int zcu_render_set_profiling(zcu_render* r, int enabled) {
@@ -696,6 +760,12 @@ uint64_t zcu_render_launches_per_run(const zcu_render* r) {
     const uint64_t nblocks = (r->cfg.total_frames + r->block_frames - 1) / r->block_frames;
     if (r->cfg.mode == ZCU_RENDER_SEGMENTS) return 2 * nblocks;
     return r->cfg.mode == ZCU_RENDER_SCAN ? 4 * nblocks : 1 + 2 * nblocks;
+}
+
+int zcu_render_set_segments(zcu_render* r, uint32_t segments_per_launch) {
+    if (!r || r->cfg.mode != ZCU_RENDER_SEGMENTS) return ZCU_ERR_INVALID;
+    r->forced_nseg = segments_per_launch;
+    return ZCU_OK;
 }
 
 int zcu_render_segment_info(zcu_ctx* ctx, zcu_render* r, uint32_t* segments, uint32_t* buffers_per_segment, uint32_t* warm_sum, uint32_t* warm_max) {

@@ -61,8 +61,9 @@ struct RenderArgs {
     const uint32_t* event_off;
     const DevEvent* events;  // note events with the host-evaluated filter cutoff, 32 bytes each
     float* partial;  // [nwarps][F1-F0][C] or null
-    float* vout;     // [vout_frames][V] window or null
+    float* vout;     // [vout_frames][vout_nv] window or null
     uint32_t vout_first, vout_frames;
+    uint32_t vout_v0, vout_nv;
     uint32_t debug_skip_mask;  // bit w set: stage w does no arithmetic (profiling aid; results are then wrong)
     unsigned long long* debug_cycles;  // optional [nCTA][4 warps][2]: cycles busy / cycles total (profiling aid)
 };
@@ -451,7 +452,8 @@ __global__ void __launch_bounds__(128, 1) k_render_nice(RenderArgs a) {
             } else if (VOUT) {
                 for (uint32_t j = 0; j < n; j++) {
                     const uint32_t f = tf + j;
-                    if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames) a.vout[(size_t)(f - a.vout_first) * a.V + v] = O[sb][j][lane];
+                    if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames && v - a.vout_v0 < a.vout_nv)
+                        a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = O[sb][j][lane];
                 }
             } else {
                 // lane sums frames lane, lane+32, ... over the warp's 32 voices with their pan gains

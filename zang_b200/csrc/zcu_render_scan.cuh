@@ -57,8 +57,9 @@ struct ScanArgs {
     float2* sstart;           // [nchunks][V] filter state at the chunk start
     double2* fstate;          // [V] filter state carried across launches
     float* partial;           // [nvgroups][F1-F0][C]
-    float* vout;
+    float* vout;              // [vout_frames][vout_nv] window of the un-mixed voice outputs, or null
     uint32_t vout_first, vout_frames;
+    uint32_t vout_v0, vout_nv;  // voices [vout_v0, vout_v0 + vout_nv) of the window
 };
 
 // NiceInstrument's envelope params (modules.zig:238-245)
@@ -475,7 +476,8 @@ __global__ void __launch_bounds__(128, 4) k_nice_scan_render(ScanArgs a) {
         if (VOUT) {
             for (uint32_t jj = 0; jj < tn; jj++) {
                 const uint32_t f = F + t0 + jj;
-                if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames) a.vout[(size_t)(f - a.vout_first) * a.V + v] = O[jj][lane];
+                if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames && v - a.vout_v0 < a.vout_nv)
+                    a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = O[jj][lane];
             }
         } else {
             // lane sums frames lane, lane+32, ... over the warp's 32 voices with their pan gains (the reference's

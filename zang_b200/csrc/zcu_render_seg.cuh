@@ -29,6 +29,7 @@ struct SegArgs {
     uint32_t seg_chunks;   // chunks per segment
     float2* carry;         // [V] filter state at F0 (read by segment 0), at F1 (written by the last segment)
     uint32_t* warm_stats;  // optional [2]: sum and max of warm-up chunks over all warp tasks (diagnostics)
+    uint32_t need_carry;   // VOUT: a later launch follows, so the last segment must run even outside the window
 };
 
 // M = M * A^n  (A^n acts BEFORE M in time)
@@ -111,6 +112,13 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
     const uint32_t Fs = a.F0 + seg * g.seg_chunks * a.L;
     if (Fs >= a.F1) return;
     const uint32_t Fe = (uint32_t)min((uint64_t)a.F1, (uint64_t)Fs + (uint64_t)g.seg_chunks * a.L);
+    if (VOUT) {
+        // A voice window is rendered with the segmentation of the whole job (the arithmetic under test is that of
+        // zcu_render_run); warp tasks that cannot touch the window are dropped.
+        const bool frames_hit = Fe > a.vout_first && Fs < a.vout_first + a.vout_frames;
+        const bool voices_hit = vgroup * 32 + 32 > a.vout_v0 && vgroup * 32 < a.vout_v0 + a.vout_nv;
+        if (!(frames_hit && voices_hit) && !(g.need_carry && Fe == a.F1)) return;
+    }
 
     // ---- how many mix buffers of warm-up does the Filter need? (per voice, then the warp's maximum)
     uint32_t wc = 0;
@@ -233,7 +241,8 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
         if (VOUT) {
             for (uint32_t jj = 0; jj < tn; jj++) {
                 const uint32_t f = T0 + jj;
-                if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames) a.vout[(size_t)(f - a.vout_first) * a.V + v] = O[jj][lane];
+                if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames && v - a.vout_v0 < a.vout_nv)
+                    a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = O[jj][lane];
             }
         } else {
             for (uint32_t fr = lane; fr < tn; fr += 32) {

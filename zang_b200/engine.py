@@ -647,6 +647,11 @@ class Render:
     def run_voices(self, first_frame, out_voices):
         _check(self.ctx, lib.zcu_render_run_voices(self.ctx._h, self._h, first_frame, out_voices._h))
 
+    def run_voice_window(self, first_voice, first_frame, out_voices):
+        """Un-mixed output of voices [first_voice, first_voice + out.voices) over [first_frame, first_frame + out.frames),
+        rendered with the launches and time segments of the whole job."""
+        _check(self.ctx, lib.zcu_render_run_voice_window(self.ctx._h, self._h, int(first_voice), int(first_frame), out_voices._h))
+
     def set_profiling(self, enabled=True):
         _check(self.ctx, lib.zcu_render_set_profiling(self._h, 1 if enabled else 0))
 
@@ -661,6 +666,12 @@ class Render:
         ms, n = C.c_float(), C.c_uint32()
         _check(self.ctx, lib.zcu_render_aux_kernel_ms(self.ctx._h, self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def set_segments(self, segments_per_launch):
+        """ZCU_RENDER_SEGMENTS: force the number of time segments per launch (0 = sized to the GPU)."""
+        rc = lib.zcu_render_set_segments(self._h, int(segments_per_launch))
+        if rc != L.OK:
+            raise ZangCuError("zcu_render_set_segments: not a ZCU_RENDER_SEGMENTS render")
 
     def segment_info(self):
         """ZCU_RENDER_SEGMENTS: dict(segments, buffers_per_segment, warm_sum, warm_max) of the last run."""

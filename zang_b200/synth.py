@@ -7,7 +7,7 @@ buffer.  Every voice has its own pulse colour and pan position.
 """
 import numpy as np
 
-from . import _lib as L
+from . import abi as L  # dtypes only: generating a workload must not need the CUDA library
 
 SEED = 0x5EED
 
@@ -115,6 +115,30 @@ def pcm_loop(frames=192437, seed=SEED):
     env = np.exp(-((t % beat) / (0.12 * beat)))
     x = 0.6 * env * rng.uniform(-1.0, 1.0, size=frames) + 0.3 * np.sin(2 * np.pi * 55.0 * t / 44100.0)
     return np.clip(np.round(x * 32767.0), -32768, 32767).astype("<i2").view(np.uint8).copy()
+
+
+DRUMLOOP_MD5 = "29dec84da4c4abc7d54416c1d8a3bf5f"  # /root/reference/examples/drumloop.wav
+
+
+def drumloop_pcm():
+    """PCM bytes of the reference's own Sampler asset (examples/example_sampler.zig:66 embeds examples/drumloop.wav: mono
+    s16 44.1 kHz, 384 874 data bytes after a 44-byte RIFF header, parsed as example_sampler.zig:26-45 does), shipped as the
+    fixture tests/golden/drumloop.wav.  Returns (uint8 array, name); falls back to the synthetic stand-in when the fixture
+    is absent, and says so in the name."""
+    import hashlib
+    import os
+    import struct
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "drumloop.wav")
+    try:
+        raw = open(path, "rb").read()
+    except OSError:
+        return pcm_loop(), "synthetic stand-in for drumloop.wav"
+    assert hashlib.md5(raw).hexdigest() == DRUMLOOP_MD5, "tests/golden/drumloop.wav is not the reference's asset"
+    assert raw[:4] == b"RIFF" and raw[8:12] == b"WAVE" and raw[12:16] == b"fmt " and raw[36:40] == b"data"
+    fmt, channels, rate, _, _, bits = struct.unpack("<HHIIHH", raw[20:36])
+    (nbytes,) = struct.unpack("<I", raw[40:44])
+    assert (fmt, channels, rate, bits, nbytes) == (1, 1, 44100, 16, 384874)
+    return np.frombuffer(raw[44:44 + nbytes], dtype=np.uint8).copy(), "examples/drumloop.wav"
 
 
 def sampler_bank(voices, total_frames, sample_rate=44100.0, seed=SEED, mean_gap=0.5):
