@@ -204,7 +204,7 @@ int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& v
 int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame) {
     const zcu_render_config& c = r->cfg;
     constexpr int RT = 64;
-    const size_t smem = scan_render_smem_bytes<RT>();
+    const size_t smem = seg_render_smem_bytes<RT>();
     bool& attr_set = r->attr_set[1];
     if (!attr_set) {
         ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -151,41 +151,59 @@ struct TrigCursor {
 
 // ---- stage 0: zero(temps[0]); PulseOsc.paint (constant frequency); multiplyWithScalar(temps[0], 0.5) ----
 struct PulseStage {
+    // What the stage emits is PulseOsc's value x 0.5 (multiplyWithScalar, modules.zig:226).  Halving is exact (no value of
+    // the six cases is subnormal: they are sums with +-0.7 or +-0.7 itself), and fl(a/2 + b/2) = fl(a + b)/2, so the span
+    // constants are kept pre-halved: g = 0.35, gdf = gain/utof23(ifreq) (the reference's gdf*2, halved), c121, c212.
+    // A span whose frequency is out of range (PulseOsc.zig:82-84: paints nothing) has g = ng = 0 and ifreq = 0: the code is
+    // then 0b000 or 0b011 for ever and the value +0.  None of the six values can be -0 (a cancelling sum rounds to +0), so
+    // the reference's `0 + v` into the zeroed temp changes nothing.
     uint32_t cnt, ifreq, brpt;
-    float gdf2, col, cc121, cc212;
-    bool pskip;
+    float gdf, col, c121, c212, g, ng;
+    bool pskip, was_up;  // was_up: (cnt - ifreq) < brpt, the previous sample's is_up, carried instead of recomputed
+    __device__ void init(float color, uint32_t cnt0) {
+        brpt = ftou32(clamp01(color));
+        col = utof23(brpt);
+        cnt = cnt0;
+        ifreq = 0;
+        pskip = true;
+        gdf = c121 = c212 = g = ng = 0.0f;
+        was_up = cnt < brpt;
+    }
+    __device__ __forceinline__ void set_cnt(uint32_t c) {
+        cnt = c;
+        was_up = (uint32_t)(cnt - ifreq) < brpt;
+    }
     __device__ void begin_span(float sample_rate, float freq) {
         const float gain = 0.7f;
         pskip = (freq < 0.0f || freq > sample_rate / 8.0f);  // PulseOsc.zig:82-84: paints nothing, cnt untouched
         ifreq = 0;
+        g = ng = 0.0f;
         if (!pskip) {
             const float basefrq = 4294967296.0f / sample_rate;
             ifreq = (uint32_t)(basefrq * freq);
-            const float gdf = gain / utof23(ifreq);
-            gdf2 = gdf * 2.0f;  // exact scaling, (gdf*2)*x is the reference's evaluation order
-            cc121 = gdf2 * (col - 1.0f) + gain;
-            cc212 = gdf2 * col - gain;
+            gdf = gain / utof23(ifreq);  // the reference uses (gdf*2)*x + gain; all of it halved here
+            g = gain * 0.5f;
+            ng = -g;
+            c121 = gdf * (col - 1.0f) + g;
+            c212 = gdf * col - g;
         }
+        was_up = (uint32_t)(cnt - ifreq) < brpt;  // also how PulseOsc.zig:96 seeds its history
     }
     // :98-112, then x0.5.  The reference's 2-bit history `state` always holds (previous, current) values of
-    // `cnt < brpt`, and the previous one is (cnt - ifreq) < brpt (that is also how :96 seeds it), so the 3-bit
-    // transition code is a pure function of cnt: bits (wrapped = cnt < ifreq, was_up, is_up).  The six reachable
-    // codes are selected with predicates; 0b001 and 0b110 cannot occur (they would need ifreq > 2^32).
+    // `cnt < brpt`, so the 3-bit transition code is a pure function of cnt: bits (wrapped = cnt < ifreq, was_up, is_up).
+    // The six reachable codes are selected with predicates; 0b001 and 0b110 cannot occur (they would need ifreq > 2^32).
     __device__ __forceinline__ float sample() {
-        const float gain = 0.7f;
         const float p = utof23(cnt);
         const bool is_up = cnt < brpt;
-        const bool was_up = (uint32_t)(cnt - ifreq) < brpt;
         const bool wrapped = cnt < ifreq;
-        const float v2 = gdf2 * (col - p) + gain;  // 0b010 up down
-        const float v5 = gdf2 * p - gain;          // 0b101 down up
-        const float w1 = is_up ? (was_up ? cc121 : v5) : cc212;  // wrapped: 0b111, 0b101, 0b100
-        const float w0 = was_up ? (is_up ? gain : v2) : -gain;   // not wrapped: 0b011, 0b010, 0b000
-        float v = wrapped ? w1 : w0;
-        v = pskip ? 0.0f : v;
+        const float v2 = gdf * (col - p) + g;  // 0b010 up down
+        const float v5 = gdf * p - g;          // 0b101 down up
+        const float w1 = is_up ? (was_up ? c121 : v5) : c212;  // wrapped: 0b111, 0b101, 0b100
+        const float w0 = was_up ? (is_up ? g : v2) : ng;       // not wrapped: 0b011, 0b010, 0b000
+        const float v = wrapped ? w1 : w0;
+        was_up = is_up;
         cnt += ifreq;  // ifreq == 0 when skipped
-        const float t0 = 0.0f + v;
-        return t0 * 0.5f;
+        return v;
     }
 };
 
@@ -205,9 +223,10 @@ struct FilterStage {
         const float h = in - b * res - l;
         b += cut * h;
         // low_pass output is 0 + (l*1 + b*0 + h*0) (Filter.zig:146 into the zeroed temps[1]).  While b and h are
-        // finite, b*0 and h*0 are signed zeros and the sum is l, or +0 when l is a zero of either sign; 0 + l has
-        // exactly those bits.  The recurrence keeps l, b, h finite for cut, res in [0,1] and a bounded input.
-        return 0.0f + l;
+        // finite, b*0 and h*0 are signed zeros and the sum is l, or +0 when l is a zero of either sign.  Only the sign of
+        // a zero can differ from l itself, and it cannot reach the output: the voice's value is 0 + env*y (multiply()
+        // accumulates into the zeroed output, modules.zig:246), which is +0 for a product of either sign.
+        return l;
     }
 };
 
@@ -240,14 +259,19 @@ struct EnvStage {
     }
     // Per-run invariants of the fast path (no phase change can happen inside a run, see safe_run).
     struct Run {
-        float step, base;  // ramping: t_step, 0   else: 0, flat value (or 0)
+        // ramping: (t_step, start, goal - start); otherwise (0, flat value or 0, 0): the ramp formula start + tp*gms then
+        // yields the flat value itself (tp is finite and tp*0 = +-0), so the per-sample code needs no select.  Only the
+        // sign of a zero can differ from the reference's 0 + value, and that cannot reach the output (see FilterStage).
+        float step, start, gms;
         bool ramp, lin, sq;
     };
     __device__ __forceinline__ Run begin_run() const {
         Run r;
         r.ramp = ramping();
         r.step = r.ramp ? e.painter.t_step : 0.0f;  // t + 0 leaves t untouched
-        r.base = e.mode == EnvelopeCore::M_FLAT ? e.flat : 0.0f;
+        const float base = e.mode == EnvelopeCore::M_FLAT ? e.flat : 0.0f;
+        r.start = r.ramp ? e.painter.start : base;
+        r.gms = r.ramp ? e.painter.gms : 0.0f;
         r.lin = e.painter.kind == ZCU_CURVE_LINEAR;
         r.sq = e.painter.kind == ZCU_CURVE_SQUARED;
         return r;
@@ -267,8 +291,8 @@ struct EnvStage {
             const float curved = 1.0f - (r.sq ? sq : sq * it);
             tp = r.lin ? p.t : curved;
         }
-        lv = p.start + tp * p.gms;
-        return 0.0f + (r.ramp ? lv : r.base);
+        lv = r.start + tp * r.gms;
+        return lv;
     }
     __device__ __forceinline__ void end_run(const Run& r, float lv, bool any) {
         if (r.ramp && any) e.painter.last_value = lv;
@@ -309,12 +333,7 @@ __global__ void __launch_bounds__(128, 1) k_render_nice(RenderArgs a) {
     EnvStage es;
     if (warp == 0) {
         const float color = valid ? a.color[v] : 0.0f;
-        ps.brpt = ftou32(clamp01(color));
-        ps.col = utof23(ps.brpt);
-        ps.cnt = st.cnt;
-        ps.ifreq = 0;
-        ps.pskip = true;
-        ps.gdf2 = ps.cc121 = ps.cc212 = 0.0f;
+        ps.init(color, st.cnt);
     } else if (warp == 1) {
         fs.l = st.l;
         fs.b = st.b;
@@ -453,7 +472,7 @@ __global__ void __launch_bounds__(128, 1) k_render_nice(RenderArgs a) {
                 for (uint32_t j = 0; j < n; j++) {
                     const uint32_t f = tf + j;
                     if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames && v - a.vout_v0 < a.vout_nv)
-                        a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = O[sb][j][lane];
+                        a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = 0.0f + O[sb][j][lane];  // multiply() accumulates into the zeroed output: -0 becomes +0
                 }
             } else {
                 // lane sums frames lane, lane+32, ... over the warp's 32 voices with their pan gains

@@ -291,19 +291,14 @@ __global__ void __launch_bounds__(128) k_nice_scan_zs(ScanArgs a) {
     PulseStage ps;
     FilterStage fs;
     const float color = valid ? a.color[v] : 0.0f;
-    ps.brpt = ftou32(clamp01(color));
-    ps.col = utof23(ps.brpt);
-    ps.cnt = 0;
-    ps.ifreq = 0;
-    ps.pskip = true;
-    ps.gdf2 = ps.cc121 = ps.cc212 = 0.0f;
+    ps.init(color, 0u);
     fs.l = fs.b = 0.0f;
     fs.cut = fs.res = 0.0f;
     Mat2 M{1.0, 0.0, 0.0, 1.0}, A{1.0, 0.0, 0.0, 1.0};
     uint32_t seg = 0;
     if (cur.active) {
         ps.begin_span(a.sample_rate, cur.cur.freq);
-        ps.cnt = cur.cur.cnt0 + (F - cur.cur.frame) * ps.ifreq;
+        ps.set_cnt(cur.cur.cnt0 + (F - cur.cur.frame) * ps.ifreq);
         fs.begin_span(cur.cur.cutoff);
         A = filter_hom(fs.cut, fs.res);
     }
@@ -389,12 +384,7 @@ __global__ void __launch_bounds__(128, 4) k_nice_scan_render(ScanArgs a) {
     FilterStage fs;
     EnvStage es;
     const float color = valid ? a.color[v] : 0.0f;
-    ps.brpt = ftou32(clamp01(color));
-    ps.col = utof23(ps.brpt);
-    ps.cnt = 0;
-    ps.ifreq = 0;
-    ps.pskip = true;
-    ps.gdf2 = ps.cc121 = ps.cc212 = 0.0f;
+    ps.init(color, 0u);
     fs.l = fs.b = 0.0f;
     fs.cut = fs.res = 0.0f;
     if (valid) {
@@ -405,7 +395,7 @@ __global__ void __launch_bounds__(128, 4) k_nice_scan_render(ScanArgs a) {
     env_reset(es.e, a.sample_rate);
     if (cur.active) {
         ps.begin_span(a.sample_rate, cur.cur.freq);
-        ps.cnt = cur.cur.cnt0 + (F - cur.cur.frame) * ps.ifreq;
+        ps.set_cnt(cur.cur.cnt0 + (F - cur.cur.frame) * ps.ifreq);
         fs.begin_span(cur.cur.cutoff);
         const EnvSnap s = a.snaps[cur.next_event - 1];
         es.e.state = s.state;
@@ -477,7 +467,7 @@ __global__ void __launch_bounds__(128, 4) k_nice_scan_render(ScanArgs a) {
             for (uint32_t jj = 0; jj < tn; jj++) {
                 const uint32_t f = F + t0 + jj;
                 if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames && v - a.vout_v0 < a.vout_nv)
-                    a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = O[jj][lane];
+                    a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = 0.0f + O[jj][lane];  // multiply() accumulates into the zeroed output: -0 becomes +0
             }
         } else {
             // lane sums frames lane, lane+32, ... over the warp's 32 voices with their pan gains (the reference's

@@ -32,6 +32,26 @@ struct SegArgs {
     uint32_t need_carry;   // VOUT: a later launch follows, so the last segment must run even outside the window
 };
 
+// shared-memory tile of a warp: RT frames x 32 voices, row stride 34 floats (rows 8-byte aligned, conflict-free both for the
+// per-voice column writes and for the mix's 8-byte row reads)
+constexpr int kSegTileStride = 34;
+template <int RT>
+constexpr size_t seg_render_smem_bytes() {
+    return (size_t)(4 * RT * kSegTileStride + 4 * 2 * 32) * sizeof(float);
+}
+
+// Blackwell packed f32 pairs (PTX ISA 8.6, sm_100): one issue slot for two IEEE fused multiply-adds
+__device__ __forceinline__ unsigned long long fma_f32x2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ float sum_f32x2(unsigned long long v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return lo + hi;
+}
+
 // M = M * A^n  (A^n acts BEFORE M in time)
 __device__ inline void mat2_apply_pow_right(Mat2& M, Mat2 A, uint32_t n) {
     while (n) {
@@ -95,13 +115,14 @@ __device__ __forceinline__ void seg_warm_up(const ScanArgs& a, ChunkCursor& cur,
 }
 
 template <int C, bool VOUT, int RT>
-__global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const float2* __restrict__ carry_in, float2* __restrict__ carry_out) {
+__global__ void __launch_bounds__(128, 6) k_nice_seg_render(SegArgs g, const float2* __restrict__ carry_in, float2* __restrict__ carry_out) {
     const ScanArgs& a = g.s;
     extern __shared__ float smem[];
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = threadIdx.x & 31u;
-    float(*O)[33] = reinterpret_cast<float(*)[33]>(smem + (size_t)warp * RT * 33);
-    float(*gn)[32] = reinterpret_cast<float(*)[32]>(smem + (size_t)4 * RT * 33 + (size_t)warp * C * 32);
+    constexpr int OS = kSegTileStride;
+    float(*O)[OS] = reinterpret_cast<float(*)[OS]>(smem + (size_t)warp * RT * OS);
+    float(*gn)[32] = reinterpret_cast<float(*)[32]>(smem + (size_t)4 * RT * OS + (size_t)warp * C * 32);
     const uint32_t task = blockIdx.x * 4 + warp;
     if (task >= a.nvgroups * g.nseg) return;
     const uint32_t vgroup = task % a.nvgroups;
@@ -150,12 +171,7 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
     FilterStage fs;
     EnvStage es;
     const float color = valid ? a.color[v] : 0.0f;
-    ps.brpt = ftou32(clamp01(color));
-    ps.col = utof23(ps.brpt);
-    ps.cnt = 0;
-    ps.ifreq = 0;
-    ps.pskip = true;
-    ps.gdf2 = ps.cc121 = ps.cc212 = 0.0f;
+    ps.init(color, 0u);
     fs.l = fs.b = 0.0f;
     fs.cut = fs.res = 0.0f;
     if (valid && Fw == a.F0) {
@@ -165,7 +181,7 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
     }
     if (cur.active) {
         ps.begin_span(a.sample_rate, cur.cur.freq);
-        ps.cnt = cur.cur.cnt0 + (Fw - cur.cur.frame) * ps.ifreq;
+        ps.set_cnt(cur.cur.cnt0 + (Fw - cur.cur.frame) * ps.ifreq);
         fs.begin_span(cur.cur.cutoff);
     }
     if (Fw < Fs) seg_warm_up(a, cur, ps, fs, Fw, Fs);
@@ -216,12 +232,12 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
 #pragma unroll 4
                     for (uint32_t r = 0; r < run; r++) {
                         const float y = fs.sample(ps.sample());
-                        oo[r * 33] = es.sample_fast<true>(er, lv) * y;
+                        oo[r * OS] = es.sample_fast<true>(er, lv) * y;
                     }
                 } else {
                     for (uint32_t r = 0; r < run; r++) {
                         const float y = fs.sample(ps.sample());
-                        oo[r * 33] = es.sample_fast<false>(er, lv) * y;
+                        oo[r * OS] = es.sample_fast<false>(er, lv) * y;
                     }
                 }
                 es.end_run(er, lv, run > 0);
@@ -232,7 +248,7 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
                         const float y = fs.sample(ps.sample());
                         o = es.sample_careful() * y;
                     }
-                    oo[r * 33] = o;
+                    oo[r * OS] = o;
                 }
             }
             j += run;
@@ -242,24 +258,54 @@ __global__ void __launch_bounds__(128, 4) k_nice_seg_render(SegArgs g, const flo
             for (uint32_t jj = 0; jj < tn; jj++) {
                 const uint32_t f = T0 + jj;
                 if (valid && f >= a.vout_first && f < a.vout_first + a.vout_frames && v - a.vout_v0 < a.vout_nv)
-                    a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = O[jj][lane];
+                    a.vout[(size_t)(f - a.vout_first) * a.vout_nv + (v - a.vout_v0)] = 0.0f + O[jj][lane];  // multiply() accumulates into the zeroed output: -0 becomes +0
             }
         } else {
-            for (uint32_t fr = lane; fr < tn; fr += 32) {
-                float acc[C];
-#pragma unroll
-                for (int c = 0; c < C; c++) acc[c] = 0.0f;
-#pragma unroll 8
-                for (int vv = 0; vv < 32; vv++) {
-                    const float x = O[fr][vv];
-#pragma unroll
-                    for (int c = 0; c < C; c++) acc[c] = fmaf(gn[c][vv], x, acc[c]);
+            if (C == 2 && RT == 64) {
+                // Lane j sums frames j and j + 32 over the warp's 32 voices.  Voices are taken in pairs: one LDS.64 reads two
+                // adjacent voices of a frame row (stride 34 floats: conflict-free for 8-byte accesses), the pan gains of four
+                // voices come as one LDS.128 per channel, and each fma.rn.f32x2 does two voices of one (frame, channel), so
+                // the mix costs ~1.75 issue slots per voice-sample instead of 5 (even and odd voices accumulate separately and
+                // meet at the end; the voice summation order is not the reference's anyway: tolerance 1e-5 x sum|gain|).
+                typedef unsigned long long u64;
+                const float* rowA = &O[lane][0];
+                const float* rowB = &O[lane + 32][0];
+                u64 a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll 2
+                for (int q = 0; q < 8; q++) {
+                    const ulonglong2 g0 = *reinterpret_cast<const ulonglong2*>(&gn[0][q * 4]);
+                    const ulonglong2 g1 = *reinterpret_cast<const ulonglong2*>(&gn[1][q * 4]);
+                    const u64 xa0 = *reinterpret_cast<const u64*>(rowA + q * 4), xa1 = *reinterpret_cast<const u64*>(rowA + q * 4 + 2);
+                    const u64 xb0 = *reinterpret_cast<const u64*>(rowB + q * 4), xb1 = *reinterpret_cast<const u64*>(rowB + q * 4 + 2);
+                    a0 = fma_f32x2(g0.x, xa0, a0);
+                    a1 = fma_f32x2(g1.x, xa0, a1);
+                    b0 = fma_f32x2(g0.x, xb0, b0);
+                    b1 = fma_f32x2(g1.x, xb0, b1);
+                    a0 = fma_f32x2(g0.y, xa1, a0);
+                    a1 = fma_f32x2(g1.y, xa1, a1);
+                    b0 = fma_f32x2(g0.y, xb1, b0);
+                    b1 = fma_f32x2(g1.y, xb1, b1);
                 }
-                float* dst = a.partial + ((size_t)vgroup * nframes + (T0 - a.F0 + fr)) * C;
-                if (C == 2)
-                    *reinterpret_cast<float2*>(dst) = make_float2(acc[0], acc[1]);
-                else
-                    dst[0] = acc[0];
+                float* dst = a.partial + ((size_t)vgroup * nframes + (T0 - a.F0 + lane)) * 2;
+                if (lane < tn) *reinterpret_cast<float2*>(dst) = make_float2(sum_f32x2(a0), sum_f32x2(a1));
+                if (lane + 32 < tn) *reinterpret_cast<float2*>(dst + 64) = make_float2(sum_f32x2(b0), sum_f32x2(b1));
+            } else {
+                for (uint32_t fr = lane; fr < tn; fr += 32) {
+                    float acc[C];
+#pragma unroll
+                    for (int c = 0; c < C; c++) acc[c] = 0.0f;
+#pragma unroll 8
+                    for (int vv = 0; vv < 32; vv++) {
+                        const float x = O[fr][vv];
+#pragma unroll
+                        for (int c = 0; c < C; c++) acc[c] = fmaf(gn[c][vv], x, acc[c]);
+                    }
+                    float* dst = a.partial + ((size_t)vgroup * nframes + (T0 - a.F0 + fr)) * C;
+                    if (C == 2)
+                        *reinterpret_cast<float2*>(dst) = make_float2(acc[0], acc[1]);
+                    else
+                        dst[0] = acc[0];
+                }
             }
         }
         __syncwarp();
