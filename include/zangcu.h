@@ -490,6 +490,78 @@ int zcu_render_set_segments(zcu_render*, uint32_t segments_per_launch);
 int zcu_render_segment_info(zcu_ctx*, zcu_render*, uint32_t* segments, uint32_t* buffers_per_segment, uint32_t* warm_sum,
                             uint32_t* warm_max);
 
+/* ---- fused module graphs ---------------------------------------------------------
+ * The general form of zcu_render_*: an instrument's paint() body given as an instruction list and compiled at run time
+ * (NVRTC, sm_100a, --fmad=false) into ONE kernel that runs the whole list sample by sample with the temps in registers.
+ * The list is the reference's own: src/zangscript/codegen.zig:60-121 (`Instruction`: copy_buffer, float_to_buffer,
+ * arith_*, call) as executed by src/zangscript/runtime.zig:445-740, plus the zang basics (src/zang/basics.zig:12-78) that
+ * hand-written instruments use (examples/modules.zig).  Every instruction works on the span table it names; a CALL is the
+ * module's paint(): it ACCUMULATES into its output, so the reference's `zero; paint` pair is two instructions (the script
+ * runtime's `call`, runtime.zig:482-506, is ZERO followed by CALL).  Results equal the per-module path bit for bit
+ * (tests/test_gpu_graph.py): no instruction of the reference reads any sample of a buffer but the one it is writing.
+ * An instruction that reads a temp at a frame where nothing wrote it this call sees an unspecified value. */
+typedef struct zcu_graph zcu_graph;
+
+enum { ZCU_GREF_NONE = 0, ZCU_GREF_TEMP = 1, ZCU_GREF_OUTPUT = 2, ZCU_GREF_INPUT = 3 };
+typedef struct zcu_graph_ref {
+    int32_t kind;    /* ZCU_GREF_*: a temp of the graph, one of its outputs, or one of its external input buffers */
+    uint32_t index;
+} zcu_graph_ref;
+
+enum { ZCU_GI_BASIC = 0, ZCU_GI_ARITH = 1, ZCU_GI_CALL = 2 };
+/* basics.zig:12-78, as zcu_zero .. zcu_multiply_with_scalar */
+enum {
+    ZCU_BASIC_ZERO = 0, ZCU_BASIC_SET = 1, ZCU_BASIC_COPY = 2, ZCU_BASIC_ADD = 3, ZCU_BASIC_ADD_INTO = 4, ZCU_BASIC_ADD_SCALAR = 5,
+    ZCU_BASIC_ADD_SCALAR_INTO = 6, ZCU_BASIC_MULTIPLY = 7, ZCU_BASIC_MULTIPLY_WITH = 8, ZCU_BASIC_MULTIPLY_SCALAR = 9,
+    ZCU_BASIC_MULTIPLY_WITH_SCALAR = 10
+};
+/* the script runtime's arithmetic that OVERWRITES its output (runtime.zig:528-700; add and mul are basics there) */
+enum { ZCU_ARITH_SUB = 0, ZCU_ARITH_DIV = 1, ZCU_ARITH_MIN = 2, ZCU_ARITH_MAX = 3, ZCU_ARITH_NEG = 4, ZCU_ARITH_ABS = 5, ZCU_ARITH_SQRT = 6 };
+enum { ZCU_SCALAR_NONE = 0, ZCU_SCALAR_A = 1, ZCU_SCALAR_B = 2 };
+
+typedef struct zcu_graph_instr {
+    int32_t op;             /* ZCU_GI_* */
+    int32_t sub;            /* BASIC: ZCU_BASIC_*   ARITH: ZCU_ARITH_*   CALL: ZCU_MOD_* */
+    zcu_graph_ref out;      /* TEMP or OUTPUT */
+    zcu_graph_ref in[3];    /* BASIC / ARITH: a, b.  CALL: the buffer arguments of zcu_paint_<module> in its order (SineOsc: freq,
+                               phase; Filter: input, cutoff, res; ...); NONE = the scalar of the params row is used */
+    float scalar;           /* BASIC: the scalar of the *_SCALAR forms and SET.  ARITH: the float operand */
+    int32_t scalar_side;    /* ARITH: ZCU_SCALAR_NONE buffer op buffer, ZCU_SCALAR_A float op buffer (b = in[1]), ZCU_SCALAR_B buffer op float */
+    uint32_t field;         /* CALL: which field (a module instance: bank + params rows) of the graph */
+    uint32_t span_table;    /* which of the span tables given to zcu_graph_paint drives this instruction */
+} zcu_graph_instr;
+
+enum { ZCU_GRAPH_OUT_BUFFERS = 0, ZCU_GRAPH_OUT_MIX = 1 };
+typedef struct zcu_graph_config {
+    uint32_t voices;
+    uint32_t num_temps, num_outputs, num_inputs; /* outputs, inputs <= 4 */
+    uint32_t num_span_tables;                    /* <= 4 */
+    uint32_t num_fields;                         /* <= 12 */
+    int32_t output_mode;   /* BUFFERS: outputs are [frames][voices] buffers, accumulated (the module contract).  MIX: output 0 of
+                              every voice starts each sample at 0 and is summed x gains into a [frames][channels] mix */
+    uint32_t channels;     /* MIX: 1 or 2 */
+} zcu_graph_config;
+
+/* field_kinds[num_fields]: ZCU_MOD_* of every field.  Generates the kernel source, compiles and loads it. */
+int zcu_graph_create(zcu_ctx*, const zcu_graph_config* cfg, const zcu_graph_instr* instrs, uint32_t num_instrs, const int32_t* field_kinds,
+                     zcu_graph** out);
+void zcu_graph_free(zcu_graph*);
+/* the generated CUDA source of a graph (owned by the graph) */
+const char* zcu_graph_source(const zcu_graph*);
+/* Host-only (no device needed): generates the source of a graph and compiles it with NVRTC for sm_100a.  log (may be NULL)
+ * receives the compiler log or the generator's error; *cubin_bytes the size of the machine code.  Used by the CPU tests. */
+int zcu_graph_compile_check(const zcu_graph_config* cfg, const zcu_graph_instr* instrs, uint32_t num_instrs, const int32_t* field_kinds,
+                            char* log, size_t log_len, size_t* cubin_bytes);
+/* a field's state, params rows (`zcu_<module>_params`, row_bytes = its sizeof; kept on the device until set again) and
+ * module-specific tables.  Stateless modules take bank = NULL. */
+int zcu_graph_set_field(zcu_ctx*, zcu_graph*, uint32_t field, zcu_bank* bank, const void* params_host, size_t row_bytes, uint32_t nparams);
+int zcu_graph_set_curve_nodes(zcu_ctx*, zcu_graph*, uint32_t field, const zcu_curve_node* nodes_host, uint32_t nnodes);
+int zcu_graph_set_sample(zcu_ctx*, zcu_graph*, uint32_t field, const zcu_sample* sample);
+int zcu_graph_set_gains(zcu_ctx*, zcu_graph*, const float* gains_host); /* MIX: [voices][channels] */
+/* One launch paints the block: tables[num_span_tables] (all voices x frames of the buffers), outputs[num_outputs]
+ * (MIX: outputs[0] is the [frames][channels] mix, accumulated), inputs[num_inputs]. */
+int zcu_graph_paint(zcu_ctx*, zcu_graph*, const zcu_spans* const* tables, zcu_buf* const* outputs, const zcu_buf* const* inputs);
+
 /* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
 /* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */
 int zcu_nccl_unique_id(uint8_t id_out[128]);

@@ -1,0 +1,183 @@
+"""Fused module graphs (zcu_graph_*): the instrument bodies of BASELINE.json configs[2..4] as ONE generated
+kernel each, against (a) the per-module drop-in path on the same banks, bit for bit: outputs and every module's carried
+state, block after block; (b) the oracle's per-voice restatement (oracle/bank_oracle.hpp) at the bars of
+tests/test_gpu_banks.py; (c) MIX output mode against the voice sum of (a).  Reference for the instruction list:
+src/zangscript/codegen.zig:60-121, runtime.zig:445-740; for the bodies: examples/modules.zig, example_sampler.zig:94-118,
+example_laser.zig:77-115, example_detuned.zig:61-99."""
+import numpy as np
+import pytest
+
+import oracle
+from cases import TRANSCENDENTAL_TOL
+from helpers import assert_bit_exact, assert_close
+from zang_b200 import _lib as L
+from zang_b200 import banks, engine as E, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _states(bank):
+    out = {}
+    for name in ("noise", "curve", "filter", "env", "sampler", "decimator", "porta", "trisaw", "modulator", "carrier"):
+        m = getattr(bank, name, None)
+        if m is not None and m.bank is not None:
+            out[name] = m.bank.get_state()
+    return out
+
+
+def _render(ctx, bank, total, block, ntemps, fused, extra=None):
+    V = bank.voices
+    got = np.zeros((total, V), dtype=np.float32)
+    for first in range(0, total, block):
+        n = min(block, total - first)
+        out = ctx.buf(n, V)
+        ins = [ctx.buf(n, V, np.ascontiguousarray(a[first:first + n])) for a in (extra or ())]
+        if fused:
+            bank.paint_block_fused(first, n, out, *ins)
+            temps = []
+        else:
+            temps = [ctx.buf(n, V) for _ in range(ntemps)]
+            bank.paint_block(first, n, out, temps, *ins)
+        got[first:first + n] = out.download()
+        for b in [out] + temps + ins:
+            b.free()
+    return got
+
+
+def _same_states(a, b, what):
+    assert a.keys() == b.keys()
+    for k in a:
+        assert a[k].tobytes() == b[k].tobytes(), f"{what}: carried state of {k} differs between the fused and the per-module path"
+
+
+@pytest.mark.parametrize("jobs,job_frames,block", [(70, 6 * 1024, 2 * 1024), (33, 24576, 8 * 1024)])
+def test_sfx_graph(ctx, jobs, job_frames, block):
+    sr = 48000.0
+    wl = synth.sfx_bank(jobs, job_frames, seed=5)
+    _, want, _ = oracle.render_bank(oracle.BANK_SFX, wl, job_frames, sr, first_seed=9)
+    ref = banks.SfxBank(ctx, wl, sr, job_frames, first_seed=9)
+    unfused = _render(ctx, ref, job_frames, block, 3, fused=False)
+    bank = banks.SfxBank(ctx, wl, sr, job_frames, first_seed=9)
+    g = bank.build_graph()
+    assert "NoiseMod m0" in g.source and "FilterMod<true, false>" in g.source
+    l0 = ctx.launch_count
+    got = _render(ctx, bank, job_frames, block, 3, fused=True)
+    assert ctx.launch_count - l0 == -(-job_frames // block), "one kernel launch per block"
+    assert np.abs(want).max() > 0.05
+    assert_bit_exact(got, unfused, "sfx graph vs per-module path")
+    assert_bit_exact(got, want, "sfx graph vs oracle")
+    _same_states(_states(bank), _states(ref), "sfx")
+
+
+@pytest.mark.parametrize("voices,total,block", [(40, 7 * 1024 + 100, 3 * 1024), (33, 4 * 1024, 4 * 1024)])
+def test_sampler_graph(ctx, voices, total, block):
+    sr = 44100.0
+    wl = synth.sampler_bank(voices, total, sr, seed=11, mean_gap=0.03)
+    pcm = synth.pcm_loop(frames=3000, seed=3)
+    _, want, _ = oracle.render_bank(oracle.BANK_SAMPLER, wl, total, sr, pcm=pcm, pcm_meta=(1, 44100, L.FMT_SIGNED16_LSB))
+    smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
+    ref = banks.SamplerVoiceBank(ctx, wl, smp, sr, total)
+    unfused = _render(ctx, ref, total, block, 2, fused=False)
+    bank = banks.SamplerVoiceBank(ctx, wl, smp, sr, total)
+    bank.build_graph()
+    got = _render(ctx, bank, total, block, 2, fused=True)
+    assert np.abs(want).max() > 0.2
+    assert_bit_exact(got, unfused, "sampler graph vs per-module path")
+    assert_close(got, want, TRANSCENDENTAL_TOL, "sampler graph vs oracle (atanf per sample)")
+    _same_states(_states(bank), _states(ref), "sampler")
+
+
+def test_fm_graph(ctx):
+    sr, voices, total, block = 48000.0, 36, 9 * 1024 + 50, 4 * 1024
+    wl = synth.fm_bank(voices, total, sr, seed=21, mean_note=0.04)
+    detune, index = synth.fm_mod_inputs(voices, total)
+    _, want, _ = oracle.render_bank(oracle.BANK_FM, wl, total, sr, in0=detune, in1=index)
+    ref = banks.FmDetunedBank(ctx, wl, sr, total)
+    unfused = _render(ctx, ref, total, block, 6, fused=False, extra=(detune, index))
+    bank = banks.FmDetunedBank(ctx, wl, sr, total)
+    g = bank.build_graph()
+    assert "SineMod<true, true>" in g.source and "TriSawMod<true>" in g.source
+    got = _render(ctx, bank, total, block, 6, fused=True, extra=(detune, index))
+    assert np.abs(want).max() > 0.2
+    assert_bit_exact(got, unfused, "fm graph vs per-module path")
+    assert_close(got, want, 4e-5, "fm graph vs oracle (bar of tests/test_gpu_banks.py::test_fm_bank)")
+    _same_states(_states(bank), _states(ref), "fm")
+
+
+def test_graph_mix_mode_equals_the_voice_sum(ctx):
+    """MIX output: output 0 of every job x pan gains into a stereo mix, against the per-module path + zcu_mix_ordered-style
+    host sum (tolerance 1e-5 x sum|gain|: the voice summation order differs)."""
+    sr, jobs, frames = 48000.0, 200, 5 * 1024 + 17
+    wl = synth.sfx_bank(jobs, frames, seed=8)
+    ref = banks.SfxBank(ctx, wl, sr, frames, first_seed=3)
+    voices_out = _render(ctx, ref, frames, frames, 3, fused=False)
+    want = voices_out.astype(np.float64) @ wl["gains"].astype(np.float64)
+    bank = banks.SfxBank(ctx, wl, sr, frames, first_seed=3)
+    bank.build_graph(output_mode=L.GRAPH_OUT_MIX, channels=2, gains=wl["gains"])
+    mix = ctx.buf(frames, 2)
+    ctx.zero(None, mix)
+    bank.paint_block_fused(0, frames, mix)
+    got = mix.download()
+    tol = 1e-5 * float(np.abs(wl["gains"]).sum(axis=0).max())
+    assert float(np.abs(want).max()) > 0.05
+    assert float(np.abs(got - want).max()) <= tol, float(np.abs(got - want).max())
+    _same_states(_states(bank), _states(ref), "sfx mix")
+    # accumulates like every zang paint: a second block adds to what is there
+    bank2 = banks.SfxBank(ctx, wl, sr, frames, first_seed=3)
+    bank2.build_graph(output_mode=L.GRAPH_OUT_MIX, channels=2, gains=wl["gains"])
+    bank2.paint_block_fused(0, frames, mix)
+    assert float(np.abs(mix.download() - 2 * want).max()) <= 2 * tol
+
+
+def test_graph_arith_and_span_gaps(ctx):
+    """The script runtime's overwriting arithmetic (runtime.zig:528-700) and basics over spans with gaps: frames outside the
+    spans keep the output's previous contents; inside, out = max(|a - 0.25|, b / 2) + 0.5 built from five instructions."""
+    V, frames = 70, 3000
+    rng = np.random.default_rng(4)
+    a = rng.standard_normal((frames, V)).astype(np.float32)
+    bb = rng.standard_normal((frames, V)).astype(np.float32)
+    off, spans = [0], []
+    for v in range(V):
+        pos = int(rng.integers(0, 50))
+        while pos < frames - 10:
+            ln = int(rng.integers(1, 400))
+            end = min(frames, pos + ln, (pos // 1024 + 1) * 1024)
+            spans.append((pos, end, 0, 0))
+            pos = end + int(rng.integers(0, 3)) * int(rng.integers(0, 200))
+        off.append(len(spans))
+    spans = np.array(spans, dtype=L.span_dtype)
+    off = np.array(off, dtype=np.uint32)
+    b = E.GraphBuilder()
+    T, OUT, IN = E.T, E.OUT, E.IN
+    b.arith(L.ARITH_SUB, T(0), IN(0), 0.25)
+    b.arith(L.ARITH_ABS, T(0), T(0))
+    b.arith(L.ARITH_DIV, T(1), IN(1), 2.0)
+    b.arith(L.ARITH_MAX, T(0), T(0), T(1))
+    b.addScalar(OUT(0), T(0), 0.5)
+    cfg = E.graph_config(V, b, 2, num_inputs=2)
+    g = E.Graph(ctx, cfg, b)
+    prior = rng.standard_normal((frames, V)).astype(np.float32)
+    out = ctx.buf(frames, V, prior)
+    sp = ctx.spans(V, frames, off, spans)
+    g.paint([sp], [out], [ctx.buf(frames, V, a), ctx.buf(frames, V, bb)])
+    got = out.download()
+    want = prior.copy()
+    for v in range(V):
+        for k in range(off[v], off[v + 1]):
+            s, e = int(spans[k]["start"]), int(spans[k]["end"])
+            t0 = np.abs(a[s:e, v] - np.float32(0.25))
+            t1 = bb[s:e, v] / np.float32(2.0)
+            m = np.where(t0 > t1, t0, t1)
+            want[s:e, v] = want[s:e, v] + (m + np.float32(0.5))
+    assert_bit_exact(got, want, "arith graph")
+
+
+def test_graph_rejects_bad_lists(ctx):
+    b = E.GraphBuilder()
+    b.call(L.MOD_FILTER, E.T(0))  # no input buffer
+    with pytest.raises(E.ZangCuError):
+        E.Graph(ctx, E.graph_config(8, b, 1), b)
+    b = E.GraphBuilder()
+    b.zero(E.T(3))  # temp out of range
+    with pytest.raises(E.ZangCuError):
+        E.Graph(ctx, E.graph_config(8, b, 1), b)

@@ -127,6 +127,15 @@ PROTOTYPES = {
     "zcu_render_aux_kernel_ms": (_I, [_P, _P, _P, _P]),
     "zcu_render_set_segments": (_I, [_P, _U]),
     "zcu_render_segment_info": (_I, [_P, _P, _P, _P, _P, _P]),
+    "zcu_graph_create": (_I, [_P, _P, _P, _U, _P, _P]),
+    "zcu_graph_free": (None, [_P]),
+    "zcu_graph_source": (C.c_char_p, [_P]),
+    "zcu_graph_compile_check": (_I, [_P, _P, _U, _P, _P, _S, _P]),
+    "zcu_graph_set_field": (_I, [_P, _P, _U, _P, _P, _S, _U]),
+    "zcu_graph_set_curve_nodes": (_I, [_P, _P, _U, _P, _U]),
+    "zcu_graph_set_sample": (_I, [_P, _P, _U, _P]),
+    "zcu_graph_set_gains": (_I, [_P, _P, _P]),
+    "zcu_graph_paint": (_I, [_P, _P, _P, _P, _P]),
     "zcu_nccl_unique_id": (_I, [_P]),
     "zcu_nccl_init": (_I, [_P, _I, _I, _P]),
     "zcu_nccl_reduce_mix": (_I, [_P, _P, _I]),

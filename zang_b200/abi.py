@@ -25,6 +25,14 @@ INSTR_NICE = 0
 RENDER_EXACT, RENDER_SCAN, RENDER_SEGMENTS = 0, 1, 2
 PAINT_EXACT, PAINT_TOLERANCE = 0, 1
 MAX_POLYPHONY = 32
+# fused module graphs
+GREF_NONE, GREF_TEMP, GREF_OUTPUT, GREF_INPUT = range(4)
+GI_BASIC, GI_ARITH, GI_CALL = range(3)
+(BASIC_ZERO, BASIC_SET, BASIC_COPY, BASIC_ADD, BASIC_ADD_INTO, BASIC_ADD_SCALAR, BASIC_ADD_SCALAR_INTO, BASIC_MULTIPLY,
+ BASIC_MULTIPLY_WITH, BASIC_MULTIPLY_SCALAR, BASIC_MULTIPLY_WITH_SCALAR) = range(11)
+ARITH_SUB, ARITH_DIV, ARITH_MIN, ARITH_MAX, ARITH_NEG, ARITH_ABS, ARITH_SQRT = range(7)
+SCALAR_NONE, SCALAR_A, SCALAR_B = range(3)
+GRAPH_OUT_BUFFERS, GRAPH_OUT_MIX = 0, 1
 
 # ---- POD dtypes -------------------------------------------------------------------------------------
 span_dtype = np.dtype([("start", "<u4"), ("end", "<u4"), ("flags", "<u4"), ("param", "<u4")])
@@ -115,6 +123,20 @@ class RenderConfig(C.Structure):
                 ("mode", C.c_int32)]
 
 
+
+
+class GraphRef(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("index", C.c_uint32)]
+
+
+class GraphInstr(C.Structure):
+    _fields_ = [("op", C.c_int32), ("sub", C.c_int32), ("out", GraphRef), ("in_", GraphRef * 3), ("scalar", C.c_float),
+                ("scalar_side", C.c_int32), ("field", C.c_uint32), ("span_table", C.c_uint32)]
+
+
+class GraphConfig(C.Structure):
+    _fields_ = [("voices", C.c_uint32), ("num_temps", C.c_uint32), ("num_outputs", C.c_uint32), ("num_inputs", C.c_uint32),
+                ("num_span_tables", C.c_uint32), ("num_fields", C.c_uint32), ("output_mode", C.c_int32), ("channels", C.c_uint32)]
 
 
 def ptr(a):

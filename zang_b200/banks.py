@@ -83,6 +83,42 @@ class SamplerVoiceBank:
                 s.free()
 
 
+    # ---- the same body as ONE fused kernel (zcu_graph_*): temps in registers ----
+    @staticmethod
+    def graph_list(voices, output_mode=L.GRAPH_OUT_BUFFERS, channels=2):
+        """(builder, config, field indices) of the body above; host only."""
+        b = E.GraphBuilder()
+        T, OUT = E.T, E.OUT
+        TRIG, VOICE, ROW0 = 0, 1, 2  # span tables: the Trigger's spans, whole buffers with row = voice, whole buffers with row 0
+        b.zero(T(0), table=VOICE)
+        f_smp = b.call(L.MOD_SAMPLER, T(0), table=TRIG)
+        b.multiplyWithScalar(T(0), 2.5, table=VOICE)
+        b.zero(T(1), table=VOICE)
+        f_dec = b.call(L.MOD_DECIMATOR, T(1), (T(0),), table=VOICE)
+        f_dist = b.call(L.MOD_DISTORTION, OUT(0), (T(1),), table=ROW0)
+        cfg = E.graph_config(voices, b, 2, num_span_tables=3, output_mode=output_mode, channels=channels)
+        return b, cfg, (f_smp, f_dec, f_dist)
+
+    def build_graph(self, output_mode=L.GRAPH_OUT_BUFFERS, channels=2, gains=None):
+        b, cfg, (f_smp, f_dec, f_dist) = self.graph_list(self.voices, output_mode, channels)
+        g = E.Graph(self.ctx, cfg, b)
+        g.set_field(f_smp, self.sampler.bank, self.sampler_rows)
+        g.set_sample(f_smp, self.sample)
+        g.set_field(f_dec, self.decimator.bank, self.dec_rows)
+        g.set_field(f_dist, None, self.dist_rows)
+        if gains is not None:
+            g.set_gains(gains)
+        self.graph = g
+        return g
+
+    def paint_block_fused(self, first_frame, num_frames, out, prepared=None):
+        tabs = prepared or self.prepare_block(first_frame, num_frames)
+        self.graph.paint(tabs, [out])
+        if prepared is None:
+            for s in tabs:
+                s.free()
+
+
 class SfxBank:
     """paint body per job (per Trigger span):
         zero(t0); noise.paint(span, {t0}, .{ .color = .white })
@@ -143,6 +179,45 @@ class SfxBank:
         ctx.multiply(sp, out, t2, t0)
         if prepared is None:
             sp.free()
+
+
+    # ---- the same body as ONE fused kernel (zcu_graph_*): temps in registers ----
+    @staticmethod
+    def graph_list(voices, output_mode=L.GRAPH_OUT_BUFFERS, channels=2):
+        """(builder, config, field indices) of the body above; host only."""
+        b = E.GraphBuilder()
+        T, OUT = E.T, E.OUT
+        b.zero(T(0))
+        f_noise = b.call(L.MOD_NOISE, T(0))
+        b.zero(T(1))
+        f_curve = b.call(L.MOD_CURVE, T(1))
+        b.zero(T(2))
+        f_filter = b.call(L.MOD_FILTER, T(2), (T(0), T(1)))  # input, cutoff buffer; res from the params row
+        b.zero(T(0))
+        f_env = b.call(L.MOD_ENVELOPE, T(0))
+        b.multiply(OUT(0), T(2), T(0))
+        cfg = E.graph_config(voices, b, 3, output_mode=output_mode, channels=channels)
+        return b, cfg, (f_noise, f_curve, f_filter, f_env)
+
+    def build_graph(self, output_mode=L.GRAPH_OUT_BUFFERS, channels=2, gains=None):
+        b, cfg, (f_noise, f_curve, f_filter, f_env) = self.graph_list(self.voices, output_mode, channels)
+        g = E.Graph(self.ctx, cfg, b)
+        g.set_field(f_noise, self.noise.bank, self.noise_rows)
+        g.set_field(f_curve, self.curve.bank, self.curve_rows)
+        g.set_curve_nodes(f_curve, self.nodes)
+        g.set_field(f_filter, self.filter.bank, self.filter_rows)
+        g.set_field(f_env, self.env.bank, self.env_rows)
+        if gains is not None:
+            g.set_gains(gains)
+        self.graph = g
+        return g
+
+    def paint_block_fused(self, first_frame, num_frames, out, prepared=None):
+        tabs = prepared or self.prepare_block(first_frame, num_frames)
+        self.graph.paint(tabs, [out])
+        if prepared is None:
+            for s in tabs:
+                s.free()
 
 
 class FmDetunedBank:
@@ -240,4 +315,49 @@ class FmDetunedBank:
         ctx.multiply(sp, out, t4, t5)
         if prepared is None:
             for s in (sp_porta, sp_env, sp):
+                s.free()
+
+    # ---- the same body as ONE fused kernel (zcu_graph_*): temps in registers ----
+    @staticmethod
+    def graph_list(voices, output_mode=L.GRAPH_OUT_BUFFERS, channels=2):
+        """(builder, config, field indices) of the body above; host only."""
+        b = E.GraphBuilder()
+        T, OUT, IN = E.T, E.OUT, E.IN
+        PORTA, ENV, PLAIN = 0, 1, 2  # the three span tables of prepare_block (same spans; rows / flags differ)
+        b.zero(T(0), table=PLAIN)
+        f_porta = b.call(L.MOD_PORTAMENTO, T(0), table=PORTA)
+        b.zero(T(1), table=PLAIN)
+        b.multiply(T(1), T(0), IN(0), table=PLAIN)
+        b.zero(T(2), table=PLAIN)
+        f_trisaw = b.call(L.MOD_TRISAW_OSC, T(2), (T(1),), table=PLAIN)
+        b.zero(T(3), table=PLAIN)
+        f_mod = b.call(L.MOD_SINE_OSC, T(3), (T(0),), table=PLAIN)
+        b.multiplyWith(T(3), IN(1), table=PLAIN)
+        b.zero(T(4), table=PLAIN)
+        f_car = b.call(L.MOD_SINE_OSC, T(4), (T(0), T(3)), table=PLAIN)
+        b.zero(T(5), table=PLAIN)
+        f_env = b.call(L.MOD_ENVELOPE, T(5), table=ENV)
+        b.multiply(OUT(0), T(2), T(5), table=PLAIN)
+        b.multiply(OUT(0), T(4), T(5), table=PLAIN)
+        cfg = E.graph_config(voices, b, 6, num_inputs=2, num_span_tables=3, output_mode=output_mode, channels=channels)
+        return b, cfg, (f_porta, f_trisaw, f_mod, f_car, f_env)
+
+    def build_graph(self, output_mode=L.GRAPH_OUT_BUFFERS, channels=2, gains=None):
+        b, cfg, (f_porta, f_trisaw, f_mod, f_car, f_env) = self.graph_list(self.voices, output_mode, channels)
+        g = E.Graph(self.ctx, cfg, b)
+        g.set_field(f_porta, self.porta.bank, self.porta_rows)
+        g.set_field(f_trisaw, self.trisaw.bank, self.trisaw_rows)
+        g.set_field(f_mod, self.modulator.bank, self.sine_rows)
+        g.set_field(f_car, self.carrier.bank, self.sine_rows)
+        g.set_field(f_env, self.env.bank, self.env_rows)
+        if gains is not None:
+            g.set_gains(gains)
+        self.graph = g
+        return g
+
+    def paint_block_fused(self, first_frame, num_frames, out, detune_in, index_in, prepared=None):
+        tabs = prepared or self.prepare_block(first_frame, num_frames)
+        self.graph.paint(tabs, [out], [detune_in, index_in])
+        if prepared is None:
+            for s in tabs:
                 s.free()

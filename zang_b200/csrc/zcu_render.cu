@@ -99,6 +99,17 @@ __global__ void __launch_bounds__(256) k_partial_reduce(const float* __restrict_
     mix[i] += s;
 }
 
+}  // namespace
+
+// mix[i] += sum over warps of partial[w][i] (fixed order); also used by the fused module graphs (zcu_graph.cu)
+void zcu_launch_partial_reduce(zcu_ctx* ctx, const float* partial, float* mix, uint32_t nwarps, size_t n) {
+    if (n == 0) return;
+    k_partial_reduce<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(partial, mix, nwarps, n);
+    ctx->launches++;
+}
+
+namespace {
+
 __global__ void k_state_reset(NiceVoiceState* st, const uint32_t* event_off, uint32_t V) {
     const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= V) return;

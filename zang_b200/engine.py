@@ -687,3 +687,135 @@ class Render:
         if self._h:
             lib.zcu_render_free(self._h)
             self._h = None
+
+
+# ---- fused module graphs (zcu_graph_*) -------------------------------------------------------------------------------
+def T(i):
+    """temp i of a graph"""
+    return (L.GREF_TEMP, int(i))
+
+
+def OUT(i=0):
+    """output i of a graph"""
+    return (L.GREF_OUTPUT, int(i))
+
+
+def IN(i):
+    """external input buffer i of a graph"""
+    return (L.GREF_INPUT, int(i))
+
+
+class GraphBuilder:
+    """Instruction list of a fused graph: the body of an instrument's paint() (examples/modules.zig) or a script module's
+    instructions (src/zangscript/codegen.zig:108-121), one method per instruction."""
+
+    def __init__(self):
+        self.instrs = []
+        self.field_kinds = []
+
+    def _add(self, op, sub, out, ins=(), scalar=0.0, scalar_side=L.SCALAR_NONE, field=0, table=0):
+        x = L.GraphInstr()
+        x.op, x.sub = op, sub
+        x.out = L.GraphRef(*out)
+        for q in range(3):
+            r = ins[q] if q < len(ins) and ins[q] is not None else (L.GREF_NONE, 0)
+            x.in_[q] = L.GraphRef(*r)
+        x.scalar, x.scalar_side, x.field, x.span_table = float(scalar), scalar_side, field, table
+        self.instrs.append(x)
+        return self
+
+    # zang basics (basics.zig:12-78)
+    def zero(self, d, table=0): return self._add(L.GI_BASIC, L.BASIC_ZERO, d, table=table)
+    def set(self, d, s, table=0): return self._add(L.GI_BASIC, L.BASIC_SET, d, scalar=s, table=table)
+    def copy(self, d, a, table=0): return self._add(L.GI_BASIC, L.BASIC_COPY, d, (a,), table=table)
+    def add(self, d, a, b, table=0): return self._add(L.GI_BASIC, L.BASIC_ADD, d, (a, b), table=table)
+    def addInto(self, d, a, table=0): return self._add(L.GI_BASIC, L.BASIC_ADD_INTO, d, (a,), table=table)
+    def addScalar(self, d, a, s, table=0): return self._add(L.GI_BASIC, L.BASIC_ADD_SCALAR, d, (a,), scalar=s, table=table)
+    def addScalarInto(self, d, s, table=0): return self._add(L.GI_BASIC, L.BASIC_ADD_SCALAR_INTO, d, scalar=s, table=table)
+    def multiply(self, d, a, b, table=0): return self._add(L.GI_BASIC, L.BASIC_MULTIPLY, d, (a, b), table=table)
+    def multiplyWith(self, d, a, table=0): return self._add(L.GI_BASIC, L.BASIC_MULTIPLY_WITH, d, (a,), table=table)
+    def multiplyScalar(self, d, a, s, table=0): return self._add(L.GI_BASIC, L.BASIC_MULTIPLY_SCALAR, d, (a,), scalar=s, table=table)
+    def multiplyWithScalar(self, d, s, table=0): return self._add(L.GI_BASIC, L.BASIC_MULTIPLY_WITH_SCALAR, d, scalar=s, table=table)
+
+    # the script runtime's overwriting arithmetic (runtime.zig:528-700); a or b may be a Python float
+    def arith(self, sub, d, a, b=None, table=0):
+        if isinstance(a, (int, float)):
+            return self._add(L.GI_ARITH, sub, d, (None, b), scalar=a, scalar_side=L.SCALAR_A, table=table)
+        if isinstance(b, (int, float)):
+            return self._add(L.GI_ARITH, sub, d, (a, None), scalar=b, scalar_side=L.SCALAR_B, table=table)
+        return self._add(L.GI_ARITH, sub, d, (a, b), table=table)
+
+    def call(self, kind, d, ins=(), table=0):
+        """module.paint(span, {d}, ...): accumulates into d.  Returns the new field's index."""
+        field = len(self.field_kinds)
+        self.field_kinds.append(int(kind))
+        self._add(L.GI_CALL, int(kind), d, ins, field=field, table=table)
+        return field
+
+    def arrays(self):
+        arr = (L.GraphInstr * len(self.instrs))(*self.instrs)
+        kinds = (C.c_int32 * max(1, len(self.field_kinds)))(*self.field_kinds)
+        return arr, kinds
+
+
+def graph_config(voices, builder, num_temps, num_outputs=1, num_inputs=0, num_span_tables=1, output_mode=L.GRAPH_OUT_BUFFERS, channels=2):
+    return L.GraphConfig(int(voices), int(num_temps), int(num_outputs), int(num_inputs), int(num_span_tables), len(builder.field_kinds),
+                         int(output_mode), int(channels))
+
+
+def graph_compile_check(cfg, builder):
+    """Host-only: generate + NVRTC-compile for sm_100a.  Returns (rc, log, cubin_bytes)."""
+    arr, kinds = builder.arrays()
+    log = C.create_string_buffer(1 << 16)
+    n = C.c_size_t()
+    rc = lib.zcu_graph_compile_check(C.byref(cfg), arr, len(builder.instrs), kinds, log, len(log), C.byref(n))
+    return rc, log.value.decode(errors="replace"), n.value
+
+
+class Graph:
+    """One fused kernel for a whole instruction list (zcu_graph_create / zcu_graph_paint)."""
+
+    def __init__(self, ctx, cfg, builder):
+        self.ctx, self.cfg = ctx, cfg
+        arr, kinds = builder.arrays()
+        h = C.c_void_p()
+        _check(ctx, lib.zcu_graph_create(ctx._h, C.byref(cfg), arr, len(builder.instrs), kinds, C.byref(h)))
+        self._h = h
+        self.field_kinds = list(builder.field_kinds)
+        self._keep = []
+
+    @property
+    def source(self):
+        return lib.zcu_graph_source(self._h).decode()
+
+    def set_field(self, field, bank, params):
+        kind = self.field_kinds[field]
+        if params is None:
+            _check(self.ctx, lib.zcu_graph_set_field(self.ctx._h, self._h, field, _h(bank), None, 0, 0))
+            return
+        p = _params(kind, params)
+        _check(self.ctx, lib.zcu_graph_set_field(self.ctx._h, self._h, field, _h(bank), ptr(p), p.dtype.itemsize, p.size))
+
+    def set_curve_nodes(self, field, nodes):
+        n = np.ascontiguousarray(nodes, dtype=L.curve_node_dtype).reshape(-1)
+        _check(self.ctx, lib.zcu_graph_set_curve_nodes(self.ctx._h, self._h, field, ptr(n), n.size))
+
+    def set_sample(self, field, sample):
+        self._keep.append(sample)
+        _check(self.ctx, lib.zcu_graph_set_sample(self.ctx._h, self._h, field, sample._h))
+
+    def set_gains(self, gains):
+        g = np.ascontiguousarray(gains, dtype=np.float32)
+        assert g.shape == (self.cfg.voices, self.cfg.channels)
+        _check(self.ctx, lib.zcu_graph_set_gains(self.ctx._h, self._h, ptr(g)))
+
+    def paint(self, tables, outputs, inputs=()):
+        tabs = (C.c_void_p * len(tables))(*[t._h for t in tables])
+        outs = (C.c_void_p * len(outputs))(*[o._h for o in outputs])
+        ins = (C.c_void_p * max(1, len(inputs)))(*[i._h for i in inputs])
+        _check(self.ctx, lib.zcu_graph_paint(self.ctx._h, self._h, tabs, outs, ins if len(inputs) else None))
+
+    def free(self):
+        if self._h:
+            lib.zcu_graph_free(self._h)
+            self._h = None
