@@ -52,6 +52,37 @@ def run(ctx, name, bank, frames, ntemps, bytes_per_vs, peak, ins=(), reps=3):
     return res
 
 
+def run_fused(ctx, name, bank, frames, bytes_per_vs, peak, ins=(), reps=3, gains=None):
+    """The same bank body as ONE fused graph kernel (zcu_graph_*): per-voice output buffer (BUFFERS) and stereo mix (MIX)."""
+    V = bank.voices
+    res = {}
+    prepared = bank.prepare_block(0, frames)
+    for mode, mname in ((L.GRAPH_OUT_BUFFERS, "fused_buffers"), (L.GRAPH_OUT_MIX, "fused_mix")):
+        if mode == L.GRAPH_OUT_MIX and gains is None:
+            continue
+        t0 = time.perf_counter()
+        bank.build_graph(output_mode=mode, channels=2, gains=gains if mode == L.GRAPH_OUT_MIX else None)
+        t_build = time.perf_counter() - t0
+        out = ctx.buf(frames, V if mode == L.GRAPH_OUT_BUFFERS else 2)
+        best = 1e30
+        for rep in range(reps + 1):
+            ctx.zero(None, out)
+            ctx.timer_start()
+            bank.paint_block_fused(0, frames, out, *ins, prepared=prepared)
+            ms = ctx.timer_stop_ms()
+            if rep > 0:
+                best = min(best, ms)
+        vs = V * frames / (best * 1e-3)
+        res[mname] = dict(ms=best, voice_samples_per_s=vs, graph_build_s=t_build, equivalent_algorithmic_gbs=vs * bytes_per_vs / 1e9,
+                          equivalent_frac_of_peak=vs * bytes_per_vs / 1e9 / peak)
+        print(f"{name:34s} {mname:14s} {best:9.3f} ms  {vs:10.3e} vs/s  (graph build {t_build:5.2f} s; un-fused-equivalent {vs * bytes_per_vs / 1e9:8.1f} GB/s)", flush=True)
+        out.free()
+        bank.graph.free()
+    for b in prepared:
+        b.free()
+    return res
+
+
 class NiceBankAdapter:
     """configs[1] through the un-fused NiceInstrumentBank (engine.py), for comparison with the fused render."""
 
@@ -102,20 +133,25 @@ def main():
         ins = (ctx.buf(frames, V, det), ctx.buf(frames, V, idx))
         del det, idx
         res.append(run(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 6, 140, peak, ins=ins))
+        res[-1].update(run_fused(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 140, peak, ins=ins,
+                                 gains=np.full((V, 2), 1.0 / V, dtype=np.float32)))
         for b in ins:
             b.free()
     # configs[3] sampler: 2048 voices, 64 mix buffers @44.1 kHz
     V, frames = int(2048 * sc), 64 * 1024
     if 3 in only:
         wl = synth.sampler_bank(V, frames, 44100.0)
-        pcm = synth.pcm_loop()
+        pcm, _ = synth.drumloop_pcm()
         smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
         res.append(run(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 2, 48, peak))
+        res[-1].update(run_fused(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 48, peak,
+                                 gains=np.full((V, 2), 1.0 / V, dtype=np.float32)))
     # configs[4] SFX batch: 65536 jobs x 24 mix buffers
     V, frames = int(65536 * sc), 24 * 1024
     if 4 in only:
         wl = synth.sfx_bank(V, frames)
         res.append(run(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 3, 100, peak))
+        res[-1].update(run_fused(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 100, peak, gains=wl["gains"]))
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(dict(peak_gbs=peak, paint_mode="exact" if args.exact else "tolerance", results=res), open(args.out, "w"), indent=1)
     ctx.close()

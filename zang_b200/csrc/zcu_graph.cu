@@ -160,6 +160,7 @@ struct FieldInfo {
     std::string type;  // device module type
     uint32_t table = 0;
     bool used = false;
+    bool has_run = false;  // the module offers run_limit / run_begin / sample_run / run_end (zcu_modules.cuh: HAS_RUN)
 };
 
 bool module_type(int kind, const zcu_graph_instr& in, std::string& type, std::string& err) {
@@ -262,6 +263,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             f.kind = x.sub;
             f.table = x.span_table;
             f.used = true;
+            f.has_run = x.sub == ZCU_MOD_ENVELOPE || x.sub == ZCU_MOD_PORTAMENTO || x.sub == ZCU_MOD_CURVE;
         } else if (x.op == ZCU_GI_BASIC) {
             if (x.sub < 0 || x.sub > 10) return fail(i, "unknown basic op");
             const bool na = x.sub == 2 || x.sub == 3 || x.sub == 4 || x.sub == 5 || x.sub == 7 || x.sub == 8 || x.sub == 9;
@@ -295,7 +297,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         return b;
     };
     // the per-sample body; live[k] = expression telling whether table k is live on this lane ("true" in the all-live copy)
-    auto body = [&](bool all_live, const char* ind) {
+    auto body = [&](bool all_live, const char* ind, const char* row) {
         std::string s;
         auto live = [&](uint32_t k) -> std::string {
             if (all_live) return "true";
@@ -310,7 +312,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                 if (mask >> k & 1u) e += (e.empty() ? "" : " || ") + live(k);
             return e.empty() ? "false" : e;
         };
-        if (!mix || c.num_inputs) appendf(s, "%sconst size_t idx = base + (size_t)r * g.V;\n", ind);
+        if (!mix || c.num_inputs) appendf(s, "%sconst size_t idx = base + (size_t)%s * g.V;\n", ind, row);
         for (uint32_t i = 0; i < c.num_inputs; i++)
             if (in_used[i]) appendf(s, "%sconst float x%u = valid ? __ldg(g.in[%u] + idx) : 0.0f;\n", ind, i, i);
         for (uint32_t o = 0; o < c.num_outputs; o++) {
@@ -325,7 +327,8 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             std::string stmt;
             if (x.op == ZCU_GI_CALL) {
                 char t[160];
-                snprintf(t, sizeof t, "m%u.sample(%s, %s, %s, %s);", x.field, d.c_str(), a.c_str(), b.c_str(), cc.c_str());
+                snprintf(t, sizeof t, "m%u.%s(%s, %s, %s, %s);", x.field, (all_live && fields[x.field].has_run) ? "sample_run" : "sample", d.c_str(),
+                         a.c_str(), b.c_str(), cc.c_str());
                 stmt = t;
             } else if (x.op == ZCU_GI_BASIC) {
                 switch (x.sub) {  // basics.zig:12-78, the expression forms of BasicMod (zcu_modules.cuh)
@@ -360,7 +363,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         }
         for (uint32_t o = 0; o < c.num_outputs; o++) {
             if (mix)
-                appendf(s, "%sO[j + r][lane] = o%u;\n", ind, o);
+                appendf(s, "%sO[j + %s][lane] = o%u;\n", ind, row, o);
             else
                 appendf(s, "%sif (%s) g.out[%u][idx] = o%u;\n", ind, any_live(out_tables[o]).c_str(), o, o);
         }
@@ -407,6 +410,18 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     src += "        uint32_t dist = c0.boundary() - f;\n";
     for (uint32_t k = 1; k < K; k++) appendf(src, "        dist = min(dist, c%u.boundary() - f);\n", k);
     if (mix) src += "        dist = min(dist, (uint32_t)kMixTileFrames - j);\n";
+    // modules with a run interface: no phase change of theirs inside a run (painter_safe_run's margin covers 256 samples);
+    // a module that cannot promise a single sample sends the whole warp through the general per-sample path for one frame
+    bool any_run = false;
+    for (uint32_t f = 0; f < c.num_fields; f++) any_run = any_run || fields[f].has_run;
+    src += "        bool careful = false;\n";
+    if (any_run) {
+        src += "        dist = min(dist, 256u);\n";
+        for (uint32_t f = 0; f < c.num_fields; f++)
+            if (fields[f].has_run)
+                appendf(src, "        if (c%u.active) {\n            const uint32_t s = m%u.run_limit();\n            careful = careful || s == 0u;\n"
+                             "            dist = min(dist, s == 0u ? 1u : s);\n        }\n", fields[f].table, f);
+    }
     src += "        const uint32_t run = min(g.frames - f, __reduce_min_sync(FULL, dist));\n";
     std::string all = "", any = "";
     for (uint32_t k = 0; k < K; k++) {
@@ -417,14 +432,37 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         any += (k ? std::string(" || ") : std::string("")) + b;
     }
     src += "        const size_t base = (size_t)f * g.V + v;\n";
-    appendf(src, "        if (__all_sync(FULL, %s)) {\n#pragma unroll 4\n            for (uint32_t r = 0; r < run; r++) {\n", all.c_str());
-    src += body(true, "                ");
+    // all tables live on every lane: batches of four samples; the rows of every external buffer 16 frames ahead are pulled
+    // into L1 first (banks too small to fill the chip run one warp per scheduler: nothing else would hide the HBM latency)
+    appendf(src, "        if (__all_sync(FULL, %s && !careful)) {\n", all.c_str());
+    for (uint32_t f = 0; f < c.num_fields; f++)
+        if (fields[f].has_run) appendf(src, "            m%u.run_begin();\n", f);
+    src += "            uint32_t r = 0;\n            for (; r + 4 <= run; r += 4) {\n";
+    {
+        std::string pf;
+        for (uint32_t i = 0; i < c.num_inputs; i++)
+            if (in_used[i]) appendf(pf, "                    prefetch_rows4(g.in[%u] + pidx, g.V);\n", i);
+        if (!mix)
+            for (uint32_t o = 0; o < c.num_outputs; o++) appendf(pf, "                    prefetch_rows4(g.out[%u] + pidx, g.V);\n", o);
+        if (!pf.empty()) {
+            src += "                if (valid && f + r + kGraphPrefetchRows + 4 <= g.frames) {\n";
+            src += "                    const size_t pidx = base + (size_t)(r + kGraphPrefetchRows) * g.V;\n";
+            src += pf;
+            src += "                }\n";
+        }
+    }
+    src += "#pragma unroll\n                for (uint32_t q = 0; q < 4; q++) {\n                    const uint32_t rr = r + q;\n";
+    src += body(true, "                    ", "rr");
+    src += "                }\n            }\n            for (; r < run; r++) {\n";
+    src += body(true, "                ", "r");
     src += "            }\n";
+    for (uint32_t f = 0; f < c.num_fields; f++)
+        if (fields[f].has_run) appendf(src, "            m%u.run_end();\n", f);
     if (mix)
         src += "        } else {\n            for (uint32_t r = 0; r < run; r++) {\n";
     else
         appendf(src, "        } else if (%s) {\n            for (uint32_t r = 0; r < run; r++) {\n", any.c_str());
-    src += body(false, "                ");
+    src += body(false, "                ", "r");
     src += "            }\n        }\n";
     src += "        f += run;\n";
     if (mix) {

@@ -36,6 +36,15 @@ struct GraphArgs {
     PaintArgs pa[kGraphMaxFields];
 };
 
+// rows of an external [frames][V] buffer this many frames ahead are pulled into L1 before they are needed
+constexpr uint32_t kGraphPrefetchRows = 16;
+__device__ __forceinline__ void prefetch_rows4(const float* p, size_t V) {
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p + V));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 2 * V));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 3 * V));
+}
+
 // cursor over one voice's spans of one table
 struct SpanCursor {
     uint32_t k, ke, s_start, s_end, s_flags, s_param;
