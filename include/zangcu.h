@@ -421,6 +421,27 @@ int64_t zcu_bank_spans(zcu_bank_trigger* state, uint32_t voices, const uint32_t*
                        uint32_t buffer_frames, uint32_t total_frames, uint32_t first_frame, uint32_t num_frames,
                        uint32_t* voice_off_out, zcu_span* spans_out, uint64_t max_spans);
 
+/* The same on the DEVICE: the note events are uploaded once, and every block's span table is built by
+ * the GPU (one thread per voice replays ImpulseQueue.push + the Trigger loop, trigger.zig:80-196, twice: count, scan,
+ * write), so no span table crosses PCIe and the host does no per-block event work.  Bit-identical to zcu_bank_spans. */
+typedef struct zcu_event_bank zcu_event_bank;
+int zcu_event_bank_create(zcu_ctx*, uint32_t voices, const uint32_t* event_off_host, const struct zcu_note_event* events_host,
+                          uint32_t buffer_frames, uint32_t total_frames, zcu_event_bank** out);
+void zcu_event_bank_free(zcu_event_bank*);
+int zcu_event_bank_reset(zcu_ctx*, zcu_event_bank*); /* zcu_bank_trigger_init */
+int zcu_event_bank_get_state(zcu_ctx*, const zcu_event_bank*, zcu_bank_trigger* state_host); /* checkpoint */
+int zcu_event_bank_set_state(zcu_ctx*, zcu_event_bank*, const zcu_bank_trigger* state_host);
+/* span table of the block [first_frame, first_frame + num_frames), asynchronous on the context's stream; the Trigger state
+ * advances.  The table is sized for the worst case; zcu_spans_download reads the exact count back. */
+int zcu_event_bank_spans(zcu_ctx*, zcu_event_bank*, uint32_t first_frame, uint32_t num_frames, zcu_spans** out);
+/* reads a device span table back (tests, checkpoints): *nspans_out = rows; rows are copied when they fit max_spans */
+int zcu_spans_download(zcu_ctx*, const zcu_spans*, uint32_t* voice_off_out, zcu_span* spans_out, uint64_t max_spans, uint64_t* nspans_out);
+/* Views of a Trigger table for an instrument that keeps the previous call's note_on (examples/example_portamento.zig:51
+ * `defer self.prev_note_on = params.note_on`), per voice in span order, carried across blocks inside the event bank:
+ *   porta: span.param = 2 * param + prev_note_on     env: span.flags = (!prev_note_on && note_on)     plain: span.param = 0 */
+int zcu_spans_prev_note_on_views(zcu_ctx*, zcu_event_bank*, const zcu_spans* src, zcu_spans** porta_out, zcu_spans** env_out,
+                                 zcu_spans** plain_out);
+
 /* ---- fused instrument banks (B200-first path for the benchmark configs) ----------------------- */
 /* A note event of one voice with an ABSOLUTE frame position in the whole render.  Voice v owns
  * events[event_off[v] .. event_off[v+1]), chronological.  The device replays Trigger semantics

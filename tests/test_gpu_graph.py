@@ -50,27 +50,31 @@ def _same_states(a, b, what):
         assert a[k].tobytes() == b[k].tobytes(), f"{what}: carried state of {k} differs between the fused and the per-module path"
 
 
-@pytest.mark.parametrize("jobs,job_frames,block", [(70, 6 * 1024, 2 * 1024), (33, 24576, 8 * 1024)])
-def test_sfx_graph(ctx, jobs, job_frames, block):
+@pytest.mark.parametrize("jobs,job_frames,block,device_spans", [(70, 6 * 1024, 2 * 1024, False), (33, 24576, 8 * 1024, False),
+                                                                (70, 6 * 1024, 2 * 1024, True)])
+def test_sfx_graph(ctx, jobs, job_frames, block, device_spans):
     sr = 48000.0
     wl = synth.sfx_bank(jobs, job_frames, seed=5)
     _, want, _ = oracle.render_bank(oracle.BANK_SFX, wl, job_frames, sr, first_seed=9)
     ref = banks.SfxBank(ctx, wl, sr, job_frames, first_seed=9)
     unfused = _render(ctx, ref, job_frames, block, 3, fused=False)
     bank = banks.SfxBank(ctx, wl, sr, job_frames, first_seed=9)
+    if device_spans:
+        bank.use_device_spans(wl)
     g = bank.build_graph()
     assert "NoiseMod m0" in g.source and "FilterMod<true, false>" in g.source
     l0 = ctx.launch_count
     got = _render(ctx, bank, job_frames, block, 3, fused=True)
-    assert ctx.launch_count - l0 == -(-job_frames // block), "one kernel launch per block"
+    assert ctx.launch_count - l0 == (-(-job_frames // block)) * (4 if device_spans else 1), "one kernel launch per block (+3 for the device span table)"
     assert np.abs(want).max() > 0.05
     assert_bit_exact(got, unfused, "sfx graph vs per-module path")
     assert_bit_exact(got, want, "sfx graph vs oracle")
     _same_states(_states(bank), _states(ref), "sfx")
 
 
-@pytest.mark.parametrize("voices,total,block", [(40, 7 * 1024 + 100, 3 * 1024), (33, 4 * 1024, 4 * 1024)])
-def test_sampler_graph(ctx, voices, total, block):
+@pytest.mark.parametrize("voices,total,block,device_spans", [(40, 7 * 1024 + 100, 3 * 1024, False), (33, 4 * 1024, 4 * 1024, False),
+                                                             (40, 7 * 1024 + 100, 3 * 1024, True)])
+def test_sampler_graph(ctx, voices, total, block, device_spans):
     sr = 44100.0
     wl = synth.sampler_bank(voices, total, sr, seed=11, mean_gap=0.03)
     pcm = synth.pcm_loop(frames=3000, seed=3)
@@ -79,6 +83,8 @@ def test_sampler_graph(ctx, voices, total, block):
     ref = banks.SamplerVoiceBank(ctx, wl, smp, sr, total)
     unfused = _render(ctx, ref, total, block, 2, fused=False)
     bank = banks.SamplerVoiceBank(ctx, wl, smp, sr, total)
+    if device_spans:
+        bank.use_device_spans(wl)
     bank.build_graph()
     got = _render(ctx, bank, total, block, 2, fused=True)
     assert np.abs(want).max() > 0.2
@@ -87,7 +93,8 @@ def test_sampler_graph(ctx, voices, total, block):
     _same_states(_states(bank), _states(ref), "sampler")
 
 
-def test_fm_graph(ctx):
+@pytest.mark.parametrize("device_spans", [False, True])
+def test_fm_graph(ctx, device_spans):
     sr, voices, total, block = 48000.0, 36, 9 * 1024 + 50, 4 * 1024
     wl = synth.fm_bank(voices, total, sr, seed=21, mean_note=0.04)
     detune, index = synth.fm_mod_inputs(voices, total)
@@ -95,6 +102,8 @@ def test_fm_graph(ctx):
     ref = banks.FmDetunedBank(ctx, wl, sr, total)
     unfused = _render(ctx, ref, total, block, 6, fused=False, extra=(detune, index))
     bank = banks.FmDetunedBank(ctx, wl, sr, total)
+    if device_spans:  # Trigger replay and the prev_note_on views on the GPU (zcu_event_bank_*)
+        bank.use_device_spans(wl)
     g = bank.build_graph()
     assert "SineMod<true, true>" in g.source and "TriSawMod<true>" in g.source
     got = _render(ctx, bank, total, block, 6, fused=True, extra=(detune, index))

@@ -52,11 +52,27 @@ def run(ctx, name, bank, frames, ntemps, bytes_per_vs, peak, ins=(), reps=3):
     return res
 
 
-def run_fused(ctx, name, bank, frames, bytes_per_vs, peak, ins=(), reps=3, gains=None):
-    """The same bank body as ONE fused graph kernel (zcu_graph_*): per-voice output buffer (BUFFERS) and stereo mix (MIX)."""
+def run_fused(ctx, name, bank, frames, bytes_per_vs, peak, ins=(), reps=3, gains=None, wl=None):
+    """The same bank body as ONE fused graph kernel (zcu_graph_*): per-voice output buffer (BUFFERS) and stereo mix (MIX).
+    With wl: the block's span tables come from the device-side Trigger replay (zcu_event_bank_*); device_span_tables_ms is
+    its device time, host_span_call_ms the host time of the call that enqueues it."""
     V = bank.voices
     res = {}
-    prepared = bank.prepare_block(0, frames)
+    if wl is not None:
+        bank.use_device_spans(wl)
+        bank.prepare_block(0, frames)  # warm-up (allocations, static tables)
+        bank.dev_trigger.reset()
+        ctx.sync()
+        t0 = time.perf_counter()
+        ctx.timer_start()
+        prepared = bank.prepare_block(0, frames)
+        t_call = time.perf_counter() - t0
+        dev_ms = ctx.timer_stop_ms()
+        res["device_span_tables_ms"] = dev_ms
+        res["host_span_call_ms"] = t_call * 1e3
+        print(f"{name:34s} device span tables: {dev_ms:7.3f} ms on the GPU, {t_call * 1e3:7.3f} ms of host time to enqueue", flush=True)
+    else:
+        prepared = bank.prepare_block(0, frames)
     for mode, mname in ((L.GRAPH_OUT_BUFFERS, "fused_buffers"), (L.GRAPH_OUT_MIX, "fused_mix")):
         if mode == L.GRAPH_OUT_MIX and gains is None:
             continue
@@ -134,7 +150,7 @@ def main():
         del det, idx
         res.append(run(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 6, 140, peak, ins=ins))
         res[-1].update(run_fused(ctx, "configs[2] FmDetuned", banks.FmDetunedBank(ctx, wl, 48000.0, frames), frames, 140, peak, ins=ins,
-                                 gains=np.full((V, 2), 1.0 / V, dtype=np.float32)))
+                                 gains=np.full((V, 2), 1.0 / V, dtype=np.float32), wl=wl))
         for b in ins:
             b.free()
     # configs[3] sampler: 2048 voices, 64 mix buffers @44.1 kHz
@@ -145,13 +161,13 @@ def main():
         smp = ctx.sample(pcm, 1, 44100, L.FMT_SIGNED16_LSB)
         res.append(run(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 2, 48, peak))
         res[-1].update(run_fused(ctx, "configs[3] SamplerVoice", banks.SamplerVoiceBank(ctx, wl, smp, 44100.0, frames), frames, 48, peak,
-                                 gains=np.full((V, 2), 1.0 / V, dtype=np.float32)))
+                                 gains=np.full((V, 2), 1.0 / V, dtype=np.float32), wl=wl))
     # configs[4] SFX batch: 65536 jobs x 24 mix buffers
     V, frames = int(65536 * sc), 24 * 1024
     if 4 in only:
         wl = synth.sfx_bank(V, frames)
         res.append(run(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 3, 100, peak))
-        res[-1].update(run_fused(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 100, peak, gains=wl["gains"]))
+        res[-1].update(run_fused(ctx, "configs[4] Sfx", banks.SfxBank(ctx, wl, 48000.0, frames), frames, 100, peak, gains=wl["gains"], wl=wl))
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     json.dump(dict(peak_gbs=peak, paint_mode="exact" if args.exact else "tolerance", results=res), open(args.out, "w"), indent=1)
     ctx.close()

@@ -115,6 +115,14 @@ PROTOTYPES = {
     "zcu_cycle_advance": (None, [_P, _F, _U]),
     "zcu_bank_trigger_init": (None, [_P, _U, _P]),
     "zcu_bank_spans": (C.c_int64, [_P, _U, _P, _P, _U, _U, _U, _U, _P, _P, _U64]),
+    "zcu_event_bank_create": (_I, [_P, _U, _P, _P, _U, _U, _P]),
+    "zcu_event_bank_free": (None, [_P]),
+    "zcu_event_bank_reset": (_I, [_P, _P]),
+    "zcu_event_bank_get_state": (_I, [_P, _P, _P]),
+    "zcu_event_bank_set_state": (_I, [_P, _P, _P]),
+    "zcu_event_bank_spans": (_I, [_P, _P, _U, _U, _P]),
+    "zcu_spans_download": (_I, [_P, _P, _P, _P, _U64, _P]),
+    "zcu_spans_prev_note_on_views": (_I, [_P, _P, _P, _P, _P, _P]),
     "zcu_render_create": (_I, [_P, _P, _P, _P, _P]),
     "zcu_render_free": (None, [_P]),
     "zcu_render_set_events": (_I, [_P, _P, _P, _P]),

@@ -15,7 +15,7 @@ import numpy as np
 
 from . import _lib as L
 from . import engine as E
-from .events import BankTrigger
+from .events import BankTrigger, DeviceBankTrigger
 
 
 def full_span_table(voices, num_frames, buffer_frames, rows):
@@ -32,7 +32,28 @@ def full_span_table(voices, num_frames, buffer_frames, rows):
     return off, spans
 
 
-class SamplerVoiceBank:
+class _Kept:
+    """a span table owned by its bank: callers that free their prepared tables leave it alone"""
+
+    def __init__(self, spans):
+        self.spans, self._h, self.voices, self.frames = spans, spans._h, spans.voices, spans.frames
+
+    def free(self):
+        pass
+
+
+class _DeviceSpansMixin:
+    """use_device_spans(): the bank's Trigger is replayed on the GPU from device-resident events (zcu_event_bank_*), so a
+    block's span tables cost the host nothing; the default (host replay in libzangcu + upload) stays available."""
+    dev_trigger = None
+
+    def use_device_spans(self, wl):
+        self._full_tables = {}
+        self.dev_trigger = DeviceBankTrigger(self.ctx, wl["event_off"], wl["events"], self.total_frames, self.buffer_frames)
+        return self
+
+
+class SamplerVoiceBank(_DeviceSpansMixin):
     """paint body per voice (per mix buffer):
         zero(span, t0); while (trigger.next) sampler.paint(result.span, {t0}, ..., result.params)
         multiplyWithScalar(span, t0, 2.5)                                   (example_sampler.zig:94-108)
@@ -63,10 +84,19 @@ class SamplerVoiceBank:
     def prepare_block(self, first_frame, num_frames):
         """Host side of a block: Trigger replay and upload of the span tables (the reference's per-buffer event logic)."""
         ctx, V = self.ctx, self.voices
-        off, spans = self.trigger.spans(first_frame, num_frames)
-        return (ctx.spans(V, num_frames, off, spans),
-                ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.arange(V))),
-                ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.zeros(V))))
+        if self.dev_trigger is not None:
+            trig = self.dev_trigger.spans(first_frame, num_frames)
+        else:
+            trig = ctx.spans(V, num_frames, *self.trigger.spans(first_frame, num_frames))
+        if self.dev_trigger is None:
+            return (trig,
+                    ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.arange(V))),
+                    ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, np.zeros(V))))
+        # the whole-buffer tables depend on the block length alone: built once, kept on the device
+        if num_frames not in self._full_tables:
+            self._full_tables[num_frames] = tuple(_Kept(ctx.spans(V, num_frames, *full_span_table(V, num_frames, self.buffer_frames, rows)))
+                                                  for rows in (np.arange(V), np.zeros(V)))
+        return (trig,) + self._full_tables[num_frames]
 
     def paint_block(self, first_frame, num_frames, out, temps, prepared=None):
         ctx = self.ctx
@@ -119,7 +149,7 @@ class SamplerVoiceBank:
                 s.free()
 
 
-class SfxBank:
+class SfxBank(_DeviceSpansMixin):
     """paint body per job (per Trigger span):
         zero(t0); noise.paint(span, {t0}, .{ .color = .white })
         zero(t1); curve.paint(span, {t1}, note_id_changed, .{ .function = .smoothstep, .curve = job's 3 nodes })
@@ -161,6 +191,8 @@ class SfxBank:
         self.env_rows["note_on"][:ev.size] = ev["note_on"]
 
     def prepare_block(self, first_frame, num_frames):
+        if self.dev_trigger is not None:
+            return (self.dev_trigger.spans(first_frame, num_frames),)
         off, spans = self.trigger.spans(first_frame, num_frames)
         return (self.ctx.spans(self.voices, num_frames, off, spans),)
 
@@ -220,7 +252,7 @@ class SfxBank:
                 s.free()
 
 
-class FmDetunedBank:
+class FmDetunedBank(_DeviceSpansMixin):
     """paint body per voice (per Trigger span), params = {sample_rate, freq, note_on}, two per-sample inputs:
         defer self.prev_note_on = params.note_on                                        (example_portamento.zig:51)
         zero(t0); porta.paint(span, {t0}, note_id_changed, .{ .curve = .{ .cubed = 0.5 }, .goal = freq, note_on, prev_note_on })
@@ -291,6 +323,11 @@ class FmDetunedBank:
         return off, spans, sp_porta, sp_env, sp_plain
 
     def prepare_block(self, first_frame, num_frames):
+        if self.dev_trigger is not None:  # Trigger replay and the prev_note_on bookkeeping both on the device
+            src = self.dev_trigger.spans(first_frame, num_frames)
+            views = self.dev_trigger.prev_note_on_views(src)
+            src.free()
+            return views
         off, _, a_porta, a_env, a_plain = self.span_tables(first_frame, num_frames)
         return tuple(self.ctx.spans(self.voices, num_frames, off, a) for a in (a_porta, a_env, a_plain))
 

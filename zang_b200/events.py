@@ -143,3 +143,76 @@ class BankTrigger:
         if n < 0:
             raise RuntimeError(f"span table needs {-n} rows, {cap} provided")
         return off, spans[:n].copy()
+
+
+def _err(ctx):
+    m = lib.zcu_last_error(ctx._h)
+    return m.decode() if m else ""
+
+
+class DeviceSpans:
+    """A span table that was built on the device (same handle type as engine.Spans)."""
+
+    def __init__(self, ctx, handle, voices, frames):
+        self.ctx, self._h, self.voices, self.frames = ctx, handle, voices, frames
+
+    def download(self):
+        """(voice_off[V+1], spans) read back from the device."""
+        off = np.zeros(self.voices + 1, dtype=np.uint32)
+        n = C.c_uint64()
+        rc = lib.zcu_spans_download(self.ctx._h, self._h, ptr(off), None, 0, C.byref(n))
+        assert rc == L.OK, _err(self.ctx)
+        spans = np.zeros(max(int(n.value), 1), dtype=L.span_dtype)
+        rc = lib.zcu_spans_download(self.ctx._h, self._h, ptr(off), ptr(spans), int(n.value), C.byref(n))
+        assert rc == L.OK, _err(self.ctx)
+        return off, spans[:int(n.value)].copy()
+
+    def free(self):
+        if self._h:
+            lib.zcu_spans_free(self._h)
+            self._h = None
+
+
+class DeviceBankTrigger:
+    """BankTrigger with the events resident on the GPU and the Trigger replayed there (zcu_event_bank_*): `spans()` returns a
+    device span table without any per-block host work."""
+
+    def __init__(self, ctx, event_off, events, total_frames, buffer_frames=1024):
+        self.ctx = ctx
+        off = np.ascontiguousarray(event_off, dtype=np.uint32)
+        ev = np.ascontiguousarray(events, dtype=L.note_event_dtype)
+        self.voices = off.size - 1
+        self.total_frames, self.buffer_frames = int(total_frames), int(buffer_frames)
+        h = C.c_void_p()
+        rc = lib.zcu_event_bank_create(ctx._h, self.voices, ptr(off), ptr(ev), self.buffer_frames, self.total_frames, C.byref(h))
+        if rc != L.OK:
+            raise RuntimeError(f"zcu_event_bank_create: {_err(ctx)}")
+        self._h = h
+
+    def reset(self):
+        assert lib.zcu_event_bank_reset(self.ctx._h, self._h) == L.OK
+
+    def spans(self, first_frame, num_frames):
+        h = C.c_void_p()
+        rc = lib.zcu_event_bank_spans(self.ctx._h, self._h, int(first_frame), int(num_frames), C.byref(h))
+        if rc != L.OK:
+            raise RuntimeError(f"zcu_event_bank_spans: {_err(self.ctx)}")
+        return DeviceSpans(self.ctx, h, self.voices, int(num_frames))
+
+    def prev_note_on_views(self, src):
+        """(porta, env, plain) views of a Trigger table for an instrument that keeps prev_note_on (example_portamento.zig:51)."""
+        hs = [C.c_void_p() for _ in range(3)]
+        rc = lib.zcu_spans_prev_note_on_views(self.ctx._h, self._h, src._h, *[C.byref(h) for h in hs])
+        if rc != L.OK:
+            raise RuntimeError(f"zcu_spans_prev_note_on_views: {_err(self.ctx)}")
+        return tuple(DeviceSpans(self.ctx, h, self.voices, src.frames) for h in hs)
+
+    def state(self):
+        st = np.zeros(self.voices, dtype=L.bank_trigger_dtype)
+        assert lib.zcu_event_bank_get_state(self.ctx._h, self._h, ptr(st)) == L.OK
+        return st
+
+    def free(self):
+        if self._h:
+            lib.zcu_event_bank_free(self._h)
+            self._h = None
