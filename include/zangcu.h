@@ -182,12 +182,24 @@ int zcu_selftest_div_numerator(zcu_ctx* ctx, float numerator, uint64_t* mismatch
 enum { ZCU_PAINT_EXACT = 0, ZCU_PAINT_TOLERANCE = 1 };
 int zcu_ctx_set_paint_mode(zcu_ctx* ctx, int mode);
 int zcu_ctx_paint_mode(const zcu_ctx* ctx);
+/* Output mode of the module paints (zcu_paint_*), per context.  ZCU_OUT_ACCUMULATE (default) is the reference's contract:
+ * paint() adds to what the output holds.  ZCU_OUT_OVERWRITE makes one call stand for the reference's ubiquitous pair
+ * `zang.zero(span, out); module.paint(span, {out}, ...)` (examples/modules.zig:220-246): inside its spans the output is
+ * 0 + what the module adds, bit for bit what the pair leaves, and the output is never read (a generator then moves 4
+ * instead of 4 + 8 bytes per voice-sample).  Frames outside the spans keep their contents in both modes. */
+enum { ZCU_OUT_ACCUMULATE = 0, ZCU_OUT_OVERWRITE = 1 };
+int zcu_ctx_set_paint_output(zcu_ctx* ctx, int mode);
+int zcu_ctx_paint_output(const zcu_ctx* ctx);
 /* Noise (src/modules/Noise.zig) is painted in time segments that start from an exact jump of the xoshiro256++ state by the
  * number of samples painted before the segment.  Zig's Random.float(f32) draws a second u64 with probability 2^-41 per
  * sample; a jump cannot foresee that, and the voice's later segments of that one call are then one draw behind the
  * sequential loop.  This counter (since context creation; synchronises the stream) tells how often it happened: 0 means
  * every Noise paint so far is bit-identical to the reference loop.  Expected once per 2.2e12 noise samples. */
 int zcu_ctx_noise_resync_count(zcu_ctx* ctx, uint64_t* out);
+/* ZCU_PAINT_TOLERANCE diagnostics since the last call: out[0] CTAs (128 voices x time segment) that started from a warm-up
+ * window, out[1] the sum and out[2] the maximum of those windows in frames, out[3] CTAs whose verification failed and which
+ * waited for their predecessor segment's end state instead.  Synchronises; resets the counters. */
+int zcu_ctx_paint_warm_stats(zcu_ctx*, uint32_t out[4]);
 /* Host-only (no device): the same jump applied on the CPU, state <- T^n state of xoshiro256 (n < 2^24), for checking the
  * matrices against n plain steps of the generator. */
 int zcu_xoshiro_jump_host(uint64_t state[4], uint32_t n);

@@ -153,8 +153,10 @@ def test_scan_mode_matches_exact_mode_mix(ctx, tmode):
     assert_close(mixes[1], mixes[0], tol, "scan-mode mix vs exact-mode mix")
 
 
-def test_unfused_module_path_bit_exact(ctx):
-    """The drop-in path: every module called through its own C-ABI entry point on device buffers."""
+@pytest.mark.parametrize("overwrite", [False, True])
+def test_unfused_module_path_bit_exact(ctx, overwrite):
+    """The drop-in path: every module called through its own C-ABI entry point on device buffers.  overwrite: the body's
+    `zero; paint` pairs as single calls in ZCU_OUT_OVERWRITE mode (5 calls instead of 8), temps pre-filled with garbage."""
     voices, nbuf = 40, 6
     total = nbuf * 1024
     wl = small_workload(voices, total, seed=99)
@@ -174,8 +176,10 @@ def test_unfused_module_path_bit_exact(ctx):
     for blk in range(2):
         off, spans = synth.spans_from_events(wl["event_off"], wl["events"], total, 1024, first_frame=blk * half, num_frames=half)
         sp = ctx.spans(voices, half, off, spans)
-        o, a, b = ctx.buf(half, voices), ctx.buf(half, voices), ctx.buf(half, voices)
-        bank.paint(sp, [o], [a, b], instr_params)
+        junk = np.random.default_rng(blk).standard_normal((half, voices)).astype(np.float32)
+        o, a, b = ctx.buf(half, voices), ctx.buf(half, voices, junk), ctx.buf(half, voices, junk * 3)
+        bank.paint(sp, [o], [a, b], instr_params, overwrite=overwrite)
+        assert ctx.paint_output() == L.OUT_ACCUMULATE
         got = o.download()
         assert_bit_exact(got, want[blk * half:(blk + 1) * half], f"un-fused NiceInstrument block {blk}")
         for x in (sp, o, a, b):

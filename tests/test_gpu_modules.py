@@ -23,6 +23,47 @@ from cases import CASES, NBUF, SR, TRANSCENDENTAL_TOL, V, case_rng, gen_block
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_module_overwrite_mode(ctx, case):
+    """ZCU_OUT_OVERWRITE: one call = `zang.zero(span, out); module.paint(span, {out}, ...)` (examples/modules.zig:220-246):
+    inside the spans the output is what the pair leaves in a buffer of garbage, outside them the garbage is untouched."""
+    name, kind, variant, ins, bf, exact = case
+    rng = case_rng(name + "/overwrite")
+    frames = NBUF * bf
+    mod = E.MODULE_CLASSES[kind](ctx, V, first_seed=5)
+    ostate = oracle.state_init(kind, V, first_seed=5)
+    off, spans, params, out0, inputs = gen_block(case, rng)
+    want = out0.copy()
+    oracle.basic(0, off, spans, want)  # zero(span, out)
+    oracle.paint(kind, off, spans, params, ostate, want, *inputs)
+    d_out = ctx.buf(frames, V, out0)
+    d_in = [None if a is None else ctx.buf(frames, V, a) for a in inputs]
+    sp = ctx.spans(V, frames, off, spans)
+    ctx.set_paint_output(L.OUT_OVERWRITE)
+    try:
+        if kind == L.MOD_SINE_OSC:
+            mod.paint(sp, [d_out], [], params, freq=d_in[0], phase=d_in[1])
+        elif kind in (L.MOD_PULSE_OSC, L.MOD_TRISAW_OSC):
+            mod.paint(sp, [d_out], [], params, freq=d_in[0])
+        elif kind == L.MOD_FILTER:
+            mod.paint(sp, [d_out], [], params, input=d_in[0], cutoff=d_in[1], res=d_in[2])
+        elif kind in (L.MOD_DECIMATOR, L.MOD_DISTORTION):
+            mod.paint(sp, [d_out], [], params, input=d_in[0])
+        elif kind == L.MOD_CYCLE:
+            mod.paint(sp, [d_out], [], params, speed=d_in[0])
+        else:
+            mod.paint(sp, [d_out], [], params)
+    finally:
+        ctx.set_paint_output(L.OUT_ACCUMULATE)
+    got = d_out.download()
+    if exact:
+        assert_bit_exact(got, want, f"{name} overwrite")
+    else:
+        assert_close(got, want, TRANSCENDENTAL_TOL, f"{name} overwrite")
+    for b in [d_out, sp] + [x for x in d_in if x is not None]:
+        b.free()
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_module_parity(ctx, case):
     name, kind, variant, ins, bf, exact = case
     rng = case_rng(name)

@@ -36,5 +36,25 @@ for name, bps, fn in calls:
         fn()
         best = min(best, ctx.timer_stop_ms())
     tot += best
-    print(f"{name:20s} {best:8.3f} ms  {V * frames * bps / best / 1e6:8.1f} GB/s (full-coverage bytes)")
-print(f"sum {tot:.3f} ms")
+    import ctypes as C
+    st = (C.c_uint32 * 4)()
+    L.lib.zcu_ctx_paint_warm_stats(ctx._h, st)
+    extra = f"   warm-up: {st[0] // 3} CTAs/launch, mean window {st[1] / max(st[0], 1):.0f} frames, max {st[2]}, chained {st[3] // 3}/launch" if st[0] else ""
+    print(f"{name:20s} {best:8.3f} ms  {V * frames * bps / best / 1e6:8.1f} GB/s (full-coverage bytes){extra}")
+print(f"sum {tot:.3f} ms = {V * frames * 64 / tot / 1e6:.0f} GB/s of the reference chain's 64 B per voice-sample")
+# the same body with every `zero; paint` pair as ONE call (ZCU_OUT_OVERWRITE): 5 calls
+ctx.set_paint_output(L.OUT_OVERWRITE)
+calls2 = [("PulseOsc (overwrite)", lambda: bank.osc.paint(sp, [t0], [], pp)), ("multiplyWithScalar", lambda: ctx.multiplyWithScalar(sp, t0, 0.5)),
+          ("Filter (overwrite)", lambda: bank.flt.paint(sp, [t1], [], fp, input=t0)), ("Envelope (overwrite)", lambda: bank.env.paint(sp, [t0], [], ep)),
+          ("multiply", lambda: ctx.multiply(sp, out, t0, t1))]
+tot2 = 0.0
+for name, fn in calls2:
+    best = 1e9
+    for rep in range(3):
+        ctx.timer_start()
+        fn()
+        best = min(best, ctx.timer_stop_ms())
+    tot2 += best
+    print(f"{name:22s} {best:8.3f} ms")
+ctx.set_paint_output(L.OUT_ACCUMULATE)
+print(f"sum {tot2:.3f} ms = {V * frames * 64 / tot2 / 1e6:.0f} GB/s of the reference chain's 64 B per voice-sample")

@@ -28,7 +28,10 @@ PROTOTYPES = {
     "zcu_ctx_launch_count": (_U64, [_P]),
     "zcu_ctx_set_paint_mode": (_I, [_P, _I]),
     "zcu_ctx_paint_mode": (_I, [_P]),
+    "zcu_ctx_set_paint_output": (_I, [_P, _I]),
+    "zcu_ctx_paint_output": (_I, [_P]),
     "zcu_ctx_noise_resync_count": (_I, [_P, _P]),
+    "zcu_ctx_paint_warm_stats": (_I, [_P, _P]),
     "zcu_xoshiro_jump_host": (_I, [_P, _U]),
     "zcu_selftest_div_by_const": (_I, [_P, _F, _P, _P]),
     "zcu_selftest_div_numerator": (_I, [_P, _F, _P, _P]),

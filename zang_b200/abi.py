@@ -24,6 +24,7 @@ AUDIO_SIGNED8, AUDIO_SIGNED16_LSB = 0, 1
 INSTR_NICE = 0
 RENDER_EXACT, RENDER_SCAN, RENDER_SEGMENTS = 0, 1, 2
 PAINT_EXACT, PAINT_TOLERANCE = 0, 1
+OUT_ACCUMULATE, OUT_OVERWRITE = 0, 1
 MAX_POLYPHONY = 32
 # fused module graphs
 GREF_NONE, GREF_TEMP, GREF_OUTPUT, GREF_INPUT = range(4)

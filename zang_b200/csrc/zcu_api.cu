@@ -125,6 +125,23 @@ int zcu_ctx_set_paint_mode(zcu_ctx* ctx, int mode) {
     return ZCU_OK;
 }
 int zcu_ctx_paint_mode(const zcu_ctx* ctx) { return ctx ? ctx->paint_mode : ZCU_PAINT_EXACT; }
+int zcu_ctx_set_paint_output(zcu_ctx* ctx, int mode) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, mode == ZCU_OUT_ACCUMULATE || mode == ZCU_OUT_OVERWRITE, "unknown output mode");
+    ctx->paint_output = mode;
+    return ZCU_OK;
+}
+int zcu_ctx_paint_output(const zcu_ctx* ctx) { return ctx ? ctx->paint_output : ZCU_OUT_ACCUMULATE; }
+int zcu_ctx_paint_warm_stats(zcu_ctx* ctx, uint32_t out[4]) {
+    if (!ctx || !out) return ZCU_ERR_INVALID;
+    zcu_use_device(ctx);
+    out[0] = out[1] = out[2] = out[3] = 0;
+    if (!ctx->paint_ticket) return ZCU_OK;
+    ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ZCU_CUDA(ctx, cudaMemcpy(out, ctx->paint_ticket + 2, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    ZCU_CUDA(ctx, cudaMemset(ctx->paint_ticket + 2, 0, 4 * sizeof(uint32_t)));
+    return ZCU_OK;
+}
 int zcu_ctx_noise_resync_count(zcu_ctx* ctx, uint64_t* out) {
     if (!ctx || !out) return ZCU_ERR_INVALID;
     *out = 0;

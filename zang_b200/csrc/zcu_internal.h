@@ -23,6 +23,7 @@ struct zcu_ctx {
     int sm_count = 148;
     // ZCU_PAINT_TOLERANCE: published segment end states + ready flags (stamped with paint_epoch) of the lockstep kernel
     int paint_mode = 0;
+    int paint_output = 0;  // ZCU_OUT_ACCUMULATE / ZCU_OUT_OVERWRITE
     void* chain = nullptr;
     size_t chain_bytes = 0;
     uint32_t* chain_flags = nullptr;

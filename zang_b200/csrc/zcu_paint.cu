@@ -35,8 +35,8 @@ int ensure_chain(zcu_ctx* ctx, size_t states, size_t flags) {
         ctx->paint_epoch = 0;
     }
     if (!ctx->paint_ticket) {
-        ZCU_CUDA(ctx, cudaMalloc(&ctx->paint_ticket, 2 * sizeof(uint32_t)));
-        ZCU_CUDA(ctx, cudaMemsetAsync(ctx->paint_ticket, 0, 2 * sizeof(uint32_t), ctx->stream));
+        ZCU_CUDA(ctx, cudaMalloc(&ctx->paint_ticket, 8 * sizeof(uint32_t)));
+        ZCU_CUDA(ctx, cudaMemsetAsync(ctx->paint_ticket, 0, 8 * sizeof(uint32_t), ctx->stream));
         ctx->paint_ticket_base = 0;
     }
     return ZCU_OK;
@@ -151,6 +151,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     a.ticket = nullptr;
     a.ticket_base = 0;
     a.chain_err = nullptr;
+    a.warm_stats = nullptr;
     if ((warm || scan) && p.nseg > 1) {
         int rc = ensure_chain(ctx, (size_t)p.nseg * a.V, (size_t)p.nseg * p.grid_x);
         if (rc) return rc;
@@ -161,6 +162,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         a.ticket = ctx->paint_ticket;
         a.ticket_base = ctx->paint_ticket_base;
         a.chain_err = ctx->paint_ticket + 1;
+        a.warm_stats = warm ? ctx->paint_ticket + 2 : nullptr;
         ctx->paint_ticket_base += p.grid_x * p.nseg;  // one ticket per CTA of this launch (mod 2^32, like the device counter)
     } else if (!skip) {
         p.nseg = 1;
@@ -185,11 +187,14 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         ctx->launches++;
         ZCU_CUDA(ctx, cudaGetLastError());
     }
-    if (!ctx->attr_done.count((const void*)k_paint_lockstep<M>)) {  // the attribute is per device: tracked per context
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_paint_lockstep<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
-        ctx->attr_done.insert((const void*)k_paint_lockstep<M>);
+    // ZCU_OUT_OVERWRITE: `zero; paint` in one call (modules that overwrite anyway have a single form)
+    const bool ovr = ctx->paint_output == ZCU_OUT_OVERWRITE && !WriteOnlyOf<M>::value;
+    auto kern = ovr ? k_paint_lockstep<M, true> : k_paint_lockstep<M, false>;
+    if (!ctx->attr_done.count((const void*)kern)) {  // the attribute is per device: tracked per context
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
+        ctx->attr_done.insert((const void*)kern);
     }
-    k_paint_lockstep<M><<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4, p.stages);
+    kern<<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4, p.stages);
     ctx->launches++;
     ZCU_CUDA(ctx, cudaGetLastError());
     return ZCU_OK;

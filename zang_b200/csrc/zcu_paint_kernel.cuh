@@ -44,6 +44,20 @@ struct WriteOnlyOf<M, std::void_t<decltype(M::WRITE_ONLY)>> { static constexpr b
 
 // m.sample_warm() for modules that have it (the call sits in a generic lambda, where a plain member call would be looked up
 // for every module)
+// M::WARM_EXACT: the warm-up window is computed in closed form from the spans' constants (no verification afterwards)
+template <class M, class = void>
+struct WarmExactOf { static constexpr bool value = false; };
+template <class M>
+struct WarmExactOf<M, std::void_t<decltype(M::WARM_EXACT)>> { static constexpr bool value = M::WARM_EXACT; };
+template <class M, bool = WarmExactOf<M>::value>
+struct WarmExactCall { static __device__ __forceinline__ uint32_t window(M&, const PaintArgs&, uint32_t, uint32_t, uint32_t, uint32_t) { return 0xFFFFFFFFu; } };
+template <class M>
+struct WarmExactCall<M, true> {
+    static __device__ __forceinline__ uint32_t window(M& m, const PaintArgs& a, uint32_t k0, uint32_t kb, uint32_t F, uint32_t f_lo) {
+        return m.warm_window_exact(a, k0, kb, F, f_lo);
+    }
+};
+
 template <class M, bool = WarmOf<M>::value>
 struct WarmCall { static __device__ __forceinline__ void sample(M&, float, float, float) {} };
 template <class M>
@@ -139,7 +153,9 @@ __device__ __forceinline__ void pipeline_wait_prior_rt(uint32_t n) {
 constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
 constexpr int kPaintStages = 3;   // tiles in the cp.async ring
 
-template <class M>
+// OVR (ZCU_OUT_OVERWRITE): the call stands for `zero(span, out); paint(span, out)`: inside its spans the output starts from 0
+// and is never read, so the output tile is not loaded (4 instead of 12 bytes per voice-sample for a generator)
+template <class M, bool OVR = false>
 __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a, uint32_t T, uint32_t seg_frames, uint32_t vec4, uint32_t S) {
     extern __shared__ __align__(16) float smem[];
     constexpr uint32_t W = kPaintWarps, RV = 32 * W;  // S = tiles in the cp.async ring (3..8: deeper when few CTAs share an SM)
@@ -184,7 +200,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
 
     // this CTA's segment of the frame axis (seg_frames is a multiple of T)
     constexpr bool kWarm = WarmOf<M>::value;
-    constexpr bool kWriteOnly = WriteOnlyOf<M>::value;
+    constexpr bool kWriteOnly = WriteOnlyOf<M>::value || OVR;
     constexpr bool kScan = ScanOf<M>::value;
     const bool warm = kWarm && a.chain != nullptr;  // tolerance mode: segments start from a verified warm-up or the chain
     const bool scan = kScan && a.chain != nullptr;  // exact chained prefix sum: segments pass their integer state along
@@ -388,9 +404,10 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 }
                 k = kk; s_start = p_start; s_end = p_end; s_flags = p_flags; s_param = p_param;
                 // the span painting at f_begin (or the last one before it) provides the constants of the estimate
-                uint32_t q_param = 0xFFFFFFFFu, q_flags = 0, q_len = 0;
+                uint32_t q_param = 0xFFFFFFFFu, q_flags = 0, q_len = 0, kq = kk;
                 while (p_start < f_begin) {
                     q_param = p_param; q_flags = p_flags; q_len = p_end - p_start;
+                    kq = kk;
                     kk++;
                     if (kk >= ke) break;
                     const uint4 s = *reinterpret_cast<const uint4*>(a.spans + kk);
@@ -398,8 +415,12 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 }
                 est = 0xFFFFFFFFu;  // painted before, but not inside the longest window: only the chain knows the state
                 if (q_param != 0xFFFFFFFFu) {
-                    m.begin_span(a, q_param, q_flags, q_len);
-                    est = m.warm_estimate(a.warm_cap);
+                    if constexpr (WarmExactOf<M>::value) {
+                        est = WarmExactCall<M>::window(m, a, a.off[v], kq, f_begin, f_lo);
+                    } else {
+                        m.begin_span(a, q_param, q_flags, q_len);
+                        est = m.warm_estimate(a.warm_cap);
+                    }
                 }
                 atomicMax(&s_w, est);
             }
@@ -410,6 +431,11 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             if (Wf == f_begin) Wf = 0;    // a window back to frame 0 is the sequential walk: chain instead
             const uint32_t f_w = f_begin - Wf;
             tile_first = f_w / T;
+            if (a.warm_stats && tid == 0) {
+                atomicAdd(a.warm_stats + 0, 1u);
+                atomicAdd(a.warm_stats + 1, Wf);
+                atomicMax(a.warm_stats + 2, Wf);
+            }
             if (valid && !pristine) {
                 m.warm_begin();
                 while (s_end <= f_w) {
@@ -530,6 +556,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             // no deadlock whatever the dispatch order; an undamped filter degenerates to the sequential walk)
             const bool ok = !valid || pristine || (tile_first < tile0 && m.warm_ok());
             if (!__syncthreads_and(ok)) {
+                if (a.warm_stats && tid == 0) atomicAdd(a.warm_stats + 3, 1u);
                 if (tid == 0) wait_predecessor(256);
                 __syncthreads();
                 if (valid && !pristine) m.chain_load(a.chain + (size_t)(by - 1) * V + v);
