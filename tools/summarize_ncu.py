@@ -41,6 +41,7 @@ keep = re.compile(r"dram__bytes|gpu__time_duration|sm__warps_active|launch__(reg
                   r"lts__t_bytes\.sum$|smsp__average_warp.*stalled.*ratio|sm__inst_executed_pipe_(fma|alu|lsu|fmaheavy|fmalite)")
 out = []
 traffic = []
+issue = {}
 for row in rows[2:]:
     name = row[hdr.index("Kernel Name")]
     if kname not in name:
@@ -56,10 +57,21 @@ for row in rows[2:]:
         v, u = d.get(key, ("0", "byte"))
         return float(v.replace(",", "")) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
     traffic.append(to_bytes("dram__bytes_read.sum") + to_bytes("dram__bytes_write.sum"))
+
+    def num(key):
+        try:
+            return float(d[key][0].replace(",", ""))
+        except Exception:
+            return None
+    issue = {"issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+             "pipe_fma_pct": num("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+             "pipe_alu_pct": num("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+             "warp_instructions": num("smsp__inst_executed.sum"), "duration_ms": num("gpu__time_duration.sum"),
+             "registers_per_thread": num("launch__registers_per_thread")}
 with open(os.path.join(ROOT, "profiles", f"{tag}_{kname}_ncu.txt"), "w") as f:
     f.write(f"# ncu --set full --clock-control none --import-source on (source: {rep})\n" + "\n".join(out) + "\n")
 if traffic:
     with open(os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json"), "w") as f:
         json.dump({"kernel": kname, "dram_bytes_per_launch": max(traffic), "launches_captured": len(traffic),
-                   "source": f"profiles/{tag}_{kname}_ncu.txt", "note": "largest captured launch (a full block of frames)"}, f)
+                   "source": f"profiles/{tag}_{kname}_ncu.txt", "note": "largest captured launch (a full block of frames)", "issue": issue}, f)
 print("ok", len(out), traffic)

@@ -296,6 +296,104 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         }
         return b;
     };
+    // one instruction on one sample: d, a, b, cc are the C expressions of its operands
+    auto statement = [&](const zcu_graph_instr& x, const std::string& d, const std::string& a, const std::string& b, const std::string& cc,
+                         bool run_form) -> std::string {
+        const std::string sc = float_lit(x.scalar);
+        std::string stmt;
+        if (x.op == ZCU_GI_CALL) {
+            char t[200];
+            snprintf(t, sizeof t, "m%u.%s(%s, %s, %s, %s);", x.field, (run_form && fields[x.field].has_run) ? "sample_run" : "sample", d.c_str(),
+                     a.c_str(), b.c_str(), cc.c_str());
+            stmt = t;
+        } else if (x.op == ZCU_GI_BASIC) {
+            switch (x.sub) {  // basics.zig:12-78, the expression forms of BasicMod (zcu_modules.cuh)
+                case 0: stmt = d + " = 0.0f;"; break;
+                case 1: stmt = d + " = " + sc + ";"; break;
+                case 2: stmt = d + " = " + a + ";"; break;
+                case 3: stmt = d + " += " + a + " + " + b + ";"; break;
+                case 4: stmt = d + " += " + a + ";"; break;
+                case 5: stmt = d + " += " + a + " + " + sc + ";"; break;
+                case 6: stmt = d + " += " + sc + ";"; break;
+                case 7: stmt = d + " += " + a + " * " + b + ";"; break;
+                case 8: stmt = d + " *= " + a + ";"; break;
+                case 9: stmt = d + " += " + a + " * " + sc + ";"; break;
+                case 10: stmt = d + " *= " + sc + ";"; break;
+            }
+        } else {
+            const std::string A = x.scalar_side == ZCU_SCALAR_A ? sc : a, B = x.scalar_side == ZCU_SCALAR_B ? sc : b;
+            switch (x.sub) {  // runtime.zig:528-700: these overwrite
+                case ZCU_ARITH_SUB: stmt = d + " = " + A + " - " + B + ";"; break;
+                case ZCU_ARITH_DIV: stmt = d + " = " + A + " / " + B + ";"; break;
+                case ZCU_ARITH_MIN: stmt = d + " = zs_min(" + A + ", " + B + ");"; break;
+                case ZCU_ARITH_MAX: stmt = d + " = zs_max(" + A + ", " + B + ");"; break;
+                case ZCU_ARITH_NEG: stmt = d + " = -" + a + ";"; break;
+                case ZCU_ARITH_ABS: stmt = d + " = fabsf(" + a + ");"; break;
+                case ZCU_ARITH_SQRT: stmt = d + " = sqrtf(" + a + ");"; break;
+            }
+        }
+        return stmt;
+    };
+    // Four consecutive samples at once, instruction by instruction (all tables live on every lane): the reference's order at a
+    // granularity of four frames instead of a whole span.  Every temp is a register quad; modules with a four-sample form
+    // (sample4: branch-free sines, exact divisions and PCM taps arranged so that the four evaluations overlap) use it.  The
+    // operands of the four frames are loaded before the first instruction, the results stored after the last.
+    auto body4 = [&](const char* ind) {
+        std::string s;
+        auto arr = [&](const zcu_graph_ref& r) -> std::string {
+            char b[32];
+            switch (r.kind) {
+                case ZCU_GREF_TEMP: snprintf(b, sizeof b, "t%u_", r.index); break;
+                case ZCU_GREF_OUTPUT: snprintf(b, sizeof b, "o%u_", r.index); break;
+                case ZCU_GREF_INPUT: snprintf(b, sizeof b, "x%u_", r.index); break;
+                default: snprintf(b, sizeof b, "z4_"); break;
+            }
+            return b;
+        };
+        auto elem = [&](const zcu_graph_ref& r) -> std::string { return r.kind == ZCU_GREF_NONE ? std::string("0.0f") : arr(r) + "[q]"; };
+        appendf(s, "%sconst float z4_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n%s(void)z4_;\n", ind, ind);
+        for (uint32_t i = 0; i < c.num_inputs; i++)
+            if (in_used[i]) {
+                appendf(s, "%sfloat x%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) x%u_[q] = __ldg(g.in[%u] + base + (size_t)(r + q) * g.V);\n", ind, i,
+                        ind, i, i);
+            }
+        for (uint32_t o = 0; o < c.num_outputs; o++) {
+            if (mix)
+                appendf(s, "%sfloat o%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n", ind, o);
+            else
+                appendf(s, "%sfloat o%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) o%u_[q] = g.out[%u][base + (size_t)(r + q) * g.V];\n", ind, o, ind, o, o);
+        }
+        for (uint32_t t = 0; t < c.num_temps; t++) appendf(s, "%sfloat t%u_[4] = {t%u, t%u, t%u, t%u};\n", ind, t, t, t, t, t);
+        for (uint32_t i = 0; i < n; i++) {
+            const zcu_graph_instr& x = ins[i];
+            if (x.op == ZCU_GI_CALL && !fields[x.field].has_run) {
+                // inputs that alias the output are copied first (a four-sample form may write before it has read everything)
+                std::string a[3];
+                for (int q = 0; q < 3; q++) {
+                    a[q] = arr(x.in[q]);
+                    if (x.in[q].kind != ZCU_GREF_NONE && x.in[q].kind == x.out.kind && x.in[q].index == x.out.index) {
+                        appendf(s, "%sconst float c%u_%d_[4] = {%s[0], %s[1], %s[2], %s[3]};\n", ind, i, q, a[q].c_str(), a[q].c_str(), a[q].c_str(), a[q].c_str());
+                        char b[32];
+                        snprintf(b, sizeof b, "c%u_%d_", i, q);
+                        a[q] = b;
+                    }
+                }
+                appendf(s, "%sSample4<decltype(m%u)>::call(m%u, %s, %s, %s, %s);\n", ind, x.field, x.field, arr(x.out).c_str(), a[0].c_str(), a[1].c_str(),
+                        a[2].c_str());
+            } else {
+                const std::string stmt = statement(x, arr(x.out) + "[q]", elem(x.in[0]), elem(x.in[1]), elem(x.in[2]), true);
+                appendf(s, "#pragma unroll\n%sfor (int q = 0; q < 4; q++) { %s }\n", ind, stmt.c_str());
+            }
+        }
+        for (uint32_t o = 0; o < c.num_outputs; o++) {
+            if (mix)
+                appendf(s, "#pragma unroll\n%sfor (int q = 0; q < 4; q++) O[j + r + q][lane] = o%u_[q];\n", ind, o);
+            else
+                appendf(s, "#pragma unroll\n%sfor (int q = 0; q < 4; q++) g.out[%u][base + (size_t)(r + q) * g.V] = o%u_[q];\n", ind, o, o);
+        }
+        for (uint32_t t = 0; t < c.num_temps; t++) appendf(s, "%st%u = t%u_[3];\n", ind, t, t);
+        return s;
+    };
     // the per-sample body; live[k] = expression telling whether table k is live on this lane ("true" in the all-live copy)
     auto body = [&](bool all_live, const char* ind, const char* row) {
         std::string s;
@@ -323,39 +421,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         }
         for (uint32_t i = 0; i < n; i++) {
             const zcu_graph_instr& x = ins[i];
-            const std::string d = ref(x.out), a = ref(x.in[0]), b = ref(x.in[1]), cc = ref(x.in[2]), sc = float_lit(x.scalar);
-            std::string stmt;
-            if (x.op == ZCU_GI_CALL) {
-                char t[160];
-                snprintf(t, sizeof t, "m%u.%s(%s, %s, %s, %s);", x.field, (all_live && fields[x.field].has_run) ? "sample_run" : "sample", d.c_str(),
-                         a.c_str(), b.c_str(), cc.c_str());
-                stmt = t;
-            } else if (x.op == ZCU_GI_BASIC) {
-                switch (x.sub) {  // basics.zig:12-78, the expression forms of BasicMod (zcu_modules.cuh)
-                    case 0: stmt = d + " = 0.0f;"; break;
-                    case 1: stmt = d + " = " + sc + ";"; break;
-                    case 2: stmt = d + " = " + a + ";"; break;
-                    case 3: stmt = d + " += " + a + " + " + b + ";"; break;
-                    case 4: stmt = d + " += " + a + ";"; break;
-                    case 5: stmt = d + " += " + a + " + " + sc + ";"; break;
-                    case 6: stmt = d + " += " + sc + ";"; break;
-                    case 7: stmt = d + " += " + a + " * " + b + ";"; break;
-                    case 8: stmt = d + " *= " + a + ";"; break;
-                    case 9: stmt = d + " += " + a + " * " + sc + ";"; break;
-                    case 10: stmt = d + " *= " + sc + ";"; break;
-                }
-            } else {
-                const std::string A = x.scalar_side == ZCU_SCALAR_A ? sc : a, B = x.scalar_side == ZCU_SCALAR_B ? sc : b;
-                switch (x.sub) {  // runtime.zig:528-700: these overwrite
-                    case ZCU_ARITH_SUB: stmt = d + " = " + A + " - " + B + ";"; break;
-                    case ZCU_ARITH_DIV: stmt = d + " = " + A + " / " + B + ";"; break;
-                    case ZCU_ARITH_MIN: stmt = d + " = zs_min(" + A + ", " + B + ");"; break;
-                    case ZCU_ARITH_MAX: stmt = d + " = zs_max(" + A + ", " + B + ");"; break;
-                    case ZCU_ARITH_NEG: stmt = d + " = -" + a + ";"; break;
-                    case ZCU_ARITH_ABS: stmt = d + " = fabsf(" + a + ");"; break;
-                    case ZCU_ARITH_SQRT: stmt = d + " = sqrtf(" + a + ");"; break;
-                }
-            }
+            const std::string stmt = statement(x, ref(x.out), ref(x.in[0]), ref(x.in[1]), ref(x.in[2]), all_live);
             if (all_live)
                 appendf(s, "%s%s\n", ind, stmt.c_str());
             else
@@ -434,7 +500,11 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     src += "        const size_t base = (size_t)f * g.V + v;\n";
     // all tables live on every lane: batches of four samples; the rows of every external buffer 16 frames ahead are pulled
     // into L1 first (banks too small to fill the chip run one warp per scheduler: nothing else would hide the HBM latency)
-    appendf(src, "        if (__all_sync(FULL, %s && !careful)) {\n", all.c_str());
+    // ... or live on some lanes and dead on all the others (voices that have not started yet, the tail of a partial warp):
+    // the dead lanes sit the run out
+    appendf(src, "        const bool lane_live = %s;\n        const bool lane_idle = !(%s);\n", all.c_str(), any.c_str());
+    src += "        if (__all_sync(FULL, (lane_live && !careful) || lane_idle) && __any_sync(FULL, lane_live)) {\n";
+    src += "          if (lane_live) {\n";
     for (uint32_t f = 0; f < c.num_fields; f++)
         if (fields[f].has_run) appendf(src, "            m%u.run_begin();\n", f);
     src += "            uint32_t r = 0;\n            for (; r + 4 <= run; r += 4) {\n";
@@ -451,13 +521,17 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             src += "                }\n";
         }
     }
-    src += "#pragma unroll\n                for (uint32_t q = 0; q < 4; q++) {\n                    const uint32_t rr = r + q;\n";
-    src += body(true, "                    ", "rr");
+    src += "                {\n";
+    src += body4("                    ");
     src += "                }\n            }\n            for (; r < run; r++) {\n";
     src += body(true, "                ", "r");
     src += "            }\n";
     for (uint32_t f = 0; f < c.num_fields; f++)
         if (fields[f].has_run) appendf(src, "            m%u.run_end();\n", f);
+    if (mix)
+        src += "          } else {\n            for (uint32_t r = 0; r < run; r++) O[j + r][lane] = 0.0f;\n          }\n";
+    else
+        src += "          }\n";
     if (mix)
         src += "        } else {\n            for (uint32_t r = 0; r < run; r++) {\n";
     else

@@ -42,6 +42,37 @@ struct WriteOnlyOf { static constexpr bool value = false; };
 template <class M>
 struct WriteOnlyOf<M, std::void_t<decltype(M::WRITE_ONLY)>> { static constexpr bool value = M::WRITE_ONLY; };
 
+// M::HAS_RUN: the module offers branch-free samples between its own phase changes (run_limit / run_begin / sample_run /
+// run_end, zcu_modules.cuh): a run then also ends where the module says, and all 32 lanes execute the same instructions
+template <class M, class = void>
+struct HasRunOf { static constexpr bool value = false; };
+template <class M>
+struct HasRunOf<M, std::void_t<decltype(M::HAS_RUN)>> { static constexpr bool value = M::HAS_RUN; };
+template <class M, bool = HasRunOf<M>::value>
+struct RunCall {
+    static __device__ __forceinline__ uint32_t limit(M&) { return 0xFFFFFFFFu; }
+    static __device__ __forceinline__ void begin(M&) {}
+    static __device__ __forceinline__ void sample(M& m, float& acc, float x0, float x1, float x2) { m.sample(acc, x0, x1, x2); }
+    static __device__ __forceinline__ void end(M&) {}
+};
+template <class M>
+struct RunCall<M, true> {
+    static __device__ __forceinline__ uint32_t limit(M& m) { return m.run_limit(); }
+    static __device__ __forceinline__ void begin(M& m) { m.run_begin(); }
+    static __device__ __forceinline__ void sample(M& m, float& acc, float x0, float x1, float x2) { m.sample_run(acc, x0, x1, x2); }
+    static __device__ __forceinline__ void end(M& m) { m.run_end(); }
+};
+
+// M::CONST_FILL: a write-only module whose stored value is one constant per call (zero / set)
+template <class M, class = void>
+struct ConstFillOf { static constexpr bool value = false; };
+template <class M>
+struct ConstFillOf<M, std::void_t<decltype(M::CONST_FILL)>> { static constexpr bool value = M::CONST_FILL; };
+template <class M, bool = ConstFillOf<M>::value>
+struct ConstFillCall { static __device__ __forceinline__ float value(const M&) { return 0.0f; } };
+template <class M>
+struct ConstFillCall<M, true> { static __device__ __forceinline__ float value(const M& m) { return m.fill_value(); } };
+
 // m.sample_warm() for modules that have it (the call sits in a generic lambda, where a plain member call would be looked up
 // for every module)
 // M::WARM_EXACT: the warm-up window is computed in closed form from the spans' constants (no verification afterwards)
@@ -62,22 +93,6 @@ template <class M, bool = WarmOf<M>::value>
 struct WarmCall { static __device__ __forceinline__ void sample(M&, float, float, float) {} };
 template <class M>
 struct WarmCall<M, true> { static __device__ __forceinline__ void sample(M& m, float x0, float x1, float x2) { m.sample_warm(x0, x1, x2); } };
-
-// four consecutive samples at once for modules that provide sample4() (same results as four sample() calls, arranged so
-// that the independent parts of the four evaluations can overlap); everything else gets the plain sequence
-template <class M, class = void>
-struct Sample4 {
-    static __device__ __forceinline__ void call(M& m, float (&acc)[4], const float (&x0)[4], const float (&x1)[4], const float (&x2)[4]) {
-#pragma unroll
-        for (int q = 0; q < 4; q++) m.sample(acc[q], x0[q], x1[q], x2[q]);
-    }
-};
-template <class M>
-struct Sample4<M, std::enable_if_t<M::HAS_SAMPLE4>> {
-    static __device__ __forceinline__ void call(M& m, float (&acc)[4], const float (&x0)[4], const float (&x1)[4], const float (&x2)[4]) {
-        m.sample4(acc, x0, x1, x2);
-    }
-};
 
 // M::SCAN: the carried state is an integer sum over the inputs (PulseOsc's phase with a frequency buffer), so time segments
 // can be chained exactly: every segment first sums its own inputs (scan tiles), takes its start state from the predecessor's
@@ -296,7 +311,16 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                 active = true;
             }
             const uint32_t next_boundary = active ? s_end : s_start;
-            const uint32_t run = min(n - j, __reduce_min_sync(0xffffffffu, next_boundary - f));
+            uint32_t dist = next_boundary - f;
+            bool careful = false;  // HAS_RUN: this lane's module cannot promise even one branch-free sample
+            if constexpr (HasRunOf<M>::value && !WT) {
+                if (active) {
+                    const uint32_t s = RunCall<M>::limit(m);
+                    careful = s == 0u;
+                    dist = min(dist, careful ? 1u : s);
+                }
+            }
+            const uint32_t run = min(n - j, __reduce_min_sync(0xffffffffu, dist));
             if (active) {
                 float* so = so_t + j * RV;
                 const float* s0 = s0_t + j * RV;
@@ -310,6 +334,34 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
                         const float x2 = i_in2 >= 0 ? s2[r * RV] : 0.0f;
                         if constexpr (KIND == 1) WarmCall<M>::sample(m, x0, x1, x2); else ScanCall<M>::sample(m, x0, x1, x2);
                     }
+                } else if constexpr (ConstFillOf<M>::value) {
+                    painted_mask |= (run >= 32u ? 0xFFFFFFFFu : ((1u << run) - 1u)) << j;  // nothing else to do per frame
+                } else if (HasRunOf<M>::value && !careful) {
+                    // branch-free samples of a module with a run interface (no phase change of its own inside the run)
+                    painted = 1;
+                    if (kWriteOnly) painted_mask |= ((1u << run) - 1u) << j;
+                    RunCall<M>::begin(m);
+                    uint32_t r = 0;
+                    for (; r + 4 <= run; r += 4) {
+                        float acc[4], x0[4], x1[4], x2[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            acc[q] = kWriteOnly ? 0.0f : so[(r + q) * RV];
+                            x0[q] = i_in0 >= 0 ? s0[(r + q) * RV] : 0.0f;
+                            x1[q] = i_in1 >= 0 ? s1[(r + q) * RV] : 0.0f;
+                            x2[q] = i_in2 >= 0 ? s2[(r + q) * RV] : 0.0f;
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; q++) RunCall<M>::sample(m, acc[q], x0[q], x1[q], x2[q]);
+#pragma unroll
+                        for (int q = 0; q < 4; q++) so[(r + q) * RV] = acc[q];
+                    }
+                    for (; r < run; r++) {
+                        float acc = kWriteOnly ? 0.0f : so[r * RV];
+                        RunCall<M>::sample(m, acc, i_in0 >= 0 ? s0[r * RV] : 0.0f, i_in1 >= 0 ? s1[r * RV] : 0.0f, i_in2 >= 0 ? s2[r * RV] : 0.0f);
+                        so[r * RV] = acc;
+                    }
+                    RunCall<M>::end(m);
                 } else {
                     painted = 1;
                     if (kWriteOnly) painted_mask |= ((1u << run) - 1u) << j;
@@ -346,6 +398,24 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             // the tile holds only what was painted: full rows when every voice of the CTA painted every frame of the tile,
             // otherwise every voice stores its own frames (one coalesced 128-byte row piece per warp and frame)
             const bool full = !valid || painted_mask == (n >= 32 ? 0xFFFFFFFFu : (1u << n) - 1u);
+            if constexpr (ConstFillOf<M>::value) {
+                const float cv = ConstFillCall<M>::value(m);
+                if (__syncthreads_and(full)) {
+                    if (c_valid) {
+                        float* dstg = a.out + (size_t)f0 * V + v0 + c;
+                        if (vec4) {
+                            const float4 c4 = make_float4(cv, cv, cv, cv);
+                            for (uint32_t jj = r0; jj < n; jj += rpp) *reinterpret_cast<float4*>(dstg + (size_t)jj * V) = c4;
+                        } else {
+                            for (uint32_t jj = r0; jj < n; jj += rpp) dstg[(size_t)jj * V] = cv;
+                        }
+                    }
+                } else if (valid) {
+                    float* dstv = a.out + (size_t)f0 * V + v;
+                    for (uint32_t mk = painted_mask; mk != 0; mk &= mk - 1) dstv[(size_t)(__ffs(mk) - 1) * V] = cv;
+                }
+                return;
+            }
             if (__syncthreads_and(full)) {
                 if (c_valid) {
                     float* dstg = a.out + (size_t)f0 * V + v0 + c;
