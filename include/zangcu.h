@@ -594,6 +594,15 @@ int zcu_graph_set_gains(zcu_ctx*, zcu_graph*, const float* gains_host); /* MIX: 
 /* One launch paints the block: tables[num_span_tables] (all voices x frames of the buffers), outputs[num_outputs]
  * (MIX: outputs[0] is the [frames][channels] mix, accumulated), inputs[num_inputs]. */
 int zcu_graph_paint(zcu_ctx*, zcu_graph*, const zcu_spans* const* tables, zcu_buf* const* outputs, const zcu_buf* const* inputs);
+/* Time segments.  A graph whose modules can all skip ahead exactly from their own params (constant-frequency oscillators,
+ * Envelope, Gate, Portamento, Sampler, Distortion, Cycle; Decimator through its counter) is cut along the frame axis like
+ * the module paints are: every (128 voices x segment) CTA skips ahead in closed form, re-runs a short window before its
+ * start silently (where a Decimator re-latches its held value: the window is sized from its params rows) and then paints.
+ * Bit-identical to one segment.  zcu_graph_set_segments forces the count (0 = sized to the GPU, 1 = off);
+ * zcu_graph_segment_info reports the last paint's segmentation and, in *failed, whether any segment could not establish
+ * its start state since the last call (it synchronises; the painted block is then invalid). */
+int zcu_graph_set_segments(zcu_graph*, uint32_t segments);
+int zcu_graph_segment_info(zcu_ctx*, zcu_graph*, uint32_t* segments, uint32_t* segment_frames, uint32_t* replay_frames, uint32_t* failed);
 
 /* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
 /* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */

@@ -72,9 +72,11 @@ def test_sfx_graph(ctx, jobs, job_frames, block, device_spans):
     _same_states(_states(bank), _states(ref), "sfx")
 
 
-@pytest.mark.parametrize("voices,total,block,device_spans", [(40, 7 * 1024 + 100, 3 * 1024, False), (33, 4 * 1024, 4 * 1024, False),
-                                                             (40, 7 * 1024 + 100, 3 * 1024, True)])
-def test_sampler_graph(ctx, voices, total, block, device_spans):
+@pytest.mark.parametrize("voices,total,block,device_spans,segments", [(40, 7 * 1024 + 100, 3 * 1024, False, 1), (33, 4 * 1024, 4 * 1024, False, 0),
+                                                                      (40, 7 * 1024 + 100, 3 * 1024, True, 5), (70, 16 * 1024, 16 * 1024, False, 0)])
+def test_sampler_graph(ctx, voices, total, block, device_spans, segments):
+    """segments: time segments of the fused kernel (0 = sized to the GPU, 1 = off, n = forced): Sampler skips ahead in closed
+    form, the Decimator by its counter plus a silent replay window that re-latches its held value.  Same bits either way."""
     sr = 44100.0
     wl = synth.sampler_bank(voices, total, sr, seed=11, mean_gap=0.03)
     pcm = synth.pcm_loop(frames=3000, seed=3)
@@ -85,8 +87,13 @@ def test_sampler_graph(ctx, voices, total, block, device_spans):
     bank = banks.SamplerVoiceBank(ctx, wl, smp, sr, total)
     if device_spans:
         bank.use_device_spans(wl)
-    bank.build_graph()
+    g = bank.build_graph()
+    g.set_segments(segments)
     got = _render(ctx, bank, total, block, 2, fused=True)
+    info = g.segment_info()
+    assert info["failed"] == 0, info
+    if segments != 1:
+        assert info["segments"] > 1 and info["replay_frames"] >= 44100 // 6000 + 2, info
     assert np.abs(want).max() > 0.2
     assert_bit_exact(got, unfused, "sampler graph vs per-module path")
     assert_close(got, want, TRANSCENDENTAL_TOL, "sampler graph vs oracle (atanf per sample)")
@@ -179,6 +186,47 @@ def test_graph_arith_and_span_gaps(ctx):
             m = np.where(t0 > t1, t0, t1)
             want[s:e, v] = want[s:e, v] + (m + np.float32(0.5))
     assert_bit_exact(got, want, "arith graph")
+
+
+def test_graph_time_segments_of_a_skippable_instrument(ctx):
+    """PulseOsc (constant frequency) x Envelope with Trigger spans: every module has an exact skip-ahead, so the fused kernel is
+    cut in time.  Forced to 7 segments, sized to the GPU and uncut: identical bits, identical carried state."""
+    sr, V, total = 48000.0, 90, 11 * 1024 + 333
+    wl = synth.polyphony_bank(V, total, sr, seed=3, mean_on=0.05, mean_off=0.02)
+    from zang_b200.events import BankTrigger
+    off, spans = BankTrigger(wl["event_off"], wl["events"], total, 1024).spans(0, total)
+    ev = wl["events"]
+    pp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_PULSE_OSC])
+    pp["sample_rate"], pp["freq"], pp["color"] = sr, ev["freq"], 0.3
+    ep = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_ENVELOPE])
+    ep["sample_rate"], ep["attack"], ep["decay"], ep["release"] = sr, (L.CURVE_CUBED, 0.01), (L.CURVE_SQUARED, 0.05), (L.CURVE_LINEAR, 0.1)
+    ep["sustain_volume"], ep["note_on"] = 0.7, ev["note_on"]
+    results = []
+    for segments in (1, 7, 0):
+        b = E.GraphBuilder()
+        b.zero(E.T(0))
+        f_osc = b.call(L.MOD_PULSE_OSC, E.T(0))
+        b.zero(E.T(1))
+        f_env = b.call(L.MOD_ENVELOPE, E.T(1))
+        b.multiply(E.OUT(0), E.T(0), E.T(1))
+        g = E.Graph(ctx, E.graph_config(V, b, 2), b)
+        osc, env = E.PulseOsc(ctx, V), E.Envelope(ctx, V)
+        g.set_field(f_osc, osc.bank, pp)
+        g.set_field(f_env, env.bank, ep)
+        g.set_segments(segments)
+        out = ctx.buf(total, V)
+        ctx.zero(None, out)
+        sp = ctx.spans(V, total, off, spans)
+        g.paint([sp], [out])
+        info = g.segment_info()
+        assert info["failed"] == 0
+        assert (info["segments"] == 1) == (segments == 1), info
+        results.append((out.download(), osc.bank.get_state().tobytes(), env.bank.get_state().tobytes()))
+        g.free()
+    assert float(np.abs(results[0][0]).max()) > 0.1
+    for r in results[1:]:
+        assert_bit_exact(r[0], results[0][0], "segmented graph vs one segment")
+        assert r[1] == results[0][1] and r[2] == results[0][2], "carried state differs"
 
 
 def test_graph_rejects_bad_lists(ctx):

@@ -147,6 +147,8 @@ PROTOTYPES = {
     "zcu_graph_set_sample": (_I, [_P, _P, _U, _P]),
     "zcu_graph_set_gains": (_I, [_P, _P, _P]),
     "zcu_graph_paint": (_I, [_P, _P, _P, _P, _P]),
+    "zcu_graph_set_segments": (_I, [_P, _U]),
+    "zcu_graph_segment_info": (_I, [_P, _P, _P, _P, _P, _P]),
     "zcu_nccl_unique_id": (_I, [_P]),
     "zcu_nccl_init": (_I, [_P, _I, _I, _P]),
     "zcu_nccl_reduce_mix": (_I, [_P, _P, _I]),

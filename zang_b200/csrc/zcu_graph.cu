@@ -10,6 +10,7 @@
 //   in which every table is live on every lane (no predicates, unrolled x4), one predicated per table.
 #include <dlfcn.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -161,6 +162,7 @@ struct FieldInfo {
     uint32_t table = 0;
     bool used = false;
     bool has_run = false;  // the module offers run_limit / run_begin / sample_run / run_end (zcu_modules.cuh: HAS_RUN)
+    bool skippable = false;  // exact skip-ahead from its own params alone (advance()), or a Decimator (counter + replay window)
 };
 
 bool module_type(int kind, const zcu_graph_instr& in, std::string& type, std::string& err) {
@@ -212,7 +214,8 @@ bool module_type(int kind, const zcu_graph_instr& in, std::string& type, std::st
     return true;
 }
 
-bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, const int32_t* field_kinds, std::string& src, std::string& err) {
+bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, const int32_t* field_kinds, std::string& src, std::string& err,
+             bool* segmentable_out = nullptr) {
     auto fail = [&](uint32_t i, const char* what) {
         char b[256];
         snprintf(b, sizeof b, "instruction %u: %s", i, what);
@@ -264,6 +267,22 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             f.table = x.span_table;
             f.used = true;
             f.has_run = x.sub == ZCU_MOD_ENVELOPE || x.sub == ZCU_MOD_PORTAMENTO || x.sub == ZCU_MOD_CURVE;
+            {
+                const bool b0 = x.in[0].kind != ZCU_GREF_NONE, b1 = x.in[1].kind != ZCU_GREF_NONE;
+                switch (x.sub) {
+                    case ZCU_MOD_SINE_OSC: f.skippable = !b0 && !b1; break;  // buffer-driven phases are sequential by nature
+                    case ZCU_MOD_PULSE_OSC:
+                    case ZCU_MOD_TRISAW_OSC:
+                    case ZCU_MOD_CYCLE: f.skippable = !b0; break;
+                    case ZCU_MOD_ENVELOPE:
+                    case ZCU_MOD_GATE:
+                    case ZCU_MOD_PORTAMENTO:
+                    case ZCU_MOD_SAMPLER:
+                    case ZCU_MOD_DECIMATOR:
+                    case ZCU_MOD_DISTORTION: f.skippable = true; break;
+                    default: f.skippable = false; break;  // Filter, Curve, Noise, delays, FM oscillator: one segment
+                }
+            }
         } else if (x.op == ZCU_GI_BASIC) {
             if (x.sub < 0 || x.sub > 10) return fail(i, "unknown basic op");
             const bool na = x.sub == 2 || x.sub == 3 || x.sub == 4 || x.sub == 5 || x.sub == 7 || x.sub == 8 || x.sub == 9;
@@ -395,7 +414,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         return s;
     };
     // the per-sample body; live[k] = expression telling whether table k is live on this lane ("true" in the all-live copy)
-    auto body = [&](bool all_live, const char* ind, const char* row) {
+    auto body = [&](bool all_live, const char* ind, const char* row, bool emit = true) {
         std::string s;
         auto live = [&](uint32_t k) -> std::string {
             if (all_live) return "true";
@@ -410,11 +429,11 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                 if (mask >> k & 1u) e += (e.empty() ? "" : " || ") + live(k);
             return e.empty() ? "false" : e;
         };
-        if (!mix || c.num_inputs) appendf(s, "%sconst size_t idx = base + (size_t)%s * g.V;\n", ind, row);
+        if ((!mix && emit) || c.num_inputs) appendf(s, "%sconst size_t idx = base + (size_t)%s * g.V;\n", ind, row);
         for (uint32_t i = 0; i < c.num_inputs; i++)
             if (in_used[i]) appendf(s, "%sconst float x%u = valid ? __ldg(g.in[%u] + idx) : 0.0f;\n", ind, i, i);
         for (uint32_t o = 0; o < c.num_outputs; o++) {
-            if (mix)
+            if (mix || !emit)
                 appendf(s, "%sfloat o%u = 0.0f;\n", ind, o);
             else
                 appendf(s, "%sfloat o%u = (%s) ? g.out[%u][idx] : 0.0f;\n", ind, o, any_live(out_tables[o]).c_str(), o);
@@ -428,13 +447,20 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                 appendf(s, "%sif (a%u) { %s }\n", ind, x.span_table, stmt.c_str());
         }
         for (uint32_t o = 0; o < c.num_outputs; o++) {
-            if (mix)
+            if (!emit)
+                appendf(s, "%s(void)o%u;\n", ind, o);
+            else if (mix)
                 appendf(s, "%sO[j + %s][lane] = o%u;\n", ind, row, o);
             else
                 appendf(s, "%sif (%s) g.out[%u][idx] = o%u;\n", ind, any_live(out_tables[o]).c_str(), o, o);
         }
         return s;
     };
+
+    // time segments: every module must be able to skip ahead exactly from its own params (FieldInfo::skippable)
+    bool segmentable = c.num_fields > 0;
+    for (uint32_t f = 0; f < c.num_fields; f++) segmentable = segmentable && fields[f].skippable;
+    if (segmentable_out) *segmentable_out = segmentable;
 
     src.clear();
     src += "// generated by libzangcu (zcu_graph.cu) from a zcu_graph_instr list\n#include \"zcu_graph_rt.cuh\"\nusing namespace zcu;\n\n";
@@ -452,7 +478,6 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         src += "    for (int c = 0; c < C; c++) gn[c][lane] = valid ? g.gains[(size_t)v * C + c] : 0.0f;\n";
         src += "    __syncwarp();\n";
         src += "    const uint32_t gwarp = blockIdx.x * 4u + warp;\n";
-        src += "    uint32_t j = 0, T0 = 0;\n";
     }
     for (uint32_t k = 0; k < K; k++) appendf(src, "    SpanCursor c%u;\n    c%u.init(g.tab[%u], v, valid);\n", k, k, k);
     for (uint32_t f = 0; f < c.num_fields; f++) appendf(src, "    %s m%u;\n", fields[f].type.c_str(), f);
@@ -460,8 +485,47 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     for (uint32_t f = 0; f < c.num_fields; f++) appendf(src, "        m%u.load(g.pa[%u], v);\n", f, f);
     src += "    }\n";
     for (uint32_t t = 0; t < c.num_temps; t++) appendf(src, "    float t%u = 0.0f;\n", t);
-    src += "    uint32_t f = 0;\n";
-    src += "    while (f < g.frames) {\n";
+    if (segmentable) {
+        // this CTA's segment of the frame axis; the modules skip ahead to F_play (closed forms), the frames [F_play, F_begin)
+        // are then run silently (a Decimator re-latches its held value there), [F_begin, F_end) are painted
+        src += "    const uint32_t F_begin = blockIdx.y * g.seg_frames;\n";
+        src += "    if (F_begin >= g.frames) return;\n";
+        src += "    const uint32_t F_end = min(g.frames, F_begin + g.seg_frames);\n";
+        src += "    const uint32_t F_play = F_begin > g.replay ? F_begin - g.replay : 0u;\n";
+        src += "    if (F_play > 0 && valid) {\n";
+        for (uint32_t k = 0; k < K; k++) {
+            appendf(src, "        while (c%u.s_end <= F_play) {\n", k);
+            for (uint32_t f = 0; f < c.num_fields; f++)
+                if (fields[f].table == k)
+                    appendf(src, "            m%u.begin_span(g.pa[%u], c%u.s_param, c%u.s_flags, c%u.s_end - c%u.s_start);\n"
+                                 "            m%u.advance(g.pa[%u], v, c%u.s_start, c%u.s_end - c%u.s_start);\n            m%u.end_span(g.pa[%u]);\n",
+                            f, f, k, k, k, k, f, f, k, k, k, f, f);
+            appendf(src, "            c%u.next(g.tab[%u]);\n        }\n", k, k);
+            appendf(src, "        if (c%u.s_start < F_play) {\n", k);
+            for (uint32_t f = 0; f < c.num_fields; f++)
+                if (fields[f].table == k)
+                    appendf(src, "            m%u.begin_span(g.pa[%u], c%u.s_param, c%u.s_flags, c%u.s_end - c%u.s_start);\n"
+                                 "            m%u.advance(g.pa[%u], v, c%u.s_start, F_play - c%u.s_start);\n",
+                            f, f, k, k, k, k, f, f, k, k);
+            appendf(src, "            c%u.active = true;\n        }\n", k);
+        }
+        src += "    }\n";
+    } else {
+        src += "    const uint32_t F_begin = 0, F_end = g.frames, F_play = 0;\n    (void)F_begin;\n";
+    }
+    if (mix) src += "    uint32_t j = 0, T0 = F_begin;\n";
+    src += "    uint32_t f = F_play;\n";
+    src += "    while (f < F_end) {\n";
+    if (segmentable) {
+        bool any_dec = false;
+        for (uint32_t f = 0; f < c.num_fields; f++) any_dec = any_dec || fields[f].kind == ZCU_MOD_DECIMATOR;
+        if (any_dec) {
+            src += "        if (f == F_begin && F_begin > 0 && valid) {  // the replay window must have re-latched every Decimator\n";
+            for (uint32_t f = 0; f < c.num_fields; f++)
+                if (fields[f].kind == ZCU_MOD_DECIMATOR) appendf(src, "            if (m%u.dval_unknown && g.err) atomicExch(g.err, 1u);\n", f);
+            src += "        }\n";
+        }
+    }
     for (uint32_t k = 0; k < K; k++) {
         appendf(src, "        if (c%u.active && f == c%u.s_end) {\n", k, k);
         for (uint32_t f = 0; f < c.num_fields; f++)
@@ -475,7 +539,9 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     }
     src += "        uint32_t dist = c0.boundary() - f;\n";
     for (uint32_t k = 1; k < K; k++) appendf(src, "        dist = min(dist, c%u.boundary() - f);\n", k);
-    if (mix) src += "        dist = min(dist, (uint32_t)kMixTileFrames - j);\n";
+    src += "        const bool silent = f < F_begin;  // warp-uniform\n";
+    src += "        const uint32_t limit = silent ? F_begin : F_end;\n";
+    if (mix) src += "        if (!silent) dist = min(dist, (uint32_t)kMixTileFrames - j);\n";
     // modules with a run interface: no phase change of theirs inside a run (painter_safe_run's margin covers 256 samples);
     // a module that cannot promise a single sample sends the whole warp through the general per-sample path for one frame
     bool any_run = false;
@@ -488,7 +554,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                 appendf(src, "        if (c%u.active) {\n            const uint32_t s = m%u.run_limit();\n            careful = careful || s == 0u;\n"
                              "            dist = min(dist, s == 0u ? 1u : s);\n        }\n", fields[f].table, f);
     }
-    src += "        const uint32_t run = min(g.frames - f, __reduce_min_sync(FULL, dist));\n";
+    src += "        const uint32_t run = min(limit - f, __reduce_min_sync(FULL, dist));\n";
     std::string all = "", any = "";
     for (uint32_t k = 0; k < K; k++) {
         appendf(src, "        const bool a%u = c%u.active;\n", k, k);
@@ -503,6 +569,11 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     // ... or live on some lanes and dead on all the others (voices that have not started yet, the tail of a partial warp):
     // the dead lanes sit the run out
     appendf(src, "        const bool lane_live = %s;\n        const bool lane_idle = !(%s);\n", all.c_str(), any.c_str());
+    if (segmentable) {
+        src += "        if (silent) {\n            for (uint32_t r = 0; r < run; r++) {\n";
+        src += body(false, "                ", "r", false);
+        src += "            }\n        } else\n";
+    }
     src += "        if (__all_sync(FULL, (lane_live && !careful) || lane_idle) && __any_sync(FULL, lane_live)) {\n";
     src += "          if (lane_live) {\n";
     for (uint32_t f = 0; f < c.num_fields; f++)
@@ -540,15 +611,15 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     src += "            }\n        }\n";
     src += "        f += run;\n";
     if (mix) {
-        src += "        j += run;\n";
-        src += "        if (j == (uint32_t)kMixTileFrames || f == g.frames) {\n";
+        src += "        if (!silent) j += run;\n";
+        src += "        if (j == (uint32_t)kMixTileFrames || (f == F_end && j > 0)) {\n";
         src += "            __syncwarp();\n";
         src += "            mix_tile_store<C>(O, gn, j, g.partial + ((size_t)gwarp * g.frames + T0) * C, lane);\n";
         src += "            __syncwarp();\n";
         src += "            T0 += j;\n            j = 0;\n        }\n";
     }
     src += "    }\n";
-    src += "    if (!valid) return;\n";
+    src += "    if (!valid || F_end < g.frames) return;  // only the last segment carries the state out\n";
     for (uint32_t k = 0; k < K; k++) {
         appendf(src, "    if (c%u.active) {\n", k);
         for (uint32_t f = 0; f < c.num_fields; f++)
@@ -600,11 +671,19 @@ struct zcu_graph {
         void* d_nodes = nullptr;
         uint32_t nnodes = 0;
         const zcu_sample* sample = nullptr;
+        uint32_t replay = 0;     // frames a segment must re-run before its start to re-establish this module's state
+        bool seg_ok = true;      // false: these params rule time segments out
     };
     std::vector<Field> fields;
     float* d_gains = nullptr;
     float* d_partial = nullptr;
     size_t partial_bytes = 0;
+    // time segments
+    bool segmentable = false;     // every module can skip ahead exactly (codegen)
+    uint32_t forced_nseg = 0;     // zcu_graph_set_segments: 0 = sized to the GPU
+    int resident_per_sm = 0;      // occupancy of the compiled kernel
+    uint32_t last_nseg = 1, last_seg_frames = 0, last_replay = 0;
+    uint32_t* d_err = nullptr;
 };
 
 void zcu_launch_partial_reduce(zcu_ctx* ctx, const float* partial, float* mix, uint32_t nwarps, size_t n);  // zcu_render.cu
@@ -640,7 +719,9 @@ int zcu_graph_create(zcu_ctx* ctx, const zcu_graph_config* cfg, const zcu_graph_
     *out = nullptr;
     ZCU_REQUIRE(ctx, cfg != nullptr, "null config");
     std::string src, err;
-    if (!codegen(*cfg, instrs, num_instrs, field_kinds, src, err)) return zcu_fail(ctx, ZCU_ERR_INVALID, "zcu_graph_create: %s", err.c_str());
+    bool segmentable = false;
+    if (!codegen(*cfg, instrs, num_instrs, field_kinds, src, err, &segmentable))
+        return zcu_fail(ctx, ZCU_ERR_INVALID, "zcu_graph_create: %s", err.c_str());
     std::vector<char> cubin;
     if (!nvrtc_compile(src, cubin, err)) return zcu_fail(ctx, ZCU_ERR_UNSUPPORTED, "zcu_graph_create: NVRTC: %s", err.c_str());
     zcu_graph* g = new zcu_graph;
@@ -648,6 +729,7 @@ int zcu_graph_create(zcu_ctx* ctx, const zcu_graph_config* cfg, const zcu_graph_
     g->cfg = *cfg;
     g->kinds.assign(field_kinds, field_kinds + cfg->num_fields);
     g->source = src;
+    g->segmentable = segmentable;
     g->fields.resize(cfg->num_fields);
     cudaError_t e = cudaLibraryLoadData(&g->lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
     if (e == cudaSuccess) e = cudaLibraryGetKernel(&g->kernel, g->lib, "zcu_graph_kernel");
@@ -663,7 +745,40 @@ int zcu_graph_create(zcu_ctx* ctx, const zcu_graph_config* cfg, const zcu_graph_
             return zcu_fail(ctx, ZCU_ERR_CUDA, "zcu_graph_create: shared-memory attribute: %s", cudaGetErrorString(e));
         }
     }
+    if (segmentable) {
+        if (cudaMalloc((void**)&g->d_err, sizeof(uint32_t)) != cudaSuccess || cudaMemsetAsync(g->d_err, 0, sizeof(uint32_t), ctx->stream) != cudaSuccess) {
+            zcu_graph_free(g);
+            return zcu_fail(ctx, ZCU_ERR_OOM, "zcu_graph_create: status word allocation failed");
+        }
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g->resident_per_sm, (const void*)g->kernel, 128, g->smem) != cudaSuccess || g->resident_per_sm < 1) {
+            cudaGetLastError();
+            g->resident_per_sm = 4;
+        }
+    }
     *out = g;
+    return ZCU_OK;
+}
+
+int zcu_graph_set_segments(zcu_graph* g, uint32_t segments) {
+    if (!g) return ZCU_ERR_INVALID;
+    g->forced_nseg = segments;
+    return ZCU_OK;
+}
+
+int zcu_graph_segment_info(zcu_ctx* ctx, zcu_graph* g, uint32_t* segments, uint32_t* segment_frames, uint32_t* replay_frames, uint32_t* failed) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, g != nullptr, "null graph");
+    if (segments) *segments = g->last_nseg;
+    if (segment_frames) *segment_frames = g->last_seg_frames;
+    if (replay_frames) *replay_frames = g->last_replay;
+    if (failed) {
+        *failed = 0;
+        if (g->d_err) {
+            ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            ZCU_CUDA(ctx, cudaMemcpy(failed, g->d_err, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+            ZCU_CUDA(ctx, cudaMemset(g->d_err, 0, sizeof(uint32_t)));
+        }
+    }
     return ZCU_OK;
 }
 
@@ -676,6 +791,7 @@ void zcu_graph_free(zcu_graph* g) {
     }
     if (g->d_gains) cudaFree(g->d_gains);
     if (g->d_partial) cudaFree(g->d_partial);
+    if (g->d_err) cudaFree(g->d_err);
     if (g->lib) cudaLibraryUnload(g->lib);
     delete g;
 }
@@ -702,6 +818,26 @@ int zcu_graph_set_field(zcu_ctx* ctx, zcu_graph* g, uint32_t field, zcu_bank* ba
     }
     ZCU_REQUIRE(ctx, params_host != nullptr && nparams > 0, "params required");
     ZCU_REQUIRE(ctx, row_bytes == params_row_bytes(kind), "row_bytes is not the sizeof of this module's params struct");
+    f.replay = 0;
+    f.seg_ok = true;
+    if (kind == ZCU_MOD_DECIMATOR) {
+        // a time segment re-latches the held value by running the frames before its start again: the window must hold a
+        // latch for every row (Decimator.zig:40-55: one latch per 1/ratio samples); a row that paints nothing (fake rate <= 0)
+        // leaves a value of unbounded age behind, so it rules segments out
+        const zcu_decimator_params* p = (const zcu_decimator_params*)params_host;
+        for (uint32_t i = 0; i < nparams; i++) {
+            if (!(p[i].fake_sample_rate > 0.0f)) {
+                f.seg_ok = false;
+            } else if (p[i].fake_sample_rate < p[i].sample_rate) {
+                const float ratio = p[i].fake_sample_rate / p[i].sample_rate;
+                const double need = std::ceil(1.0 / (double)ratio) + 2.0;
+                if (need > 65536.0)
+                    f.seg_ok = false;
+                else
+                    f.replay = std::max(f.replay, (uint32_t)need);
+            }
+        }
+    }
     std::vector<DistortionDerived> derived;
     const void* src = params_host;
     size_t bytes = row_bytes * nparams;
@@ -841,8 +977,31 @@ int zcu_graph_paint(zcu_ctx* ctx, zcu_graph* g, const zcu_spans* const* tables, 
         a.C = c.channels;
         a.out[0] = nullptr;
     }
+    // time segments: as many as fill the resident CTAs once (each at least 512 frames, a multiple of the mix tile)
+    uint32_t nseg = 1, seg_frames = frames, replay = 0;
+    if (g->segmentable) {
+        bool ok = true;
+        for (const auto& fd : g->fields) {
+            ok = ok && fd.seg_ok;
+            replay = std::max(replay, fd.replay);
+        }
+        if (ok) {
+            nseg = g->forced_nseg ? g->forced_nseg : std::max(1u, (uint32_t)g->resident_per_sm * (uint32_t)ctx->sm_count / grid);
+            seg_frames = (frames + nseg - 1) / nseg;
+            if (!g->forced_nseg) seg_frames = std::max(seg_frames, std::min(frames, 512u));
+            seg_frames = std::max(seg_frames, replay + 1);
+            seg_frames = (seg_frames + kMixTileFrames - 1) / kMixTileFrames * kMixTileFrames;
+            nseg = (frames + seg_frames - 1) / seg_frames;
+        }
+    }
+    a.seg_frames = seg_frames;
+    a.replay = replay;
+    a.err = g->d_err;
+    g->last_nseg = nseg;
+    g->last_seg_frames = seg_frames;
+    g->last_replay = replay;
     void* args[] = {&a};
-    ZCU_CUDA(ctx, cudaLaunchKernel((const void*)g->kernel, dim3(grid), dim3(128), args, g->smem, ctx->stream));
+    ZCU_CUDA(ctx, cudaLaunchKernel((const void*)g->kernel, dim3(grid, nseg), dim3(128), args, g->smem, ctx->stream));
     ctx->launches++;
     if (mix) zcu_launch_partial_reduce(ctx, g->d_partial, outputs[0]->d, grid * 4, (size_t)frames * c.channels);
     ZCU_CUDA(ctx, cudaGetLastError());

@@ -33,6 +33,11 @@ struct GraphArgs {
     const float* gains;  // [V][C]
     uint32_t C;
     uint32_t nfields;
+    // time segments (graphs whose modules all have an exact skip-ahead): blockIdx.y = segment of seg_frames frames; a segment
+    // skips ahead to `replay` frames before its start, runs those frames silently (a Decimator re-latches its held value
+    // there) and then paints.  err is set when a segment could not establish its start state.
+    uint32_t seg_frames, replay;
+    uint32_t* err;
     PaintArgs pa[kGraphMaxFields];
 };
 

@@ -835,6 +835,16 @@ class Graph:
         ins = (C.c_void_p * max(1, len(inputs)))(*[i._h for i in inputs])
         _check(self.ctx, lib.zcu_graph_paint(self.ctx._h, self._h, tabs, outs, ins if len(inputs) else None))
 
+    def set_segments(self, n):
+        """time segments of the next paints: 0 = sized to the GPU (default), 1 = off"""
+        assert lib.zcu_graph_set_segments(self._h, int(n)) == L.OK
+
+    def segment_info(self):
+        """dict(segments, segment_frames, replay_frames, failed) of the last paint; synchronises"""
+        v = [C.c_uint32() for _ in range(4)]
+        _check(self.ctx, lib.zcu_graph_segment_info(self.ctx._h, self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("segments", "segment_frames", "replay_frames", "failed"), (x.value for x in v)))
+
     def free(self):
         if self._h:
             lib.zcu_graph_free(self._h)
