@@ -297,3 +297,55 @@ pub const Trigger = struct {
         return c.zcu_trigger_run(&self.t, start, end, impulses.ptr, rows.ptr, @intCast(impulses.len), frame_base, out.ptr, @intCast(out.len));
     }
 };
+
+// ---- round 2: device-side Trigger, fused graphs, overwrite mode (INTEGRATION.md §6) -------------------------------------
+
+/// ImpulseQueue + Trigger of every voice of a bank replayed on the GPU (examples/example_polyphony.zig:61-92 per voice).
+pub const EventBank = struct {
+    ctx: Context,
+    h: *c.zcu_event_bank,
+
+    pub fn init(ctx: Context, event_off: []const u32, events: []const c.zcu_note_event, buffer_frames: u32, total_frames: u32) !EventBank {
+        var h: ?*c.zcu_event_bank = null;
+        try check(c.zcu_event_bank_create(ctx.h, @intCast(event_off.len - 1), event_off.ptr, events.ptr, buffer_frames, total_frames, &h));
+        return .{ .ctx = ctx, .h = h.? };
+    }
+    pub fn deinit(self: *EventBank) void {
+        c.zcu_event_bank_free(self.h);
+    }
+    /// span table of the block, built on the device; the Trigger state is carried to the next call
+    pub fn spans(self: *EventBank, first_frame: u32, num_frames: u32) !*c.zcu_spans {
+        var s: ?*c.zcu_spans = null;
+        try check(c.zcu_event_bank_spans(self.ctx.h, self.h, first_frame, num_frames, &s));
+        return s.?;
+    }
+};
+
+/// `zang.zero(span, out); module.paint(span, .{out}, ...)` as ONE call for everything painted inside `body`.
+pub fn overwriting(ctx: Context, body: anytype) !void {
+    try check(c.zcu_ctx_set_paint_output(ctx.h, c.ZCU_OUT_OVERWRITE));
+    defer _ = c.zcu_ctx_set_paint_output(ctx.h, c.ZCU_OUT_ACCUMULATE);
+    try body.run();
+}
+
+/// One fused kernel for an instrument body / a script module's instruction list (src/zangscript/codegen.zig:60-121).
+pub const Graph = struct {
+    ctx: Context,
+    h: *c.zcu_graph,
+
+    pub fn init(ctx: Context, cfg: c.zcu_graph_config, instrs: []const c.zcu_graph_instr, field_kinds: []const i32) !Graph {
+        var h: ?*c.zcu_graph = null;
+        try check(c.zcu_graph_create(ctx.h, &cfg, instrs.ptr, @intCast(instrs.len), field_kinds.ptr, &h));
+        return .{ .ctx = ctx, .h = h.? };
+    }
+    pub fn deinit(self: *Graph) void {
+        c.zcu_graph_free(self.h);
+    }
+    /// rows: a slice of the field's `zcu_<module>_params`
+    pub fn setField(self: *Graph, field: u32, bank: ?*c.zcu_bank, rows: anytype) !void {
+        try check(c.zcu_graph_set_field(self.ctx.h, self.h, field, bank, rows.ptr, @sizeOf(@TypeOf(rows[0])), @intCast(rows.len)));
+    }
+    pub fn paint(self: *Graph, tables: []const ?*const c.zcu_spans, outputs: []const ?*c.zcu_buf, inputs: []const ?*const c.zcu_buf) !void {
+        try check(c.zcu_graph_paint(self.ctx.h, self.h, tables.ptr, outputs.ptr, if (inputs.len > 0) inputs.ptr else null));
+    }
+};
