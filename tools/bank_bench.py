@@ -92,6 +92,23 @@ def run_fused(ctx, name, bank, frames, bytes_per_vs, peak, ins=(), reps=3, gains
         res[mname] = dict(ms=best, voice_samples_per_s=vs, graph_build_s=t_build, equivalent_algorithmic_gbs=vs * bytes_per_vs / 1e9,
                           equivalent_frac_of_peak=vs * bytes_per_vs / 1e9 / peak)
         print(f"{name:34s} {mname:14s} {best:9.3f} ms  {vs:10.3e} vs/s  (graph build {t_build:5.2f} s; un-fused-equivalent {vs * bytes_per_vs / 1e9:8.1f} GB/s)", flush=True)
+        if mode == L.GRAPH_OUT_MIX and wl is not None:
+            # end to end for one block, wall clock: device-side Trigger replay -> fused kernel -> partial reduce -> D2H of the mix
+            e2e = 1e30
+            for rep in range(3):
+                bank.dev_trigger.reset()
+                ctx.zero(None, out)
+                ctx.sync()
+                t0 = time.perf_counter()
+                tabs = bank.prepare_block(0, frames)
+                bank.paint_block_fused(0, frames, out, *ins, prepared=tabs)
+                host_mix = out.download()
+                e2e = min(e2e, time.perf_counter() - t0)
+                for t in tabs:
+                    t.free()
+            res[mname]["e2e_block_ms_wall"] = e2e * 1e3
+            res[mname]["e2e_d2h_bytes"] = int(host_mix.nbytes)
+            print(f"{name:34s} end to end (device spans -> fused kernel -> mix D2H, wall clock): {e2e * 1e3:8.3f} ms", flush=True)
         out.free()
         bank.graph.free()
     for b in prepared:
