@@ -595,7 +595,7 @@ int zcu_graph_set_gains(zcu_ctx*, zcu_graph*, const float* gains_host); /* MIX: 
  * (MIX: outputs[0] is the [frames][channels] mix, accumulated), inputs[num_inputs]. */
 int zcu_graph_paint(zcu_ctx*, zcu_graph*, const zcu_spans* const* tables, zcu_buf* const* outputs, const zcu_buf* const* inputs);
 /* Time segments.  A graph whose modules can all skip ahead exactly from their own params (constant-frequency oscillators,
- * Envelope, Gate, Portamento, Sampler, Distortion, Cycle; Decimator through its counter) is cut along the frame axis like
+ * Envelope, Gate, Portamento, Curve, Noise, Sampler, Distortion, Cycle; Decimator through its counter) is cut along the frame axis like
  * the module paints are: every (128 voices x segment) CTA skips ahead in closed form, re-runs a short window before its
  * start silently (where a Decimator re-latches its held value: the window is sized from its params rows) and then paints.
  * Bit-identical to one segment.  zcu_graph_set_segments forces the count (0 = sized to the GPU, 1 = off);

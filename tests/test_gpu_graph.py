@@ -209,10 +209,24 @@ def test_graph_time_segments_of_a_skippable_instrument(ctx):
         b.zero(E.T(1))
         f_env = b.call(L.MOD_ENVELOPE, E.T(1))
         b.multiply(E.OUT(0), E.T(0), E.T(1))
+        b.zero(E.T(0))
+        f_cur = b.call(L.MOD_CURVE, E.T(0))  # skip-ahead: begin_span per earlier call, exact running x / y inside the straddling one
+        b.addInto(E.OUT(0), E.T(0))
+        b.zero(E.T(1))
+        f_noi = b.call(L.MOD_NOISE, E.T(1))  # skip-ahead: the exact GF(2) jump of xoshiro256, pink spans replayed from their start
+        b.multiplyScalar(E.OUT(0), E.T(1), 0.125)
         g = E.Graph(ctx, E.graph_config(V, b, 2), b)
-        osc, env = E.PulseOsc(ctx, V), E.Envelope(ctx, V)
+        osc, env, cur, noi = E.PulseOsc(ctx, V), E.Envelope(ctx, V), E.Curve(ctx, V), E.Noise(ctx, V, first_seed=11)
+        npar = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_NOISE])
+        npar["color"] = (np.arange(ev.size) // 2) % 2  # white and pink rows
+        g.set_field(f_noi, noi.bank, npar)
         g.set_field(f_osc, osc.bank, pp)
         g.set_field(f_env, env.bank, ep)
+        cp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_CURVE])
+        cp["sample_rate"], cp["node_count"] = sr, 4
+        cp["function"] = np.arange(ev.size) % 2  # linear and smoothstep rows
+        g.set_field(f_cur, cur.bank, cp)
+        g.set_curve_nodes(f_cur, np.array([(0.0, 0.0), (0.5, 0.013), (-0.3, 0.031), (0.2, 0.09)], dtype=L.curve_node_dtype))
         g.set_segments(segments)
         out = ctx.buf(total, V)
         ctx.zero(None, out)
@@ -221,7 +235,7 @@ def test_graph_time_segments_of_a_skippable_instrument(ctx):
         info = g.segment_info()
         assert info["failed"] == 0
         assert (info["segments"] == 1) == (segments == 1), info
-        results.append((out.download(), osc.bank.get_state().tobytes(), env.bank.get_state().tobytes()))
+        results.append((out.download(), osc.bank.get_state().tobytes(), env.bank.get_state().tobytes() + cur.bank.get_state().tobytes() + noi.bank.get_state().tobytes()))
         g.free()
     assert float(np.abs(results[0][0]).max()) > 0.1
     for r in results[1:]:

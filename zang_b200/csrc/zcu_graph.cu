@@ -279,8 +279,10 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                     case ZCU_MOD_PORTAMENTO:
                     case ZCU_MOD_SAMPLER:
                     case ZCU_MOD_DECIMATOR:
+                    case ZCU_MOD_NOISE:  // exact GF(2) jump (zcu_modules.cuh), applied once after the walk
+                    case ZCU_MOD_CURVE:
                     case ZCU_MOD_DISTORTION: f.skippable = true; break;
-                    default: f.skippable = false; break;  // Filter, Curve, Noise, delays, FM oscillator: one segment
+                    default: f.skippable = false; break;  // Filter, delays, FM oscillator: one segment
                 }
             }
         } else if (x.op == ZCU_GI_BASIC) {
@@ -509,6 +511,8 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                             f, f, k, k, k, k, f, f, k, k);
             appendf(src, "            c%u.active = true;\n        }\n", k);
         }
+        for (uint32_t f = 0; f < c.num_fields; f++)
+            if (fields[f].kind == ZCU_MOD_NOISE) appendf(src, "        m%u.advance_done();  // the draws skipped so far, as one jump\n", f);
         src += "    }\n";
     } else {
         src += "    const uint32_t F_begin = 0, F_end = g.frames, F_play = 0;\n    (void)F_begin;\n";
@@ -984,6 +988,20 @@ int zcu_graph_paint(zcu_ctx* ctx, zcu_graph* g, const zcu_spans* const* tables, 
         for (const auto& fd : g->fields) {
             ok = ok && fd.seg_ok;
             replay = std::max(replay, fd.replay);
+        }
+        bool has_noise = false;
+        for (uint32_t f = 0; f < c.num_fields; f++) has_noise = has_noise || g->kinds[f] == ZCU_MOD_NOISE;
+        if (has_noise) {  // jumps are tabulated for fewer than 16^6 draws per call
+            ok = ok && frames < (1u << 24);
+            if (ok) {
+                int rc = zcu_ensure_xjump(ctx);
+                if (rc) return rc;
+                for (uint32_t f = 0; f < c.num_fields; f++)
+                    if (g->kinds[f] == ZCU_MOD_NOISE) {
+                        a.pa[f].xjump = (const ulonglong2*)ctx->xjump;
+                        a.pa[f].xjump_resync = ctx->xjump_resync;
+                    }
+            }
         }
         if (ok) {
             nseg = g->forced_nseg ? g->forced_nseg : std::max(1u, (uint32_t)g->resident_per_sm * (uint32_t)ctx->sm_count / grid);

@@ -138,3 +138,4 @@ int zcu_launch_basic(zcu_ctx* ctx, int op, const zcu_spans* spans, zcu_buf* dest
 int zcu_launch_basic_rows(zcu_ctx* ctx, int op, const zcu_spans* spans, zcu_buf* dest, const zcu_buf* a, const float* rows, uint32_t nrows);
 int zcu_launch_bank_init(zcu_ctx* ctx, zcu_bank* bank, uint32_t first_seed);
 int zcu_selftest_no_fma(zcu_ctx* ctx);
+int zcu_ensure_xjump(zcu_ctx* ctx);  // xoshiro256 jump matrices of the Noise skip-ahead (ctx->xjump, ctx->xjump_resync)

@@ -98,6 +98,9 @@ int ensure_xjump(zcu_ctx* ctx) {
 
 }  // namespace
 
+// the jump tables, for other translation units (fused graphs with a Noise field in time segments)
+int zcu_ensure_xjump(zcu_ctx* ctx) { return ensure_xjump(ctx); }
+
 // Host-only check of the jump table (no device needed): state <- T^n state, exactly as NoiseMod::advance_done applies it.
 extern "C" int zcu_xoshiro_jump_host(uint64_t state[4], uint32_t n) {
     if (!state || n >= (1u << (4 * kJumpLevels))) return ZCU_ERR_INVALID;
