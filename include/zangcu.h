@@ -541,7 +541,13 @@ typedef struct zcu_graph_ref {
     uint32_t index;
 } zcu_graph_ref;
 
-enum { ZCU_GI_BASIC = 0, ZCU_GI_ARITH = 1, ZCU_GI_CALL = 2 };
+enum { ZCU_GI_BASIC = 0, ZCU_GI_ARITH = 1, ZCU_GI_CALL = 2,
+       /* the script runtime's `delay` block (codegen.zig:97-103, runtime.zig:704-721) in its per-sample form: DELAY_READ is
+        * `zero(feedback_temp); delay.readDelayBuffer(feedback_temp)` (out = 0 + the delayed sample, delay.zig:28-56), DELAY_WRITE
+        * is `delay.writeDelayBuffer(feedback_out_temp)` (in[0] goes into the same slot, the line advances, delay.zig:63-90);
+        * the block's inner instructions sit between the two.  field = a ZCU_MOD_SIMPLE_DELAY bank (zcu_delay_bank_create: the
+        * line and its index, i.e. zang.Delay(N)); both instructions name the same field and span table. */
+       ZCU_GI_DELAY_READ = 3, ZCU_GI_DELAY_WRITE = 4 };
 /* basics.zig:12-78, as zcu_zero .. zcu_multiply_with_scalar */
 enum {
     ZCU_BASIC_ZERO = 0, ZCU_BASIC_SET = 1, ZCU_BASIC_COPY = 2, ZCU_BASIC_ADD = 3, ZCU_BASIC_ADD_INTO = 4, ZCU_BASIC_ADD_SCALAR = 5,
@@ -549,12 +555,14 @@ enum {
     ZCU_BASIC_MULTIPLY_WITH_SCALAR = 10
 };
 /* the script runtime's arithmetic that OVERWRITES its output (runtime.zig:528-700; add and mul are basics there) */
-enum { ZCU_ARITH_SUB = 0, ZCU_ARITH_DIV = 1, ZCU_ARITH_MIN = 2, ZCU_ARITH_MAX = 3, ZCU_ARITH_NEG = 4, ZCU_ARITH_ABS = 5, ZCU_ARITH_SQRT = 6 };
+enum { ZCU_ARITH_SUB = 0, ZCU_ARITH_DIV = 1, ZCU_ARITH_MIN = 2, ZCU_ARITH_MAX = 3, ZCU_ARITH_NEG = 4, ZCU_ARITH_ABS = 5, ZCU_ARITH_SQRT = 6,
+       /* libm per sample (CUDA sinf / cosf / powf; the reference's are Zig std's: parity within the tolerance of SineOsc) */
+       ZCU_ARITH_SIN = 7, ZCU_ARITH_COS = 8, ZCU_ARITH_POW = 9 };
 enum { ZCU_SCALAR_NONE = 0, ZCU_SCALAR_A = 1, ZCU_SCALAR_B = 2 };
 
 typedef struct zcu_graph_instr {
     int32_t op;             /* ZCU_GI_* */
-    int32_t sub;            /* BASIC: ZCU_BASIC_*   ARITH: ZCU_ARITH_*   CALL: ZCU_MOD_* */
+    int32_t sub;            /* BASIC: ZCU_BASIC_*   ARITH: ZCU_ARITH_*   CALL: ZCU_MOD_*   DELAY_*: unused */
     zcu_graph_ref out;      /* TEMP or OUTPUT */
     zcu_graph_ref in[3];    /* BASIC / ARITH: a, b.  CALL: the buffer arguments of zcu_paint_<module> in its order (SineOsc: freq,
                                phase; Filter: input, cutoff, res; ...); NONE = the scalar of the params row is used */

@@ -252,3 +252,75 @@ def test_graph_rejects_bad_lists(ctx):
     b.zero(E.T(3))  # temp out of range
     with pytest.raises(E.ZangCuError):
         E.Graph(ctx, E.graph_config(8, b, 1), b)
+
+
+@pytest.mark.parametrize("D", [1, 7, 300])
+def test_graph_delay_instructions_equal_simple_delay_and_the_oracle(ctx, D):
+    """The script runtime's `delay` block (runtime.zig:704-721) as DELAY_READ / DELAY_WRITE: with the block's body
+    `out += feedback_temp; feedback_out = input` it is SimpleDelay.paint (examples/modules.zig:362-386).  Random spans with gaps
+    (the line only advances on painted frames), two blocks with the line and its index carried: output, index and line
+    bit-exact against the oracle restatement of src/zang/delay.zig."""
+    from helpers import random_spans, state_equal
+    V, frames = 70, 3 * 512
+    rng = np.random.default_rng(D)
+    b = E.GraphBuilder()
+    fd = b.delay_field()
+    b.delay_read(fd, E.T(0))
+    b.addInto(E.OUT(0), E.T(0))
+    b.delay_write(fd, E.IN(0))
+    g = E.Graph(ctx, E.graph_config(V, b, 1, num_inputs=1), b)
+    bank = E.DelayBank(ctx, L.MOD_SIMPLE_DELAY, V, D)
+    g.set_field(fd, bank, None)
+    ostate = np.zeros(V, dtype=L.state_dtypes[L.MOD_SIMPLE_DELAY])
+    oline = np.zeros((D, V), dtype=np.float32)
+    for block in range(2):
+        off, spans = random_spans(rng, V, 3, 512, 1)
+        out0 = rng.uniform(-1, 1, size=(frames, V)).astype(np.float32)
+        x = rng.uniform(-1, 1, size=(frames, V)).astype(np.float32)
+        want = out0.copy()
+        oracle.paint_delay(L.MOD_SIMPLE_DELAY, off, spans, None, ostate, oline, want, x)
+        d_out, d_x = ctx.buf(frames, V, out0), ctx.buf(frames, V, x)
+        sp = ctx.spans(V, frames, off, spans)
+        g.paint([sp], [d_out], [d_x])
+        assert_bit_exact(d_out.download(), want, f"delay graph block {block}")
+        assert state_equal(bank.get_state(), ostate), "carried delay index differs"
+        assert_bit_exact(bank.get_delay_line(), oline, f"delay line after block {block}")
+    g.free()
+
+
+def test_graph_feedback_echo_and_libm_arith(ctx):
+    """A feedback echo written as a script would (delay block whose body feeds its own output back): y = x + 0.6 * delayed(y),
+    against a plain f32 loop; then sin / cos / pow of the script runtime's arithmetic within the libm tolerance."""
+    V, frames, D = 40, 2048, 37
+    rng = np.random.default_rng(12)
+    x = rng.uniform(-1, 1, size=(frames, V)).astype(np.float32)
+    b = E.GraphBuilder()
+    T, OUT, IN = E.T, E.OUT, E.IN
+    fd = b.delay_field()
+    b.delay_read(fd, T(0))                 # feedback_temp = delayed y
+    b.zero(T(1))
+    b.multiplyScalar(T(1), T(0), 0.6)      # feedback_out = 0 + delayed * 0.6
+    b.addInto(T(1), IN(0))                 #              + x
+    b.delay_write(fd, T(1))
+    b.copy(OUT(0), T(1))
+    b.arith(L.ARITH_SIN, T(0), T(1))
+    b.arith(L.ARITH_COS, T(1), T(1))
+    b.arith(L.ARITH_POW, T(1), 2.0, T(1))  # 2 ^ cos(y)
+    b.copy(OUT(1), T(0))
+    b.copy(OUT(2), T(1))
+    g = E.Graph(ctx, E.graph_config(V, b, 2, num_outputs=3, num_inputs=1), b)
+    bank = E.DelayBank(ctx, L.MOD_SIMPLE_DELAY, V, D)
+    g.set_field(fd, bank, None)
+    sp = ctx.spans_full(V, frames // 1024, 1024)
+    outs = [ctx.buf(frames, V) for _ in range(3)]
+    g.paint([sp], outs, [ctx.buf(frames, V, x)])
+    y = np.zeros((frames, V), dtype=np.float32)
+    line = np.zeros((D, V), dtype=np.float32)
+    for f in range(frames):
+        d = np.float32(0.0) + line[f % D]
+        y[f] = (np.float32(0.0) + d * np.float32(0.6)) + x[f]
+        line[f % D] = y[f]
+    assert_bit_exact(outs[0].download(), y, "feedback echo")
+    assert_close(outs[1].download(), np.sin(y.astype(np.float64)).astype(np.float32), 2e-6, "sin")
+    assert_close(outs[2].download(), np.power(2.0, np.cos(y.astype(np.float64))).astype(np.float32), 4e-6, "pow(2, cos)")
+    g.free()

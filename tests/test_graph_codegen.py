@@ -45,5 +45,33 @@ def test_generator_rejects_malformed_lists():
     check(b, cfg, "MIX")
 
 
+def test_delay_block_instructions_are_checked():
+    def check(b, cfg, needle):
+        rc, log, n = E.graph_compile_check(cfg, b)
+        assert rc == L.ERR_INVALID and needle in log, (rc, log)
+
+    b = E.GraphBuilder()
+    fd = b.delay_field()
+    b.delay_write(fd, E.T(0))
+    check(b, E.graph_config(8, b, 1), "without a preceding DELAY_READ")
+    b = E.GraphBuilder()
+    fd = b.delay_field()
+    b.delay_read(fd, E.T(0))
+    check(b, E.graph_config(8, b, 1), "has no DELAY_WRITE")
+    b = E.GraphBuilder()
+    f = b.call(L.MOD_GATE, E.T(0))
+    b.delay_read(f, E.T(0))
+    check(b, E.graph_config(8, b, 1), "needs a ZCU_MOD_SIMPLE_DELAY field")
+    b = E.GraphBuilder()
+    fd = b.delay_field()
+    b.delay_read(fd, E.T(0))
+    b.arith(L.ARITH_POW, E.T(0), 2.0, E.T(0))
+    b.arith(L.ARITH_SIN, E.T(0), E.T(0))
+    b.delay_write(fd, E.T(0))
+    b.addInto(E.OUT(0), E.T(0))
+    rc, log, n = E.graph_compile_check(E.graph_config(8, b, 1), b)
+    assert rc == L.OK and n > 10000, log
+
+
 def test_struct_sizes_match_the_header():
     assert C.sizeof(L.GraphRef) == 8 and C.sizeof(L.GraphInstr) == 56 and C.sizeof(L.GraphConfig) == 32

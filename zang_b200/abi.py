@@ -28,10 +28,10 @@ OUT_ACCUMULATE, OUT_OVERWRITE = 0, 1
 MAX_POLYPHONY = 32
 # fused module graphs
 GREF_NONE, GREF_TEMP, GREF_OUTPUT, GREF_INPUT = range(4)
-GI_BASIC, GI_ARITH, GI_CALL = range(3)
+GI_BASIC, GI_ARITH, GI_CALL, GI_DELAY_READ, GI_DELAY_WRITE = range(5)
 (BASIC_ZERO, BASIC_SET, BASIC_COPY, BASIC_ADD, BASIC_ADD_INTO, BASIC_ADD_SCALAR, BASIC_ADD_SCALAR_INTO, BASIC_MULTIPLY,
  BASIC_MULTIPLY_WITH, BASIC_MULTIPLY_SCALAR, BASIC_MULTIPLY_WITH_SCALAR) = range(11)
-ARITH_SUB, ARITH_DIV, ARITH_MIN, ARITH_MAX, ARITH_NEG, ARITH_ABS, ARITH_SQRT = range(7)
+ARITH_SUB, ARITH_DIV, ARITH_MIN, ARITH_MAX, ARITH_NEG, ARITH_ABS, ARITH_SQRT, ARITH_SIN, ARITH_COS, ARITH_POW = range(10)
 SCALAR_NONE, SCALAR_A, SCALAR_B = range(3)
 GRAPH_OUT_BUFFERS, GRAPH_OUT_MIX = 0, 1
 

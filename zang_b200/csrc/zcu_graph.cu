@@ -163,6 +163,8 @@ struct FieldInfo {
     bool used = false;
     bool has_run = false;  // the module offers run_limit / run_begin / sample_run / run_end (zcu_modules.cuh: HAS_RUN)
     bool skippable = false;  // exact skip-ahead from its own params alone (advance()), or a Decimator (counter + replay window)
+    bool is_delay = false;   // a zang.Delay(N) served by DELAY_READ / DELAY_WRITE
+    int delay_reads = 0, delay_writes = 0;
 };
 
 bool module_type(int kind, const zcu_graph_instr& in, std::string& type, std::string& err) {
@@ -249,8 +251,10 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     for (uint32_t i = 0; i < n; i++) {
         const zcu_graph_instr& x = ins[i];
         if (x.span_table >= K) return fail(i, "span_table out of range");
-        if (!ref_ok(x.out, true)) return fail(i, "out must be a temp or an output of the graph");
-        if (x.out.kind == ZCU_GREF_OUTPUT) out_tables[x.out.index] |= 1u << x.span_table;
+        if (x.op != ZCU_GI_DELAY_WRITE) {  // (DELAY_WRITE has no destination buffer)
+            if (!ref_ok(x.out, true)) return fail(i, "out must be a temp or an output of the graph");
+            if (x.out.kind == ZCU_GREF_OUTPUT) out_tables[x.out.index] |= 1u << x.span_table;
+        }
         for (int q = 0; q < 3; q++) {
             if (x.in[q].kind == ZCU_GREF_NONE) continue;
             if (!ref_ok(x.in[q], false)) return fail(i, "operand reference out of range");
@@ -285,6 +289,26 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                     default: f.skippable = false; break;  // Filter, delays, FM oscillator: one segment
                 }
             }
+        } else if (x.op == ZCU_GI_DELAY_READ || x.op == ZCU_GI_DELAY_WRITE) {
+            if (x.field >= c.num_fields) return fail(i, "field out of range");
+            FieldInfo& f = fields[x.field];
+            if (field_kinds[x.field] != ZCU_MOD_SIMPLE_DELAY) return fail(i, "a delay instruction needs a ZCU_MOD_SIMPLE_DELAY field (zang.Delay)");
+            if (f.used && !f.is_delay) return fail(i, "this field is a module instance, not a delay line");
+            if (f.used && f.table != x.span_table) return fail(i, "DELAY_READ and DELAY_WRITE of a field must name the same span table");
+            if (x.op == ZCU_GI_DELAY_READ) {
+                if (f.delay_reads != f.delay_writes) return fail(i, "DELAY_READ twice without a DELAY_WRITE in between");
+                f.delay_reads++;
+            } else {
+                if (f.delay_reads != f.delay_writes + 1) return fail(i, "DELAY_WRITE without a preceding DELAY_READ");
+                if (x.in[0].kind == ZCU_GREF_NONE) return fail(i, "DELAY_WRITE needs the buffer to store (in[0])");
+                f.delay_writes++;
+            }
+            if (f.delay_reads > 1) return fail(i, "a delay line is served once per graph");
+            f.kind = ZCU_MOD_SIMPLE_DELAY;
+            f.type = "GraphDelayMod";
+            f.table = x.span_table;
+            f.used = true;
+            f.is_delay = true;
         } else if (x.op == ZCU_GI_BASIC) {
             if (x.sub < 0 || x.sub > 10) return fail(i, "unknown basic op");
             const bool na = x.sub == 2 || x.sub == 3 || x.sub == 4 || x.sub == 5 || x.sub == 7 || x.sub == 8 || x.sub == 9;
@@ -292,8 +316,8 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             if (na && x.in[0].kind == ZCU_GREF_NONE) return fail(i, "this basic op needs operand a");
             if (nb && x.in[1].kind == ZCU_GREF_NONE) return fail(i, "this basic op needs operand b");
         } else if (x.op == ZCU_GI_ARITH) {
-            if (x.sub < 0 || x.sub > ZCU_ARITH_SQRT) return fail(i, "unknown arith op");
-            const bool unary = x.sub >= ZCU_ARITH_NEG;
+            if (x.sub < 0 || x.sub > ZCU_ARITH_POW) return fail(i, "unknown arith op");
+            const bool unary = x.sub >= ZCU_ARITH_NEG && x.sub <= ZCU_ARITH_COS;
             if (unary) {
                 if (x.in[0].kind == ZCU_GREF_NONE) return fail(i, "unary arith needs operand a");
             } else {
@@ -304,8 +328,10 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             return fail(i, "unknown instruction kind");
         }
     }
-    for (uint32_t f = 0; f < c.num_fields; f++)
+    for (uint32_t f = 0; f < c.num_fields; f++) {
         if (!fields[f].used) return err = "a field is never called", false;
+        if (fields[f].is_delay && fields[f].delay_reads != fields[f].delay_writes) return err = "a DELAY_READ has no DELAY_WRITE", false;
+    }
 
     auto ref = [&](const zcu_graph_ref& r) -> std::string {
         char b[32];
@@ -326,6 +352,14 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
             char t[200];
             snprintf(t, sizeof t, "m%u.%s(%s, %s, %s, %s);", x.field, (run_form && fields[x.field].has_run) ? "sample_run" : "sample", d.c_str(),
                      a.c_str(), b.c_str(), cc.c_str());
+            stmt = t;
+        } else if (x.op == ZCU_GI_DELAY_READ) {
+            char t[96];
+            snprintf(t, sizeof t, "m%u.read(%s);", x.field, d.c_str());
+            stmt = t;
+        } else if (x.op == ZCU_GI_DELAY_WRITE) {
+            char t[96];
+            snprintf(t, sizeof t, "m%u.write(%s);", x.field, a.c_str());
             stmt = t;
         } else if (x.op == ZCU_GI_BASIC) {
             switch (x.sub) {  // basics.zig:12-78, the expression forms of BasicMod (zcu_modules.cuh)
@@ -351,6 +385,9 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                 case ZCU_ARITH_NEG: stmt = d + " = -" + a + ";"; break;
                 case ZCU_ARITH_ABS: stmt = d + " = fabsf(" + a + ");"; break;
                 case ZCU_ARITH_SQRT: stmt = d + " = sqrtf(" + a + ");"; break;
+                case ZCU_ARITH_SIN: stmt = d + " = sinf(" + a + ");"; break;
+                case ZCU_ARITH_COS: stmt = d + " = cosf(" + a + ");"; break;
+                case ZCU_ARITH_POW: stmt = d + " = powf(" + A + ", " + B + ");"; break;
             }
         }
         return stmt;
@@ -582,7 +619,10 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     src += "          if (lane_live) {\n";
     for (uint32_t f = 0; f < c.num_fields; f++)
         if (fields[f].has_run) appendf(src, "            m%u.run_begin();\n", f);
-    src += "            uint32_t r = 0;\n            for (; r + 4 <= run; r += 4) {\n";
+    bool has_delay = false;  // a delay line is read and written slot by slot: no four-sample batches
+    for (uint32_t f = 0; f < c.num_fields; f++) has_delay = has_delay || fields[f].is_delay;
+    src += "            uint32_t r = 0;\n";
+    src += has_delay ? "            for (; false;) {\n" : "            for (; r + 4 <= run; r += 4) {\n";
     {
         std::string pf;
         for (uint32_t i = 0; i < c.num_inputs; i++)

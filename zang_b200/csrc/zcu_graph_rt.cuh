@@ -82,6 +82,31 @@ struct SpanCursor {
     __device__ __forceinline__ uint32_t boundary() const { return active ? s_end : s_start; }
 };
 
+// zang.Delay(N) inside a graph (src/zang/delay.zig:7-91; the script runtime's `delay` block, runtime.zig:704-721).  The
+// reference serves the line in chunks of at most N frames: add the delayed samples (readDelayBuffer), run the inner
+// instructions, store the new samples in the same slots (writeDelayBuffer).  A chunk only reads slots none of its own writes
+// has touched, so per sample "read slot, ..., write slot, advance" leaves the same values in the same slots.
+struct GraphDelayMod {
+    DelayLine d;
+    float* slot;
+    __device__ void load(const PaintArgs& a, uint32_t v) {
+        d.bind(a, v);
+        d.index = ((const zcu_delay_state*)a.state)[v].index;
+        slot = d.col;
+    }
+    __device__ void store(const PaintArgs& a, uint32_t v) { ((zcu_delay_state*)a.state)[v].index = d.index; }
+    __device__ void begin_span(const PaintArgs&, uint32_t, uint32_t, uint32_t) {}
+    __device__ void end_span(const PaintArgs&) {}
+    __device__ __forceinline__ void read(float& acc) {  // zero(temp); readDelayBuffer(temp)
+        slot = d.col + (size_t)d.index * d.V;
+        acc = 0.0f + *slot;
+    }
+    __device__ __forceinline__ void write(float x) {  // writeDelayBuffer
+        *slot = x;
+        d.index = d.index + 1 == d.n ? 0u : d.index + 1;
+    }
+};
+
 // ---- voice mix of a warp's tile (shared with k_nice_seg_render) ----------------------------------------------------
 // tile of a warp: RT frames x 32 voices, row stride 34 floats (rows 8-byte aligned, conflict-free both for the per-voice
 // column writes and for the mix's 8-byte row reads)

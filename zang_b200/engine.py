@@ -772,6 +772,19 @@ class GraphBuilder:
         self._add(L.GI_CALL, int(kind), d, ins, field=field, table=table)
         return field
 
+    def delay_field(self):
+        """a zang.Delay(N) of the graph (bank: DelayBank of kind MOD_SIMPLE_DELAY); returns the field index"""
+        self.field_kinds.append(int(L.MOD_SIMPLE_DELAY))
+        return len(self.field_kinds) - 1
+
+    def delay_read(self, field, d, table=0):
+        """zero(d); delay.readDelayBuffer(d)  (runtime.zig:711-713)"""
+        return self._add(L.GI_DELAY_READ, 0, d, field=field, table=table)
+
+    def delay_write(self, field, a, table=0):
+        """delay.writeDelayBuffer(a)  (runtime.zig:718)"""
+        return self._add(L.GI_DELAY_WRITE, 0, a, (a,), field=field, table=table)
+
     def arrays(self):
         arr = (L.GraphInstr * len(self.instrs))(*self.instrs)
         kinds = (C.c_int32 * max(1, len(self.field_kinds)))(*self.field_kinds)
