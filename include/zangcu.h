@@ -420,6 +420,20 @@ int64_t zcu_poly_voice_spans(zcu_poly_voice* pv, const int32_t* param_note_on, f
                              uint32_t num_buffers, uint32_t last_buffer_frames, uint32_t* voice_off_out, zcu_span* spans_out,
                              uint64_t max_spans);
 
+/* The same on the DEVICE for a bank of independent polyphonic voices ("songs"): song s owns
+ * events[song_off[s] .. song_off[s+1]) (chronological; event.param = a row of param_note_on, or every impulse is a note-on
+ * when that is NULL), all with one polyphony.  zcu_poly_bank_spans replays NoteTracker.consume -> PolyphonyDispatcher.dispatch
+ * -> one Trigger per slot for the NEXT num_buffers mix buffers of every song (the trackers keep their time, like
+ * zcu_poly_voice_spans) and leaves a device span table with songs * polyphony voice columns (column = song * polyphony + slot,
+ * span.param = the event's params row).  Bit-identical to zcu_poly_voice_spans per song. */
+typedef struct zcu_poly_bank zcu_poly_bank;
+int zcu_poly_bank_create(zcu_ctx*, uint32_t songs, uint32_t polyphony, const uint32_t* song_off_host, const zcu_song_event* events_host,
+                         const int32_t* param_note_on_host, uint32_t nparams, float sample_rate, uint32_t buffer_frames, zcu_poly_bank** out);
+void zcu_poly_bank_free(zcu_poly_bank*);
+int zcu_poly_bank_reset(zcu_ctx*, zcu_poly_bank*);
+int zcu_poly_bank_get_state(zcu_ctx*, const zcu_poly_bank*, zcu_poly_voice* state_host); /* [songs]; tracker.song is NULL */
+int zcu_poly_bank_spans(zcu_ctx*, zcu_poly_bank*, uint32_t num_buffers, uint32_t last_buffer_frames, zcu_spans** out);
+
 /* A bank of monophonic voices, each with its own ImpulseQueue + Trigger (examples/example_polyphony.zig:61-92 per voice).
  * Voice v owns events[event_off[v] .. event_off[v+1]) (absolute frames, chronological; zcu_note_event below).  Every mix
  * buffer's events are pushed into the voice's queue (capacity 32, notes.zig:108-118) and the Trigger splits the buffer.

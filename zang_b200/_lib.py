@@ -118,6 +118,11 @@ PROTOTYPES = {
     "zcu_cycle_advance": (None, [_P, _F, _U]),
     "zcu_bank_trigger_init": (None, [_P, _U, _P]),
     "zcu_bank_spans": (C.c_int64, [_P, _U, _P, _P, _U, _U, _U, _U, _P, _P, _U64]),
+    "zcu_poly_bank_create": (_I, [_P, _U, _U, _P, _P, _P, _U, _F, _U, _P]),
+    "zcu_poly_bank_free": (None, [_P]),
+    "zcu_poly_bank_reset": (_I, [_P, _P]),
+    "zcu_poly_bank_get_state": (_I, [_P, _P, _P]),
+    "zcu_poly_bank_spans": (_I, [_P, _P, _U, _U, _P]),
     "zcu_event_bank_create": (_I, [_P, _U, _P, _P, _U, _U, _P]),
     "zcu_event_bank_free": (None, [_P]),
     "zcu_event_bank_reset": (_I, [_P, _P]),

@@ -139,7 +139,7 @@ uint32_t zcu_note_tracker_consume(zcu_note_tracker* nt, float sample_rate, uint3
         const zcu_song_event& ev = nt->song[nt->next_song_event];
         if (!(ev.t < end_t)) break;
         const float f = (ev.t - nt->t) / buf_time;
-        uint32_t rel = (uint32_t)(f * flen);
+        uint32_t rel = (uint32_t)(long long)(f * flen);  // through 64 bits: what x86-64 does anyway, and what the device replay does
         if (rel > out_len - 1) rel = out_len - 1;
         nt->next_song_event++;
         if (count < max_out) {

@@ -216,3 +216,47 @@ class DeviceBankTrigger:
         if self._h:
             lib.zcu_event_bank_free(self._h)
             self._h = None
+
+
+class DevicePolyBank:
+    """Many independent polyphonic voices (NoteTracker -> PolyphonyDispatcher -> Trigger per slot) replayed on the GPU
+    (zcu_poly_bank_*): songs = list of [(t, note_id, params_row)], one polyphony for all."""
+
+    def __init__(self, ctx, songs, polyphony, param_note_on, sample_rate, buffer_frames=1024):
+        self.ctx, self.songs, self.polyphony, self.buffer_frames = ctx, len(songs), int(polyphony), int(buffer_frames)
+        off = np.zeros(len(songs) + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(s) for s in songs])
+        ev = np.zeros(int(off[-1]), dtype=L.song_event_dtype)
+        k = 0
+        for s in songs:
+            for t, nid, row in s:
+                ev[k] = (t, nid, row)
+                k += 1
+        on = None if param_note_on is None else np.ascontiguousarray(param_note_on, dtype=np.int32)
+        h = C.c_void_p()
+        rc = lib.zcu_poly_bank_create(ctx._h, self.songs, self.polyphony, ptr(off), ptr(ev), ptr(on), 0 if on is None else on.size,
+                                      float(sample_rate), self.buffer_frames, C.byref(h))
+        if rc != L.OK:
+            raise RuntimeError(f"zcu_poly_bank_create: {_err(ctx)}")
+        self._h = h
+
+    def spans(self, num_buffers, last_buffer_frames=None):
+        last = self.buffer_frames if last_buffer_frames is None else int(last_buffer_frames)
+        h = C.c_void_p()
+        rc = lib.zcu_poly_bank_spans(self.ctx._h, self._h, int(num_buffers), last, C.byref(h))
+        if rc != L.OK:
+            raise RuntimeError(f"zcu_poly_bank_spans: {_err(self.ctx)}")
+        return DeviceSpans(self.ctx, h, self.songs * self.polyphony, (int(num_buffers) - 1) * self.buffer_frames + last)
+
+    def reset(self):
+        assert lib.zcu_poly_bank_reset(self.ctx._h, self._h) == L.OK
+
+    def state(self):
+        st = (L.PolyVoicePOD * self.songs)()
+        assert lib.zcu_poly_bank_get_state(self.ctx._h, self._h, st) == L.OK
+        return st
+
+    def free(self):
+        if self._h:
+            lib.zcu_poly_bank_free(self._h)
+            self._h = None
