@@ -43,6 +43,19 @@ def test_song_opening_bit_exact(ctx):
     assert hashlib.sha256(got_pcm[:64 * 1024 * 2].tobytes()).hexdigest() == gold["pcm_sha256"][str(64 * 1024)]
 
 
+def test_song_dispatched_on_the_device(ctx):
+    """configs[0] with the whole event path on the GPU: NoteTracker -> PolyphonyDispatcher -> Trigger of the three voices
+    (polyphony 3 / 10 / 4, example_song.zig:28-74) replayed by zcu_poly_bank_*; the PCM must be the host-dispatched render's,
+    byte for byte, over 16 s that include the pedal's entry, with a block size that does not divide anything."""
+    notes = load_fixture()
+    n = 750 * 1024 + 77
+    host_pcm, host_mix = song.render_song(ctx, notes, n, block_buffers=96, want_mix=True)
+    dev_pcm, dev_mix = song.render_song(ctx, notes, n, block_buffers=61, want_mix=True, device_events=True)
+    assert np.abs(host_mix).max() > 0.5
+    assert_bit_exact(dev_mix, host_mix, "song mix, device-side dispatch vs host-side dispatch")
+    assert dev_pcm.tobytes() == host_pcm.tobytes()
+
+
 def test_song_with_pedal_within_tolerance(ctx):
     notes = load_fixture()
     n = 1500 * 1024  # 32 s: pedal (PMOscInstrument, two SineOscs) + regular organ

@@ -192,8 +192,9 @@ class PolyVoice:
     """Voice(T) (example_song.zig:287-350): NoteTracker + PolyphonyDispatcher + one Trigger per sub-voice on
     the host, the instrument bank with `polyphony` voice columns on the device."""
 
-    def __init__(self, ctx, bank, notes, polyphony, freq_mul=1.0, sample_rate=AUDIO_SAMPLE_RATE):
+    def __init__(self, ctx, bank, notes, polyphony, freq_mul=1.0, sample_rate=AUDIO_SAMPLE_RATE, device_events=False):
         self.ctx, self.bank, self.polyphony, self.sample_rate = ctx, bank, polyphony, float(sample_rate)
+        self.dev = None
         self.song = np.zeros(notes.size, dtype=L.song_event_dtype)
         self.song["t"], self.song["note_id"], self.song["param"] = notes["t"], notes["note_id"], np.arange(notes.size)
         self.note_on = np.ascontiguousarray(notes["note_on"], dtype=np.int32)
@@ -207,6 +208,10 @@ class PolyVoice:
         if rc != L.OK:
             raise E.ZangCuError(f"zcu_poly_voice_init failed ({rc})")
         self.bufs = None
+        if device_events:  # the same event logic replayed on the GPU (zcu_poly_bank_*): no span table crosses PCIe
+            from .events import DevicePolyBank
+            song = list(zip(self.song["t"].tolist(), self.song["note_id"].tolist(), self.song["param"].tolist()))
+            self.dev = DevicePolyBank(ctx, [[(np.float32(t), nid, row) for t, nid, row in song]], polyphony, self.note_on, sample_rate, AUDIO_BUFFER_SIZE)
 
     def _buffers(self, frames):
         if self.bufs is None or self.bufs[0].frames != frames:
@@ -229,6 +234,15 @@ class PolyVoice:
     def paint(self, num_buffers, buffer_frames, last_frames, mix):
         """Paints the block's spans of every sub-voice and adds the sub-voices, in order, into mix ([frames][1])."""
         frames = (num_buffers - 1) * buffer_frames + last_frames
+        if self.dev is not None:
+            assert buffer_frames == self.dev.buffer_frames
+            out, *temps = self._buffers(frames)
+            sp = self.dev.spans(num_buffers, last_frames)
+            self.ctx.zero(None, out)
+            self.bank.paint(sp, [out], temps, self.params)
+            self.ctx.mix_ordered(out, None, 1, mix)
+            sp.free()
+            return -1
         off, spans = self.span_table(num_buffers, buffer_frames, last_frames)
         if spans.size == 0:
             return 0
@@ -244,6 +258,9 @@ class PolyVoice:
         for b in self.bufs or ():
             b.free()
         self.bufs = None
+        if self.dev is not None:
+            self.dev.free()
+            self.dev = None
 
 
 def wav_header(num_channels, sample_rate, bytes_per_sample, data_bytes):
@@ -252,16 +269,16 @@ def wav_header(num_channels, sample_rate, bytes_per_sample, data_bytes):
                        sample_rate * num_channels * bytes_per_sample, num_channels * bytes_per_sample, 8 * bytes_per_sample, b"data", data_bytes)
 
 
-def render_song(ctx, notes, total_frames=NUM_SECONDS * AUDIO_SAMPLE_RATE, block_buffers=512, want_mix=False):
+def render_song(ctx, notes, total_frames=NUM_SECONDS * AUDIO_SAMPLE_RATE, block_buffers=512, want_mix=False, device_events=False):
     """write_wav.zig:49-95 for the first total_frames frames.  `notes` is the song text or the three event arrays
     parse_song returns.  Returns (pcm bytes as uint8 array, f32 mix or None)."""
     if isinstance(notes, (str, bytes)):
         notes = parse_song(notes)
     sr, B = AUDIO_SAMPLE_RATE, AUDIO_BUFFER_SIZE
     voices = [  # example_song.zig:28-74
-        PolyVoice(ctx, E.PMOscInstrumentBank(ctx, 3, 0.4), notes[0], 3, freq_mul=0.5, sample_rate=sr),
-        PolyVoice(ctx, E.NiceInstrumentBank(ctx, 10, 0.25), notes[1], 10, sample_rate=sr),
-        PolyVoice(ctx, E.NiceInstrumentBank(ctx, 4, 0.1), notes[2], 4, sample_rate=sr),
+        PolyVoice(ctx, E.PMOscInstrumentBank(ctx, 3, 0.4), notes[0], 3, freq_mul=0.5, sample_rate=sr, device_events=device_events),
+        PolyVoice(ctx, E.NiceInstrumentBank(ctx, 10, 0.25), notes[1], 10, sample_rate=sr, device_events=device_events),
+        PolyVoice(ctx, E.NiceInstrumentBank(ctx, 4, 0.1), notes[2], 4, sample_rate=sr, device_events=device_events),
     ]
     pcm = np.zeros(total_frames * 2, dtype=np.uint8)
     mix_all = np.zeros(total_frames, dtype=np.float32) if want_mix else None
