@@ -690,12 +690,20 @@ def main():
                 from zang_b200 import engine as E
                 bf = 64 * BUFFER_FRAMES
                 nb = E.NiceInstrumentBank(ctx, V, 0.3)
-                wl64 = synth.polyphony_bank(V, bf, SAMPLE_RATE)  # the same generator and seed, cut to the block (params rows = its events)
-                soff, sspans = BankTrigger(wl64["event_off"], wl64["events"], bf, BUFFER_FRAMES).spans(0, bf)
-                sp = ctx.spans(V, bf, soff, sspans)
+                # a steady-state block of the benched job: buffers [1024, 1088) (21.8 s into the 60 s), every voice holding the
+                # note it holds there; the preceding 64 buffers are painted first so that the module states are mid-render too
+                first = min(1024 * BUFFER_FRAMES, max(bf, (total_frames // bf - 1) * bf))
+                wl64 = synth.window_bank(wl, first - bf, first + bf)
+                trig = BankTrigger(wl64["event_off"], wl64["events"], 2 * bf, BUFFER_FRAMES)
                 rows = np.zeros(wl64["events"].size, dtype=E.NiceInstrumentBank.Params)
                 rows["sample_rate"], rows["freq"], rows["note_on"] = SAMPLE_RATE, wl64["events"]["freq"], wl64["events"]["note_on"]
                 bufs = [ctx.buf(bf, V) for _ in range(3)]
+                ctx.set_paint_mode(L.PAINT_TOLERANCE)
+                sp0 = ctx.spans(V, bf, *trig.spans(0, bf))
+                nb.paint(sp0, [bufs[0]], bufs[1:], rows)
+                sp0.free()
+                soff, sspans = trig.spans(bf, bf)
+                sp = ctx.spans(V, bf, soff, sspans)
                 dp = {}
                 for pm, pname, ovr in ((L.PAINT_TOLERANCE, "tolerance", False), (L.PAINT_TOLERANCE, "tolerance_overwrite", True), (L.PAINT_EXACT, "exact", False)):
                     ctx.set_paint_mode(pm)
@@ -712,6 +720,9 @@ def main():
                                  "kernel_launches_per_block": int(calls)}
                 ctx.set_paint_mode(L.PAINT_EXACT)
                 line["dropin_module_path"] = {"block_frames": bf, "calls_per_block": 8, "bytes_per_voice_sample": 64, "paint_modes": dp,
+                                              "block": f"mix buffers [{first // BUFFER_FRAMES}, {first // BUFFER_FRAMES + 64}) of the benched job (steady state: every voice "
+                                                       "playing; round 1 measured the job's first 64 buffers, in which voices start one by one)",
+                                              "span_coverage": float((sspans["end"].astype(np.int64) - sspans["start"]).sum()) / (V * bf),
                                               "note": "tolerance = Filter in time segments whose warm-up windows are computed from the spans' constants (<= 1e-5), "
                                                       "everything else bit-exact; tolerance_overwrite = the same with every `zero; paint` pair of the body as ONE "
                                                       "call in ZCU_OUT_OVERWRITE mode (5 C-ABI calls, same bits; still counted at the reference chain's 64 B); "

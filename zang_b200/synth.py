@@ -45,6 +45,30 @@ def polyphony_bank(voices, total_frames, sample_rate=48000.0, seed=SEED, mean_on
     return {"event_off": event_off, "events": ev, "color": color, "gains": gains}
 
 
+def window_bank(wl, f0, f1):
+    """The events of a bank inside the frame window [f0, f1), re-based to frame 0, plus every voice's last event before f0 placed
+    at frame 0 (the note it is holding when the window opens): a short job whose voices are all in the state a long render has
+    in its middle.  Used to measure the module chain on a steady-state block instead of the job's first seconds, in which the
+    voices have not started yet."""
+    off, ev = wl["event_off"], wl["events"]
+    V = off.size - 1
+    parts, counts = [], np.zeros(V, dtype=np.int64)
+    for v in range(V):
+        e = ev[off[v]:off[v + 1]]
+        a = int(np.searchsorted(e["frame"], f0, side="left"))
+        b = int(np.searchsorted(e["frame"], f1, side="left"))
+        w = e[max(a - 1, 0):b].copy() if a > 0 else e[a:b].copy()
+        fr = w["frame"].astype(np.int64) - f0
+        fr[fr < 0] = 0
+        w["frame"] = fr.astype(np.uint32)
+        parts.append(w)
+        counts[v] = w.size
+    out = dict(wl)
+    out["event_off"] = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+    out["events"] = np.concatenate(parts) if parts else ev[:0]
+    return out
+
+
 def shard_voices(wl, rank, world):
     """Contiguous voice range of `rank`: voices are independent, no data-path exchange."""
     V = wl["color"].shape[0]
