@@ -146,7 +146,9 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     // exact chained prefix sum (M::SCAN): no aliasing either, the scan pass reads inputs while earlier segments paint
     const bool scan = ScanOf<M>::value && !getenv("ZCU_PAINT_NO_SCAN") && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
                       !overlaps(a.out, a.in2, n);
-    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, warm ? 4u : 8u);
+    uint32_t warm_resident = 4;
+    if (const char* e = getenv("ZCU_PAINT_WARM_RESIDENT")) warm_resident = (uint32_t)std::min(8, std::max(1, atoi(e)));  // tuning
+    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, warm ? warm_resident : 8u);
     a.chain = nullptr;
     a.chain_flags = nullptr;
     a.epoch = 0;
