@@ -4,7 +4,9 @@
 //   A  one-warp CTAs, 4-byte cp.async per lane and frame, direct 4-byte stores (the r01 kernel's pipeline)
 //   B  W-warp CTAs over 32*W adjacent voices, 16-byte cp.async rows staged in smem, in-place update, 16-byte row stores
 //   C  as B with 1-D TMA bulk copies (cp.async.bulk + mbarrier) in and bulk stores out
+//   D  as B with ONE 2-D tensor-map TMA copy per tile ([T][32*W] box, cp.async.bulk.tensor.2d) in and one out (round 2)
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/ubench_rowtile tools/ubench_rowtile.cu
+#include <cuda.h>
 #include <cuda_pipeline.h>
 #include <cuda_runtime.h>
 
@@ -131,6 +133,68 @@ __global__ void __launch_bounds__(32 * W) k_C(float* out, uint32_t V, uint32_t f
     if (warp == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// D: one 2-D TMA load and one 2-D TMA store per tile; one elected thread issues both
+template <int W, int S>
+__global__ void __launch_bounds__(32 * W) k_D(const CUtensorMap* __restrict__ tmap_p, uint32_t V, uint32_t frames, uint32_t T, uint32_t seg) {
+    // the tensor copies need their shared-memory tile on a 128-byte boundary: no static shared memory in front of the tiles,
+    // the base rounded up by hand, the mbarriers behind the tiles
+    extern __shared__ float smem_raw[];
+    constexpr uint32_t RV = 32 * W;
+    float* smem = smem_raw + ((128u - (s2u(smem_raw) & 127u)) & 127u) / 4;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)S * T * RV);
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t v0 = blockIdx.x * RV;
+    const uint32_t f_begin = blockIdx.y * seg, f_end = min(frames, f_begin + seg);
+    if (tid == 0) { for (int s = 0; s < S; s++) mbar_init(&full[s], 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncthreads();
+    auto issue = [&](uint32_t tile) {
+        const uint32_t st = tile % S;
+        mbar_expect(&full[st], T * RV * 4);
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                         s2u(smem + (size_t)st * T * RV)),
+                     "l"(tmap_p), "r"(v0), "r"(tile * T), "r"(s2u(&full[st]))
+                     : "memory");
+    };
+    const uint32_t t0 = f_begin / T, nt = (f_end + T - 1) / T;
+    if (tid == 0) for (int s = 0; s < S - 1; s++) if (t0 + s < nt) issue(t0 + s);
+    for (uint32_t tile = t0; tile < nt; tile++) {
+        const uint32_t it = tile - t0, st = tile % S;
+        if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncthreads();
+        if (tid == 0 && tile + S - 1 < nt) issue(tile + S - 1);
+        mbar_wait(&full[st], (it / S) & 1);
+        float* sp = smem + (size_t)st * T * RV + warp * 32 + lane;
+#pragma unroll 4
+        for (uint32_t j = 0; j < T; j++) sp[j * RV] += 1.0f;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(tmap_p), "r"(v0), "r"(tile * T),
+                         "r"(s2u(smem + (size_t)st * T * RV))
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static CUtensorMap make_map(float* buf, uint32_t V, uint32_t frames, uint32_t T, uint32_t RV) {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        cudaDriverEntryPointQueryResult q;
+        CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void**)&fn, cudaEnableDefault, &q));
+    }
+    CUtensorMap m;
+    const cuuint64_t dims[2] = {V, frames}, strides[1] = {(cuuint64_t)V * 4};
+    const cuuint32_t box[2] = {RV, T}, estr[2] = {1, 1};
+    const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, buf, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { printf("cuTensorMapEncodeTiled failed: %d\n", (int)r); exit(1); }
+    return m;
+}
+
 static float time_it(void (*launch)(float*, uint32_t, uint32_t), float* buf, uint32_t V, uint32_t frames, float* flush, size_t flush_n) {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
@@ -162,6 +226,16 @@ template <int W, int S> static void launch_C(float* b, uint32_t V, uint32_t fram
     size_t sm = (size_t)S * g_T * 32 * W * 4;
     CK(cudaFuncSetAttribute(k_C<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     k_C<W, S><<<dim3(V / (32 * W), (frames + seg - 1) / seg), 32 * W, sm>>>(b, V, frames, g_T, seg);
+}
+template <int W, int S> static void launch_D(float* b, uint32_t V, uint32_t frames) {
+    uint32_t seg = (frames + g_nseg - 1) / g_nseg; seg = (seg + g_T - 1) / g_T * g_T;
+    size_t sm = (size_t)S * g_T * 32 * W * 4 + 128 + 8 * S;
+    const CUtensorMap m = make_map(b, V, frames, g_T, 32 * W);
+    static CUtensorMap* dm = nullptr;
+    if (!dm) CK(cudaMalloc(&dm, sizeof(CUtensorMap)));
+    CK(cudaMemcpy(dm, &m, sizeof m, cudaMemcpyHostToDevice));
+    CK(cudaFuncSetAttribute(k_D<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    k_D<W, S><<<dim3(V / (32 * W), (frames + seg - 1) / seg), 32 * W, sm>>>(dm, V, frames, g_T, seg);
 }
 static void launch_A(float* b, uint32_t V, uint32_t frames) {
     uint32_t seg = (frames + g_nseg - 1) / g_nseg; seg = (seg + g_T - 1) / g_T * g_T;
@@ -196,6 +270,9 @@ int main() {
                 report("C W=4 S=3 TMA bulk", time_it(launch_C<4, 3>, buf, cfg.V, cfg.frames, flush, flush_n)); launches += 4;
                 report("C W=8 S=3 TMA bulk", time_it(launch_C<8, 3>, buf, cfg.V, cfg.frames, flush, flush_n)); launches += 4;
                 report("C W=4 S=4 TMA bulk", time_it(launch_C<4, 4>, buf, cfg.V, cfg.frames, flush, flush_n)); launches += 4;
+                report("D W=4 S=3 TMA 2-D tile", time_it(launch_D<4, 3>, buf, cfg.V, cfg.frames, flush, flush_n)); launches += 4;
+                report("D W=4 S=4 TMA 2-D tile", time_it(launch_D<4, 4>, buf, cfg.V, cfg.frames, flush, flush_n)); launches += 4;
+                report("D W=8 S=3 TMA 2-D tile", time_it(launch_D<8, 3>, buf, cfg.V, cfg.frames, flush, flush_n)); launches += 4;
             }
         }
         // verify: every element must equal the number of launches
