@@ -309,3 +309,50 @@ def test_pulse_gain_division_is_exact(ctx):
     assert lib.zcu_selftest_div_numerator(ctx._h, C.c_float(0.7), C.byref(bad), C.byref(claimed)) == 0
     assert bad.value == 0, f"{bad.value} of {claimed.value} quotients differ"
     assert claimed.value == (1 << 23) - 1
+
+
+RELAY_CASES = [c for c in CASES if c[0] in ("sine bc", "sine bb", "trisaw ctrl", "cycle buffer")]
+
+
+@pytest.mark.parametrize("nseg", [0, 7, 24], ids=["planned", "7seg", "24seg"])
+@pytest.mark.parametrize("case", RELAY_CASES, ids=[c[0] for c in RELAY_CASES])
+def test_buffer_frequency_phase_relay(ctx, case, nseg, monkeypatch):
+    """Oscillators driven by a frequency (speed) buffer carry an order-dependent f32 phase sum: no skip-ahead exists, so
+    a walk of its own (zcu_paint_kernel.cuh, k_paint_prefix_ring, M::PREFIX_RING) tabulates the phase at every segment start: one warp
+    per 32 voices runs the frames state-only through a cp.async ring, then the segments paint in parallel.  A long block (spans that straddle, end on
+    and start on segment boundaries; two voice blocks), planned and forced segment counts, two consecutive calls: the carried
+    phase is bit-equal to the sequential loop's, TriSawOsc and Cycle outputs bit-exact, SineOsc within the sinf tolerance."""
+    name, kind, variant, ins, bf, exact = case
+    Vn, NB = 150, 24
+    frames = NB * bf
+    if nseg:
+        monkeypatch.setenv("ZCU_PAINT_SEGMENTS", str(nseg))
+    rng = np.random.default_rng(4242 + nseg)
+    from cases import buf_input, make_params
+    mod = E.MODULE_CLASSES[kind](ctx, Vn)
+    ostate = oracle.state_init(kind, Vn)
+    for block in range(2):
+        off, spans = random_spans(rng, Vn, NB, bf, 9, max_cuts=2, p_empty=0.1, p_gap=0.3)
+        params = make_params(kind, rng, 9, variant)
+        out0 = rng.uniform(-1, 1, size=(frames, Vn)).astype(np.float32)
+        inputs = [None if r is None else buf_input(rng, frames, *r)[:, :1].repeat(Vn, axis=1) * rng.uniform(0.5, 1.0, Vn).astype(np.float32) for r in ins]
+        inputs = [None if a is None else np.ascontiguousarray(a, dtype=np.float32) for a in inputs]
+        want = out0.copy()
+        oracle.paint(kind, off, spans, params, ostate, want, *inputs)
+        d_out = ctx.buf(frames, Vn, out0)
+        d_in = [None if a is None else ctx.buf(frames, Vn, a) for a in inputs]
+        sp = ctx.spans(Vn, frames, off, spans)
+        if kind == L.MOD_SINE_OSC:
+            mod.paint(sp, [d_out], [], params, freq=d_in[0], phase=d_in[1])
+        elif kind == L.MOD_TRISAW_OSC:
+            mod.paint(sp, [d_out], [], params, freq=d_in[0])
+        else:
+            mod.paint(sp, [d_out], [], params, speed=d_in[0])
+        got = d_out.download()
+        if exact:
+            assert_bit_exact(got, want, f"{name} relay block {block}")
+        else:
+            assert_close(got, want, TRANSCENDENTAL_TOL, f"{name} relay block {block}")
+        assert state_equal(mod.bank.get_state(), ostate), f"{name}: carried phase differs after block {block}"
+        for b in [d_out, sp] + [x for x in d_in if x is not None]:
+            b.free()

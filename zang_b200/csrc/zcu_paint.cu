@@ -148,7 +148,14 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
                       !overlaps(a.out, a.in2, n);
     uint32_t warm_resident = 4;
     if (const char* e = getenv("ZCU_PAINT_WARM_RESIDENT")) warm_resident = (uint32_t)std::min(8, std::max(1, atoi(e)));  // tuning
-    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, warm ? warm_resident : 8u);
+    // order-dependent f32 phase sums (M::PREFIX_RING): a walk of its own tabulates the state at the segment starts, if the
+    // bank needs time segments to fill the machine at all
+    bool ring = PrefixRingOf<M>::value && !getenv("ZCU_PAINT_NO_PREFIX") && !overlaps(a.out, a.in0, n);
+    PaintPlan p = zcu_paint_plan(ctx, a, nb, skip || warm || scan || ring, warm ? warm_resident : 8u);
+    if (ring && p.nseg < 4 && !getenv("ZCU_PAINT_SEGMENTS")) {
+        ring = false;
+        p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, 8u);
+    }
     a.chain = nullptr;
     a.chain_flags = nullptr;
     a.epoch = 0;
@@ -169,13 +176,13 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         a.chain_err = ctx->paint_ticket + 1;
         a.warm_stats = warm ? ctx->paint_ticket + 2 : nullptr;
         ctx->paint_ticket_base += p.grid_x * p.nseg;  // one ticket per CTA of this launch (mod 2^32, like the device counter)
-    } else if (!skip) {
+    } else if (!skip && !ring) {
         p.nseg = 1;
         p.seg_frames = a.frames;
     }
     a.prefix = nullptr;
     a.prefix_stride = 0;
-    if (PrefixOf<M>::value && p.nseg > 1 && !getenv("ZCU_PAINT_NO_PREFIX")) {
+    if (PrefixOf<M>::value && (ring || !PrefixRingOf<M>::value) && p.nseg > 1 && !getenv("ZCU_PAINT_NO_PREFIX")) {
         // one sequential walk per voice tabulates the state at every segment start (instead of a re-walk per segment)
         const size_t stride = zcu_bank_state_size(kind), need = (size_t)p.nseg * a.V * stride;
         if (ctx->prefix_bytes < need) {
@@ -188,7 +195,12 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         }
         a.prefix = ctx->prefix;
         a.prefix_stride = (uint32_t)stride;
-        k_paint_prefix<M><<<(a.V + 127) / 128, 128, 0, ctx->stream>>>(a, p.seg_frames, p.nseg);
+        if constexpr (PrefixRingOf<M>::value) {
+            const bool v4 = a.V % 4 == 0 && ((uintptr_t)a.in0 & 15u) == 0;
+            k_paint_prefix_ring<M><<<(a.V + 31) / 32, 32, kRingRows * 32 * sizeof(float), ctx->stream>>>(a, p.seg_frames, p.nseg, v4 ? 1u : 0u);
+        } else {
+            k_paint_prefix<M><<<(a.V + 127) / 128, 128, 0, ctx->stream>>>(a, p.seg_frames, p.nseg);
+        }
         ctx->launches++;
         ZCU_CUDA(ctx, cudaGetLastError());
     }

@@ -152,6 +152,141 @@ __global__ void __launch_bounds__(128) k_paint_prefix(PaintArgs a, uint32_t seg_
     while (s < nseg) record();
 }
 
+// M::PREFIX_RING (with M::PREFIX): the carried state is an order-dependent f32 sum over an input buffer (the phase of SineOsc /
+// TriSawOsc / Cycle driven by a frequency buffer): no skip-ahead exists and the per-voice walk has to read every input sample,
+// but one step of it is a multiply and an add where a painted sample costs a sine.  k_paint_prefix_ring is that walk, alone
+// on the machine before the paint launch: one warp per 32 voices in frame lockstep, the input rows (128 bytes per warp and
+// frame) staged through a 32 KB cp.async ring per warp, eight frames per batch so that only the additions are a dependent
+// chain, the state recorded at every segment start like k_paint_prefix does.  The paint launch then runs its time segments
+// in parallel from those rows.
+template <class M, class = void>
+struct PrefixRingOf { static constexpr bool value = false; };
+template <class M>
+struct PrefixRingOf<M, std::void_t<decltype(M::PREFIX_RING)>> { static constexpr bool value = M::PREFIX_RING; };
+
+constexpr uint32_t kRingRows = 256;   // rows of 32 voices in a warp's ring
+constexpr uint32_t kRingGroup = 32;   // rows per cp.async group
+constexpr uint32_t kRingAhead = 1024; // frames between the walk and its L2 prefetch
+
+template <class M>
+__global__ void __launch_bounds__(32) k_paint_prefix_ring(PaintArgs a, uint32_t seg_frames, uint32_t nseg, uint32_t vec4) {
+    extern __shared__ __align__(16) float ring[];  // [kRingRows][32]
+    constexpr uint32_t G = kRingGroup, NG = kRingRows / kRingGroup;
+    const uint32_t lane = threadIdx.x, v0 = blockIdx.x * 32u, v = v0 + lane;
+    const bool valid = v < a.V;
+    const size_t V = a.V;
+    const uint32_t f_stop = (nseg - 1) * seg_frames;  // the state at the last segment start is the last one anybody needs
+    const uint32_t ngroups = (f_stop + G - 1) / G;
+    const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(ring);
+    const uint32_t chunk = (lane & 7u) * 4u, rsub = lane >> 3;
+    auto issue = [&](uint32_t g) {
+        const uint32_t f0 = g * G, n = min(G, f_stop - f0);
+        const uint32_t base = ring_u32 + (g % NG) * G * 128u;
+        if (vec4) {  // a row = eight 16-byte chunks: four rows per warp instruction
+            if (v0 + chunk < a.V) {
+                const char* sp = reinterpret_cast<const char*>(a.in0 + ((size_t)(f0 + rsub) * V + v0 + chunk));
+                uint32_t dp = base + rsub * 128u + chunk * 4u;
+#pragma unroll 4
+                for (uint32_t j = rsub; j < n; j += 4) {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dp), "l"(sp) : "memory");
+                    sp += V * 16u;
+                    dp += 512u;
+                }
+            }
+        } else if (valid) {
+            const char* sp = reinterpret_cast<const char*>(a.in0 + ((size_t)f0 * V + v));
+            uint32_t dp = base + lane * 4u;
+#pragma unroll 4
+            for (uint32_t j = 0; j < n; j++) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
+                sp += V * 4u;
+                dp += 128u;
+            }
+        }
+        __pipeline_commit();
+    };
+    for (uint32_t g = 0; g + 1 < NG; g++) {
+        if (g < ngroups) issue(g); else __pipeline_commit();
+    }
+
+    M m;
+    uint32_t k = 0, ke = 0;
+    if (valid) {
+        m.load(a, v);
+        k = a.off[v];
+        ke = a.off[v + 1];
+    }
+    // the span under the cursor, and the one after it already on its way (a lone warp cannot hide the fetch behind others)
+    uint4 cur = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u), nxt = cur;
+    if (k < ke) cur = *reinterpret_cast<const uint4*>(a.spans + k);
+    if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
+    bool active = false;
+    PaintArgs row = a;
+    uint32_t s = 1, next_b = seg_frames;
+    auto record = [&]() {
+        row.state = (char*)a.prefix + (size_t)s * a.V * a.prefix_stride;
+        if (valid) m.store(row, v);
+        s++;
+        next_b += seg_frames;
+    };
+    for (uint32_t g = 0; g < ngroups; g++) {
+        __pipeline_wait_prior(NG - 2);
+        __syncwarp();  // group g has landed for every lane; every lane is done with the slot refilled next
+        if (g + NG - 1 < ngroups) issue(g + NG - 1); else __pipeline_commit();
+        const uint32_t f0 = g * G, n = min(G, f_stop - f0);
+        {
+            const uint32_t fr = f0 + kRingAhead + lane;
+            if (lane < n && fr < f_stop) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.in0 + (size_t)fr * V + v0));
+        }
+        const float* gp = ring + (size_t)(g % NG) * G * 32u + lane;
+        uint32_t j = 0;
+        while (j < n) {
+            const uint32_t f = f0 + j;
+            if (active && f == cur.y) {
+                m.end_span(a);
+                active = false;
+                k++;
+                cur = nxt;
+                nxt = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
+                if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
+            }
+            if (f == next_b) record();  // between the span that ended here and the one that starts here
+            if (!active && f == cur.x) {
+                m.begin_span(a, cur.w, cur.z, cur.y - cur.x);
+                active = true;
+            }
+            const uint32_t dist = (active ? cur.y : cur.x) - f;
+            const uint32_t run = min(min(n - j, next_b - f), __reduce_min_sync(0xffffffffu, dist));
+            if (active) {
+                // batches of eight frames, software-pipelined: the increments of the next batch (loads, multiplies, divisions)
+                // are computed in the shadow of this batch's chain of additions
+                const float* s0 = gp + j * 32u;
+                uint32_t r = 0;
+                if (run >= 8) {
+                    float d[8], xs[8];
+#pragma unroll
+                    for (int q = 0; q < 8; q++) xs[q] = s0[q * 32u];
+                    m.scan_prep(xs, d);
+                    for (r = 8; r + 8 <= run; r += 8) {
+                        float dn[8];
+#pragma unroll
+                        for (int q = 0; q < 8; q++) xs[q] = s0[(r + q) * 32u];
+                        m.scan_prep(xs, dn);
+                        m.scan_acc(d);
+#pragma unroll
+                        for (int q = 0; q < 8; q++) d[q] = dn[q];
+                    }
+                    m.scan_acc(d);
+                }
+                for (; r < run; r++) m.scan_sample(s0[r * 32u]);
+            }
+            j += run;
+        }
+    }
+    if (active && cur.y == f_stop) m.end_span(a);
+    while (s < nseg) record();
+}
+
 // cp.async.wait_group takes an immediate: dispatch the ring depths in use
 __device__ __forceinline__ void pipeline_wait_prior_rt(uint32_t n) {
     switch (n) {
@@ -219,7 +354,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     constexpr bool kScan = ScanOf<M>::value;
     const bool warm = kWarm && a.chain != nullptr;  // tolerance mode: segments start from a verified warm-up or the chain
     const bool scan = kScan && a.chain != nullptr;  // exact chained prefix sum: segments pass their integer state along
-    const bool segmented = M::SKIP || warm || scan;
+    const bool segmented = M::SKIP || warm || scan || (PrefixOf<M>::value && a.prefix != nullptr);
     const uint32_t f_begin = segmented ? by * seg_frames : 0u;
     const uint32_t f_end = segmented ? min(a.frames, f_begin + seg_frames) : a.frames;
     if (f_begin >= f_end) return;  // uniform over the CTA
@@ -232,19 +367,35 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const bool c_valid = v0 + c < a.V;
 
     bool inputs_only = false;  // scan pass: the refill skips the output buffer
+    // Row copies are address arithmetic more than anything else (one cp.async per 512-byte row and warp): the shared-memory
+    // address is a 32-bit offset bumped by a constant, the global one a pointer bumped by four rows.
+    const uint32_t smem_u32 = (uint32_t)__cvta_generic_to_shared(smem);
+    const size_t src_step = (size_t)V * sizeof(float) * rpp;
     auto copy_rows = [&](const float* buf, int slot, uint32_t stage, uint32_t f0, uint32_t n) {
-        const float* src = buf + (size_t)f0 * V + v0 + c;
-        float* dst = tile_ptr(stage, slot) + c;
+        const char* sp = reinterpret_cast<const char*>(buf + ((size_t)(f0 + r0) * V + v0 + c));
+        uint32_t dp = smem_u32 + (((stage * nb + slot) * T + r0) * RV + c) * 4u;
         if (vec4) {
-            for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 16);
+#pragma unroll 4
+            for (uint32_t j = r0; j < n; j += 4) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dp), "l"(sp) : "memory");
+                sp += src_step;
+                dp += 4u * RV * 4u;
+            }
         } else {
-            for (uint32_t j = r0; j < n; j += rpp) __pipeline_memcpy_async(dst + j * RV, src + (size_t)j * V, 4);
+#pragma unroll 4
+            for (uint32_t j = r0; j < n; j++) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
+                sp += src_step;
+                dp += RV * 4u;
+            }
         }
     };
+    uint32_t st_iss = 0, st_cur = 0;  // ring stage of the next tile to issue / to walk (tiles of a pass are taken in order)
     auto issue = [&](uint32_t tile) {
         const uint32_t f0 = tile * T;
         const uint32_t n = min(T, f_end - f0);
-        const uint32_t stage = tile % S;
+        const uint32_t stage = st_iss;
+        st_iss = st_iss + 1 == S ? 0u : st_iss + 1;
         if (c_valid) {
             // warm-up tiles (before the segment) only read the inputs: the output rows there belong to the previous segment
             if (!kWriteOnly && !(kWarm && f0 < f_begin) && !(kScan && inputs_only)) copy_rows(a.out, i_out, stage, f0, n);
@@ -283,7 +434,8 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         if (tile + S - 1 < ntiles) issue(tile + S - 1); else __pipeline_commit();
         const uint32_t f0 = tile * T;
         const uint32_t n = min(T, f_end - f0);
-        const uint32_t stage = tile % S;
+        const uint32_t stage = st_cur;
+        st_cur = st_cur + 1 == S ? 0u : st_cur + 1;
         float* so_t = tile_ptr(stage, i_out) + tid;
         const float* s0_t = i_in0 >= 0 ? tile_ptr(stage, i_in0) + tid : so_t;
         const float* s1_t = i_in1 >= 0 ? tile_ptr(stage, i_in1) + tid : so_t;
@@ -546,6 +698,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             const bool act_0 = active;
             m.scan_begin();
             inputs_only = true;
+            st_iss = st_cur = 0;
             for (uint32_t s = 0; s + 1 < S; s++) {
                 if (tile0 + s < ntiles) issue(tile0 + s); else __pipeline_commit();
             }
@@ -571,6 +724,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
         }
     }
     // the ring is primed before the skip-ahead so that its latency hides behind it
+    st_iss = st_cur = 0;
     for (uint32_t s = 0; s + 1 < S; s++) {
         if (tile_first + s < ntiles) issue(tile_first + s); else __pipeline_commit();
     }
