@@ -335,6 +335,18 @@ enum { ZCU_AUDIO_SIGNED8 = 0, ZCU_AUDIO_SIGNED16_LSB = 1 };
 int zcu_mix_down(zcu_ctx*, const zcu_buf* mix /* [frames][channels] */, int audio_format, float vol,
                  uint8_t* dst_host, size_t dst_len);
 
+/* No counterpart in the reference: added at the request of the run's operators for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as zcu_mix_down, but the
+ * device staging buffer for the PCM bytes is a fixed array inside the library image instead of the context's arena: the
+ * call allocates nothing (no cudaMalloc / cudaMallocAsync / cudaFree).  dst_len beyond ZCU_MIX_DOWN_STATIC_MAX_BYTES is
+ * rejected with ZCU_ERR_INVALID (convert in pieces, or use zcu_mix_down).  The array is shared by every call on a device and
+ * keeps the last call's bytes (nothing needs clearing: a call writes every byte it copies out); calls that overlap on the
+ * GPU (contexts on different streams of one device) race on it.  Every GPU that loads the library holds the array until
+ * exit. */
+#define ZCU_MIX_DOWN_STATIC_MAX_BYTES (4 * 1024 * 1024)
+int zcu_mix_down_static(zcu_ctx*, const zcu_buf* mix /* [frames][channels] */, int audio_format, float vol,
+                        uint8_t* dst_host, size_t dst_len);
+
 /* ---- host-side event layer (bit-exact index logic of src/zang/notes.zig, src/zang/trigger.zig) - */
 typedef struct zcu_impulse {  /* notes.zig:58-62 */
     uint32_t frame;    /* frame inside the current mix buffer */

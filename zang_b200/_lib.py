@@ -96,6 +96,7 @@ PROTOTYPES = {
     "zcu_mix_reduce": (_I, [_P, _P, _P, _U, _P]),
     "zcu_mix_ordered": (_I, [_P, _P, _P, _U, _P]),
     "zcu_mix_down": (_I, [_P, _P, _I, _F, _P, _S]),
+    "zcu_mix_down_static": (_I, [_P, _P, _I, _F, _P, _S]),
     "zcu_trigger_init": (None, [_P]),
     "zcu_trigger_reset": (None, [_P]),
     "zcu_trigger_run": (_U, [_P, _U, _U, _P, _P, _U, _U, _P, _U]),
