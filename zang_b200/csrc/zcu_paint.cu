@@ -197,7 +197,15 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         a.prefix_stride = (uint32_t)stride;
         if constexpr (PrefixRingOf<M>::value) {
             const bool v4 = a.V % 4 == 0 && ((uintptr_t)a.in0 & 15u) == 0;
-            k_paint_prefix_ring<M><<<(a.V + 31) / 32, 32, kRingRows * 32 * sizeof(float), ctx->stream>>>(a, p.seg_frames, p.nseg, v4 ? 1u : 0u);
+            auto pk = k_paint_prefix_ring<M>;
+            constexpr size_t ring_bytes = kRingRows * 32 * sizeof(float);
+            if (!ctx->attr_done.count((const void*)pk)) {
+                ZCU_CUDA(ctx, cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes));
+                ctx->attr_done.insert((const void*)pk);
+            }
+            uint32_t ahead = kRingAhead;
+            if (const char* e = getenv("ZCU_RING_AHEAD")) ahead = (uint32_t)std::max(0, atoi(e));  // tuning
+            pk<<<(a.V + 31) / 32, kRingThreads, ring_bytes, ctx->stream>>>(a, p.seg_frames, p.nseg, v4 ? 1u : 0u, ahead);
         } else {
             k_paint_prefix<M><<<(a.V + 127) / 128, 128, 0, ctx->stream>>>(a, p.seg_frames, p.nseg);
         }

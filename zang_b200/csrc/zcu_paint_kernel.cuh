@@ -154,72 +154,106 @@ __global__ void __launch_bounds__(128) k_paint_prefix(PaintArgs a, uint32_t seg_
 
 // M::PREFIX_RING (with M::PREFIX): the carried state is an order-dependent f32 sum over an input buffer (the phase of SineOsc /
 // TriSawOsc / Cycle driven by a frequency buffer): no skip-ahead exists and the per-voice walk has to read every input sample,
-// but one step of it is a multiply and an add where a painted sample costs a sine.  k_paint_prefix_ring is that walk, alone
-// on the machine before the paint launch: one warp per 32 voices in frame lockstep, the input rows (128 bytes per warp and
-// frame) staged through a 32 KB cp.async ring per warp, eight frames per batch so that only the additions are a dependent
-// chain, the state recorded at every segment start like k_paint_prefix does.  The paint launch then runs its time segments
-// in parallel from those rows.
+// but one step of it is a multiply (or an exact division) and an add where a painted sample costs a sine.
+// k_paint_prefix_ring is that walk, alone on the machine before the paint launch.  One CTA per 32 voices, lane = voice, the
+// input rows (128 bytes per frame) staged through a 64 KB cp.async ring in groups of 32 frames.  Only the additions are a
+// dependent chain, so only they stay with the one warp that walks the frames (warp 0: span boundaries, the adds, the state
+// recorded at every segment start like k_paint_prefix does); eight producer warps issue the copies and turn the landed input
+// samples into increments in place, one group ahead (each with a span cursor of its own, for the span constants of its
+// rows).  The module's begin_span() must leave the carried state alone (it only derives span constants): the walker does
+// not call it.  The paint launch then runs its time segments in parallel from the recorded rows.
 template <class M, class = void>
 struct PrefixRingOf { static constexpr bool value = false; };
 template <class M>
 struct PrefixRingOf<M, std::void_t<decltype(M::PREFIX_RING)>> { static constexpr bool value = M::PREFIX_RING; };
 
-constexpr uint32_t kRingRows = 256;   // rows of 32 voices in a warp's ring
-constexpr uint32_t kRingGroup = 32;   // rows per cp.async group
-constexpr uint32_t kRingAhead = 1024; // frames between the walk and its L2 prefetch
+constexpr uint32_t kRingRows = 512;    // rows of 32 voices in a CTA's ring
+constexpr uint32_t kRingGroup = 64;    // rows per cp.async group
+constexpr uint32_t kRingAhead = 1024;  // frames between the walk and its L2 prefetch
+constexpr uint32_t kRingProducers = 8; // producer warps (two per scheduler: they hide each other's latencies)
+constexpr uint32_t kRingThreads = 32 * (1 + kRingProducers);  // warp 0 walks
 
 template <class M>
-__global__ void __launch_bounds__(32) k_paint_prefix_ring(PaintArgs a, uint32_t seg_frames, uint32_t nseg, uint32_t vec4) {
+__global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a, uint32_t seg_frames, uint32_t nseg, uint32_t vec4, uint32_t ahead) {
     extern __shared__ __align__(16) float ring[];  // [kRingRows][32]
     constexpr uint32_t G = kRingGroup, NG = kRingRows / kRingGroup;
-    const uint32_t lane = threadIdx.x, v0 = blockIdx.x * 32u, v = v0 + lane;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const uint32_t v0 = blockIdx.x * 32u, v = v0 + lane;
     const bool valid = v < a.V;
     const size_t V = a.V;
     const uint32_t f_stop = (nseg - 1) * seg_frames;  // the state at the last segment start is the last one anybody needs
-    const uint32_t ngroups = (f_stop + G - 1) / G;
+    const int ngroups = (int)((f_stop + G - 1) / G);
     const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(ring);
-    const uint32_t chunk = (lane & 7u) * 4u, rsub = lane >> 3;
-    auto issue = [&](uint32_t g) {
-        const uint32_t f0 = g * G, n = min(G, f_stop - f0);
-        const uint32_t base = ring_u32 + (g % NG) * G * 128u;
-        if (vec4) {  // a row = eight 16-byte chunks: four rows per warp instruction
-            if (v0 + chunk < a.V) {
-                const char* sp = reinterpret_cast<const char*>(a.in0 + ((size_t)(f0 + rsub) * V + v0 + chunk));
-                uint32_t dp = base + rsub * 128u + chunk * 4u;
-#pragma unroll 4
-                for (uint32_t j = rsub; j < n; j += 4) {
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dp), "l"(sp) : "memory");
-                    sp += V * 16u;
-                    dp += 512u;
+    const bool producer = warp != 0;
+    constexpr uint32_t P = kRingProducers;
+    const uint32_t pt = tid - 32u;  // producer thread
+    // producers: the rows of the next group on their way into the next slot.  Groups are issued in order, so everything is a
+    // running value: source pointer of this thread's first row, slot offset, prefetch pointer.
+    const uint32_t chunk = vec4 ? (pt & 7u) * 4u : lane, rsub = vec4 ? pt >> 3 : pt >> 5;
+    const bool col_ok = v0 + chunk < a.V;
+    const uint32_t rstep = vec4 ? 4u * P : P;                      // rows between two copies of a thread
+    const size_t src_rstep = (size_t)V * 4u * rstep, src_gstep = (size_t)V * 4u * G;
+    const uint32_t dst_rstep = rstep * 128u;
+    const char* iss_src = reinterpret_cast<const char*>(a.in0 + ((size_t)rsub * V + v0 + chunk));
+    // L2 prefetch, one 32-byte sector per producer thread (a prefetch brings in the sector it names, not the 128-byte line)
+    const uint32_t pf_row = pt >> 2, pf_col = (pt & 3u) * 8u;
+    const bool pf_ok = pf_row < G && v0 + pf_col < a.V;
+    const char* iss_pf = reinterpret_cast<const char*>(a.in0 + ((size_t)(ahead + pf_row) * V + v0 + pf_col));
+    uint32_t iss_slot = 0, iss_f0 = 0;
+    auto issue = [&]() {
+        if (iss_f0 < f_stop) {
+            const uint32_t n = min(G, f_stop - iss_f0);
+            const char* sp = iss_src;
+            uint32_t dp = ring_u32 + iss_slot * (G * 128u) + rsub * 128u + chunk * 4u;
+            if (col_ok) {
+                if (vec4) {  // a row = eight 16-byte chunks: 4 P rows per pass of the producer threads
+#pragma unroll
+                    for (uint32_t j = 0; j < G / (4u * P); j++) {
+                        if (rsub + j * 4u * P < n) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dp), "l"(sp) : "memory");
+                        sp += src_rstep;
+                        dp += dst_rstep;
+                    }
+                } else {
+#pragma unroll
+                    for (uint32_t j = 0; j < G / P; j++) {
+                        if (rsub + j * P < n) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
+                        sp += src_rstep;
+                        dp += dst_rstep;
+                    }
                 }
             }
-        } else if (valid) {
-            const char* sp = reinterpret_cast<const char*>(a.in0 + ((size_t)f0 * V + v));
-            uint32_t dp = base + lane * 4u;
-#pragma unroll 4
-            for (uint32_t j = 0; j < n; j++) {
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
-                sp += V * 4u;
-                dp += 128u;
-            }
+            // the rows kRingAhead frames further on are pulled into L2
+            if (pf_ok && ahead != 0u && iss_f0 + ahead + pf_row < f_stop) asm volatile("prefetch.global.L2 [%0];" ::"l"(iss_pf));
+            iss_src += src_gstep;
+            iss_pf += src_gstep;
+            iss_f0 += G;
+            iss_slot = iss_slot + 1 == NG ? 0u : iss_slot + 1;
         }
         __pipeline_commit();
     };
-    for (uint32_t g = 0; g + 1 < NG; g++) {
-        if (g < ngroups) issue(g); else __pipeline_commit();
+    if (producer) {
+        for (int g = 0; g + 2 < (int)NG; g++) issue();  // groups 0 .. NG-3
     }
 
-    M m;
+    M m = M();
     uint32_t k = 0, ke = 0;
     if (valid) {
-        m.load(a, v);
+        if (!producer) m.load(a, v);
         k = a.off[v];
         ke = a.off[v + 1];
     }
     // the span under the cursor, and the one after it already on its way (a lone warp cannot hide the fetch behind others)
-    uint4 cur = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u), nxt = cur;
+    const uint4 kNoSpan = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
+    uint4 cur = kNoSpan, nxt = kNoSpan;
     if (k < ke) cur = *reinterpret_cast<const uint4*>(a.spans + k);
     if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
+    auto next_span = [&]() {
+        k++;
+        cur = nxt;
+        nxt = kNoSpan;
+        if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
+    };
+    // walker state
     bool active = false;
     PaintArgs row = a;
     uint32_t s = 1, next_b = seg_frames;
@@ -229,60 +263,103 @@ __global__ void __launch_bounds__(32) k_paint_prefix_ring(PaintArgs a, uint32_t 
         s++;
         next_b += seg_frames;
     };
-    for (uint32_t g = 0; g < ngroups; g++) {
-        __pipeline_wait_prior(NG - 2);
-        __syncwarp();  // group g has landed for every lane; every lane is done with the slot refilled next
-        if (g + NG - 1 < ngroups) issue(g + NG - 1); else __pipeline_commit();
-        const uint32_t f0 = g * G, n = min(G, f_stop - f0);
-        {
-            const uint32_t fr = f0 + kRingAhead + lane;
-            if (lane < n && fr < f_stop) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.in0 + (size_t)fr * V + v0));
-        }
-        const float* gp = ring + (size_t)(g % NG) * G * 32u + lane;
-        uint32_t j = 0;
-        while (j < n) {
-            const uint32_t f = f0 + j;
-            if (active && f == cur.y) {
-                m.end_span(a);
-                active = false;
-                k++;
-                cur = nxt;
-                nxt = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
-                if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
-            }
-            if (f == next_b) record();  // between the span that ended here and the one that starts here
-            if (!active && f == cur.x) {
-                m.begin_span(a, cur.w, cur.z, cur.y - cur.x);
-                active = true;
-            }
-            const uint32_t dist = (active ? cur.y : cur.x) - f;
-            const uint32_t run = min(min(n - j, next_b - f), __reduce_min_sync(0xffffffffu, dist));
-            if (active) {
-                // batches of eight frames, software-pipelined: the increments of the next batch (loads, multiplies, divisions)
-                // are computed in the shadow of this batch's chain of additions
-                const float* s0 = gp + j * 32u;
-                uint32_t r = 0;
-                if (run >= 8) {
-                    float d[8], xs[8];
-#pragma unroll
-                    for (int q = 0; q < 8; q++) xs[q] = s0[q * 32u];
-                    m.scan_prep(xs, d);
-                    for (r = 8; r + 8 <= run; r += 8) {
-                        float dn[8];
-#pragma unroll
-                        for (int q = 0; q < 8; q++) xs[q] = s0[(r + q) * 32u];
-                        m.scan_prep(xs, dn);
-                        m.scan_acc(d);
-#pragma unroll
-                        for (int q = 0; q < 8; q++) d[q] = dn[q];
+    // producer state: the span whose constants m holds, the slot of the next group to prepare
+    uint32_t k_consts = 0xFFFFFFFFu, prep_slot = 0;
+    uint32_t walk_slot = 0;
+
+    // iteration i: group i + 1 has landed (barrier), group i + NG - 1 is issued into the slot of group i - 1, the producers turn
+    // group i + 1 into increments while the walker adds up group i
+    for (int i = -1; i < ngroups; i++) {
+        if (producer) __pipeline_wait_prior(NG - 3);
+        __syncthreads();
+        if (producer) {
+            issue();  // group i + NG - 1
+            const int g = i + 1;
+            if (g < ngroups) {
+                const uint32_t f0 = (uint32_t)g * G, n = min(G, f_stop - f0);
+                float* gp0 = ring + (size_t)prep_slot * G * 32u + lane;
+                prep_slot = prep_slot + 1 == NG ? 0u : prep_slot + 1;
+#pragma unroll 1
+                for (uint32_t r0 = (warp - 1u) * (G / P), re = r0 + G / P; r0 < re && r0 < n; r0 += 8u) {
+                    float* gp = gp0 + r0 * 32u;
+                    const uint32_t fa = f0 + r0, nr = min(8u, n - r0);
+                    while (cur.y <= fa) next_span();
+                    const bool whole = cur.x <= fa && cur.y >= fa + nr;  // every row of mine inside the span under the cursor
+                    const bool none = cur.x >= fa + nr;                  // ... or before it
+                    if (whole && k != k_consts) {
+                        m.begin_span(a, cur.w, cur.z, cur.y - cur.x);
+                        k_consts = k;
                     }
-                    m.scan_acc(d);
+                    if (nr == 8u && __all_sync(0xffffffffu, whole || none)) {
+                        float xs[8], d[8];  // lanes outside every span compute values nobody reads
+#pragma unroll
+                        for (int q = 0; q < 8; q++) xs[q] = gp[q * 32];
+                        m.scan_prep(xs, d);
+#pragma unroll
+                        for (int q = 0; q < 8; q++) gp[q * 32] = d[q];
+                    } else {
+                        for (uint32_t r = 0; r < nr; r++) {
+                            const uint32_t f = fa + r;
+                            while (cur.y <= f) next_span();
+                            if (cur.x <= f) {
+                                if (k != k_consts) {
+                                    m.begin_span(a, cur.w, cur.z, cur.y - cur.x);
+                                    k_consts = k;
+                                }
+                                gp[r * 32] = m.scan_prep1(gp[r * 32]);
+                            }
+                        }
+                    }
                 }
-                for (; r < run; r++) m.scan_sample(s0[r * 32u]);
             }
-            j += run;
+        } else if (i >= 0) {
+            const uint32_t f0 = (uint32_t)i * G, n = min(G, f_stop - f0);
+            const float* gp = ring + (size_t)walk_slot * G * 32u + lane;
+            walk_slot = walk_slot + 1 == NG ? 0u : walk_slot + 1;
+            uint32_t j = 0;
+            while (j < n) {
+                const uint32_t f = f0 + j;
+                if (active && f == cur.y) {
+                    m.end_span(a);
+                    active = false;
+                    next_span();
+                }
+                if (f == next_b) record();  // between the span that ended here and the one that starts here
+                if (!active && f == cur.x) active = true;
+                const uint32_t dist = (active ? cur.y : cur.x) - f;
+                const uint32_t run = min(min(n - j, next_b - f), __reduce_min_sync(0xffffffffu, dist));
+                if (active) {
+                    const float* s0 = gp + j * 32u;
+                    uint32_t r = 0;
+                    // the common case is a run over the whole group: all the loads first, then the chain of additions
+                    if (run == G) {
+                        float d[G / 8][8];
+#pragma unroll
+                        for (int q = 0; q < (int)G; q++) d[q >> 3][q & 7] = s0[q * 32];
+#pragma unroll
+                        for (int b = 0; b < (int)G / 8; b++) m.scan_acc(d[b]);
+                        r = G;
+                    }
+                    for (; r + 32 <= run; r += 32) {
+                        float d[4][8];
+#pragma unroll
+                        for (int q = 0; q < 32; q++) d[q >> 3][q & 7] = s0[(r + q) * 32u];
+#pragma unroll
+                        for (int b = 0; b < 4; b++) m.scan_acc(d[b]);
+                    }
+                    for (; r + 8 <= run; r += 8) {
+                        float d[8];
+#pragma unroll
+                        for (int q = 0; q < 8; q++) d[q] = s0[(r + q) * 32u];
+                        m.scan_acc(d);
+                    }
+                    for (; r < run; r++) m.scan_add(s0[r * 32u]);
+                }
+                j += run;
+            }
         }
     }
+    if (producer) return;
     if (active && cur.y == f_stop) m.end_span(a);
     while (s < nseg) record();
 }
