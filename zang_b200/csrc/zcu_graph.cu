@@ -990,6 +990,7 @@ int zcu_graph_paint(zcu_ctx* ctx, zcu_graph* g, const zcu_spans* const* tables, 
         p.state = fd.bank ? fd.bank->d : nullptr;
         p.line = fd.bank ? fd.bank->line : nullptr;
         p.delay_samples = fd.bank ? fd.bank->delay_samples : 0;
+        p.line_ring = 0;
         if (kind == ZCU_MOD_CURVE) {
             ZCU_REQUIRE(ctx, fd.d_nodes != nullptr, "a Curve field has no nodes (zcu_graph_set_curve_nodes)");
             p.nodes = (const zcu_curve_node*)fd.d_nodes;

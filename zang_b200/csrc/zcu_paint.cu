@@ -129,6 +129,10 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     // tolerance mode reads the inputs of the frames before a segment while the previous segment is still painting them:
     // only possible when no input aliases the output
     const size_t n = (size_t)a.V * a.frames;
+    // delay modules: a line longer than any prefetch queue (S * T <= 8 * 16 slots) rides the cp.async ring, as one more
+    // staged buffer of the launch geometry
+    a.line_ring = (LineRingOf<M>::value && a.delay_samples >= 256 && !getenv("ZCU_PAINT_NO_LINE_RING")) ? 1u : 0u;
+    if (a.line_ring) nb++;
     const bool warm = WarmOf<M>::value && ctx->paint_mode == ZCU_PAINT_TOLERANCE && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
                       !overlaps(a.out, a.in2, n);
     bool skip = M::SKIP;

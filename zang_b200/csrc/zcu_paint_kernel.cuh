@@ -106,6 +106,29 @@ struct ScanCall { static __device__ __forceinline__ void sample(M&, float, float
 template <class M>
 struct ScanCall<M, true> { static __device__ __forceinline__ void sample(M& m, float x0, float x1, float x2) { m.scan_sample(x0, x1, x2); } };
 
+// M::LINE_RING: delay modules.  The k-th painted sample of a call uses line slot index0 + k, whatever frame it falls on, so the
+// line can be fetched in slot order ahead of time: every tile that is issued into the cp.async ring takes up to T more slots
+// of each voice's line with it, into a per-thread queue of S * T entries behind the tile ring (one more staged buffer in the
+// launch geometry).  A tile paints at most T frames, so the slots it needs have landed with it (and a slot is only fetched
+// when fewer than S * T are outstanding, which also keeps the fetch behind the last write to that slot as long as the line
+// is longer than the queue).  Without it a delay module waits for one global-memory round trip per four frames.
+template <class M, class = void>
+struct LineRingOf { static constexpr bool value = false; };
+template <class M>
+struct LineRingOf<M, std::void_t<decltype(M::LINE_RING)>> { static constexpr bool value = M::LINE_RING; };
+template <class M, bool = LineRingOf<M>::value>
+struct LineRingCall {
+    static __device__ __forceinline__ void bind(M&, const float*, uint32_t, uint32_t) {}
+    static __device__ __forceinline__ uint32_t taken(M&) { return 0; }
+    static __device__ __forceinline__ uint32_t index(M&) { return 0; }
+};
+template <class M>
+struct LineRingCall<M, true> {
+    static __device__ __forceinline__ void bind(M& m, const float* q, uint32_t stride, uint32_t L) { m.delay_line().ring_bind(q, stride, L); }
+    static __device__ __forceinline__ uint32_t taken(M& m) { return m.delay_line().taken; }
+    static __device__ __forceinline__ uint32_t index(M& m) { return m.delay_line().index; }
+};
+
 // m.advance_done() for modules whose advance() only accumulates (M::LAZY)
 template <class M, class = void>
 struct LazyCall { static __device__ __forceinline__ void done(M&) {} };
@@ -443,6 +466,11 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const uint32_t c = (tid % cpr) * cw, r0 = tid / cpr;
     const bool c_valid = v0 + c < a.V;
 
+    M m;
+    // delay modules: the line prefetch queue behind the tile ring, [S * T][RV]
+    const bool line_ring = LineRingOf<M>::value && a.line_ring != 0u;
+    const uint32_t lq_len = S * T;
+    uint32_t lq_pos = 0, lq_slot = 0, lq_total = 0;  // next queue entry / line slot to fetch, slots fetched so far
     bool inputs_only = false;  // scan pass: the refill skips the output buffer
     // Row copies are address arithmetic more than anything else (one cp.async per 512-byte row and warp): the shared-memory
     // address is a 32-bit offset bumped by a constant, the global one a pointer bumped by four rows.
@@ -480,15 +508,41 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             if (M::NIN >= 2 && i_in1 >= 0) copy_rows(a.in1, i_in1, stage, f0, n);
             if (M::NIN >= 3 && i_in2 >= 0) copy_rows(a.in2, i_in2, stage, f0, n);
         }
+        if constexpr (LineRingOf<M>::value) {
+            if (line_ring && valid) {
+                const uint32_t np = min(T, lq_len - (lq_total - LineRingCall<M>::taken(m)));
+                const char* sp = reinterpret_cast<const char*>(a.line + ((size_t)lq_slot * V + v));
+                uint32_t dp = smem_u32 + ((S * nb * T + lq_pos) * RV + tid) * 4u;
+                for (uint32_t j = 0; j < np; j++) {
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
+                    lq_slot++;
+                    sp += V * sizeof(float);
+                    if (lq_slot == a.delay_samples) {
+                        lq_slot = 0;
+                        sp = reinterpret_cast<const char*>(a.line + v);
+                    }
+                    lq_pos++;
+                    dp += RV * 4u;
+                    if (lq_pos == lq_len) {
+                        lq_pos = 0;
+                        dp = smem_u32 + (S * nb * T * RV + tid) * 4u;
+                    }
+                }
+                lq_total += np;
+            }
+        }
         __pipeline_commit();
     };
 
-    M m;
     uint32_t k = 0, ke = 0;
     if (valid) {
         m.load(a, v);
         k = a.off[v];
         ke = a.off[v + 1];
+        if (line_ring) {
+            LineRingCall<M>::bind(m, smem + (size_t)S * nb * T * RV + tid, RV, lq_len);
+            lq_slot = LineRingCall<M>::index(m);
+        }
     }
     uint32_t s_start = 0xFFFFFFFFu, s_end = 0xFFFFFFFFu, s_flags = 0, s_param = 0;
     if (k < ke) {
