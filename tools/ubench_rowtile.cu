@@ -256,9 +256,14 @@ int main() {
         auto report = [&](const char* name, float ms) { printf("V=%6u frames=%6u %-28s T=%3u nseg=%3u  %8.3f ms  %7.1f GB/s\n", cfg.V, cfg.frames, name, g_T, g_nseg, ms, gb / (ms * 1e-3)); fflush(stdout); };
         // correctness of each variant: count increments
         int launches = 0;
-        for (uint32_t nseg : {1u, 4u, 16u, 27u, 64u}) {
+        // ROWTILE_ONESEG=1: only the 4096-voice buffer, cut into 1, 2 or 4 segments (what a launch looks like that cannot be
+        // cut in time: few CTAs, all of them walking the same narrow window of rows)
+        const bool oneseg = getenv("ROWTILE_ONESEG") != nullptr;
+        if (oneseg && cfg.V != 4096) { CK(cudaFree(buf)); continue; }
+        for (uint32_t nseg : {1u, 2u, 4u, 16u, 27u, 64u}) {
+            if (oneseg != (nseg == 1 || nseg == 2 || (nseg == 4 && cfg.V == 4096))) { if (!(cfg.V == 65536 && (nseg == 1 || nseg == 4) && !oneseg)) continue; }
             if (cfg.V == 65536 && nseg > 4) continue;
-            if (cfg.V == 4096 && nseg < 16) continue;
+            if (cfg.V == 4096 && nseg < 16 && !oneseg) continue;
             g_nseg = nseg;
             for (uint32_t T : {16u, 32u, 64u}) {
                 g_T = T;

@@ -132,7 +132,8 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     // delay modules: a line longer than any prefetch queue (S * T <= 8 * 16 slots) rides the cp.async ring, as one more
     // staged buffer of the launch geometry
     a.line_ring = (LineRingOf<M>::value && a.delay_samples >= 256 && !getenv("ZCU_PAINT_NO_LINE_RING")) ? 1u : 0u;
-    if (a.line_ring) nb++;
+    const bool nb_line = a.line_ring != 0u;  // nb counts the line queue as a staged buffer
+    if (nb_line) nb++;
     const bool warm = WarmOf<M>::value && ctx->paint_mode == ZCU_PAINT_TOLERANCE && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
                       !overlaps(a.out, a.in2, n);
     bool skip = M::SKIP;
@@ -159,6 +160,42 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     if (ring && p.nseg < 4 && !getenv("ZCU_PAINT_SEGMENTS")) {
         ring = false;
         p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, 8u);
+    }
+    // A module that has to walk its frames in order, on a bank too small to fill the machine with 128-voice CTAs: the walker /
+    // producer kernel (k_paint_walk).  One walker warp per CTA, so the bank is cut into as many CTAs as the SMs' four
+    // schedulers can hold: 32, 16 or 8 voices each (narrower rows, idle lanes, but that many more walkers).  Delay modules
+    // need a line longer than the prefetch queue.
+    {
+        const bool one_segment = !(skip || warm || scan || ring);
+        const bool ovr_now = ctx->paint_output == ZCU_OUT_OVERWRITE && !WriteOnlyOf<M>::value;
+        const uint32_t sms = (uint32_t)ctx->sm_count;
+        uint32_t rw = 32;  // narrower CTAs (more walkers) measured no faster: see DESIGN.md §4.1
+        if (const char* e = getenv("ZCU_PAINT_WALK_VOICES")) rw = (uint32_t)std::min(32, std::max(8, atoi(e))) & ~7u;  // tuning: 8, 16, 32
+        if (rw == 24) rw = 16;
+        const uint32_t ctas = (a.V + rw - 1) / rw;
+        const bool line_ok = !LineRingOf<M>::value || a.delay_samples >= kWalkGroup * kWalkGroups + 64u;
+        uint32_t max_ctas = 4 * sms;
+        if (const char* e = getenv("ZCU_PAINT_WALK_MAX_CTAS")) max_ctas = (uint32_t)std::max(1, atoi(e));  // tuning
+        if (one_segment && !WriteOnlyOf<M>::value && !ovr_now && ctas <= max_ctas && line_ok && a.frames > 0 && !getenv("ZCU_PAINT_NO_WALK")) {
+            a.line_ring = LineRingOf<M>::value ? 1u : 0u;
+            a.chain = nullptr;
+            a.prefix = nullptr;
+            auto al16 = [](const void* q) { return ((uintptr_t)q & 15u) == 0; };
+            const uint32_t v4 = (a.V % 4 == 0 && al16(a.out) && al16(a.in0) && al16(a.in1) && al16(a.in2)) ? 1u : 0u;
+            const int nb_tiles = nb - (nb_line ? 1 : 0);  // output + inputs
+            const size_t group = (size_t)(nb_tiles + (a.line_ring ? 1 : 0)) * kWalkGroup * rw * sizeof(float);
+            const uint32_t per_sm = std::min(4u, (ctas + sms - 1) / sms);
+            const uint32_t ng = (size_t)kWalkGroups * group * per_sm <= (size_t)kPaintMaxSmem ? kWalkGroups : kWalkGroups / 2;
+            auto wk = k_paint_walk<M>;
+            if (!ctx->attr_done.count((const void*)wk)) {
+                ZCU_CUDA(ctx, cudaFuncSetAttribute(wk, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
+                ctx->attr_done.insert((const void*)wk);
+            }
+            wk<<<ctas, kWalkThreads, ng * group, ctx->stream>>>(a, v4, rw, ng);
+            ctx->launches++;
+            ZCU_CUDA(ctx, cudaGetLastError());
+            return ZCU_OK;
+        }
     }
     a.chain = nullptr;
     a.chain_flags = nullptr;

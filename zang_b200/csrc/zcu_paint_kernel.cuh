@@ -400,6 +400,246 @@ __device__ __forceinline__ void pipeline_wait_prior_rt(uint32_t n) {
     }
 }
 
+// ---- k_paint_walk: modules that cannot be cut in time, on banks too small to fill the machine ----------------------------
+// A module without a skip-ahead (the delay modules, the FM oscillator, the Filter in exact mode) walks its frames in order;
+// with 4096 voices that is 128 warps on 592 schedulers, each paying for its own tile copies, ring bookkeeping and write-back
+// at one dependent instruction every ~3.6 cycles (ncu: SimpleDelay 62 instructions per warp and frame, 28 % issue).  Here a CTA
+// is 32 voices (one CTA per SM up to 4736 voices): warp 0 walks the frames and does nothing but the module (operands from the
+// tiles in shared memory, results back into the output tile, delay-line stores to global); warps 2 and 3 issue the cp.async
+// copies of the output and input tiles (groups of 32 frames, eight groups in the ring) and write finished output tiles back;
+// warp 1 fetches the delay line in slot order (M::LINE_RING above; idle for other modules).  One barrier per group.
+constexpr uint32_t kWalkGroup = 32;    // frames per group
+constexpr uint32_t kWalkGroups = 8;    // groups in the ring, at most
+constexpr uint32_t kWalkThreads = 128;
+
+template <class M>
+__global__ void __launch_bounds__(kWalkThreads) k_paint_walk(PaintArgs a, uint32_t vec4, uint32_t RW, uint32_t NG) {
+    extern __shared__ __align__(16) float smem[];
+    // RW = voices of this CTA (32, 16 or 8: rows of RW floats, lanes >= RW idle), NG = groups in the ring
+    constexpr uint32_t G = kWalkGroup;
+    const uint32_t L = G * NG;
+    __shared__ uint32_t s_taken[32];
+    __shared__ uint32_t s_painted[kWalkGroups];
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+    const uint32_t v0 = blockIdx.x * RW, v = v0 + lane;
+    const bool valid = lane < RW && v < a.V;
+    const size_t V = a.V;
+    const uint32_t frames = a.frames;
+    const int ngroups = (int)((frames + G - 1) / G);
+    // staged buffers: slot 0 = output, then the inputs that are present
+    int nb = 1;
+    int i_in0 = -1, i_in1 = -1, i_in2 = -1;
+    if (M::NIN >= 1 && a.in0) i_in0 = nb++;
+    if (M::NIN >= 2 && a.in1) i_in1 = nb++;
+    if (M::NIN >= 3 && a.in2) i_in2 = nb++;
+    // smem: [NG][nb][G][32] tiles, then the line queue [L][32]
+    const uint32_t smem_u32 = (uint32_t)__cvta_generic_to_shared(smem);
+    float* lq = smem + (size_t)NG * nb * G * RW;
+    const bool line_ring = LineRingOf<M>::value && a.line_ring != 0u;
+    if (tid < 32) s_taken[tid] = 0;
+    if (tid < NG) s_painted[tid] = 0;
+
+    // ---- producers -----------------------------------------------------------------------------------------------------
+    const uint32_t pt = tid - 64u;  // tile-copy thread 0..63 (warps 2, 3)
+    const uint32_t cpr = vec4 ? RW / 4u : RW;  // copies per row
+    const uint32_t chunk = (pt % cpr) * (vec4 ? 4u : 1u), rsub = pt / cpr;
+    const uint32_t rstep = 64u / cpr;           // rows per pass of the 64 copy threads
+    const bool col_ok = v0 + chunk < a.V;
+    uint32_t iss_slot = 0, iss_f0 = 0;
+    uint32_t lq_pos = 0, lq_slot = 0, lq_total = 0;
+    auto copy_buf = [&](const float* buf, int b, uint32_t n) {
+        const char* sp = reinterpret_cast<const char*>(buf + ((size_t)(iss_f0 + rsub) * V + v0 + chunk));
+        uint32_t dp = smem_u32 + (((iss_slot * nb + b) * G + rsub) * RW + chunk) * 4u;
+        const size_t sstep = V * 4u * rstep;
+        const uint32_t dstep = rstep * RW * 4u;
+        if (vec4) {
+#pragma unroll 4
+            for (uint32_t j = rsub; j < n; j += rstep) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dp), "l"(sp) : "memory");
+                sp += sstep;
+                dp += dstep;
+            }
+        } else {
+#pragma unroll 4
+            for (uint32_t j = rsub; j < n; j += rstep) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
+                sp += sstep;
+                dp += dstep;
+            }
+        }
+    };
+    auto issue = [&]() {  // the next group into the next slot (groups are issued in order)
+        if (iss_f0 < frames) {
+            const uint32_t n = min(G, frames - iss_f0);
+            if (warp >= 2 && col_ok) {
+                copy_buf(a.out, 0, n);
+                if (M::NIN >= 1 && i_in0 >= 0) copy_buf(a.in0, i_in0, n);
+                if (M::NIN >= 2 && i_in1 >= 0) copy_buf(a.in1, i_in1, n);
+                if (M::NIN >= 3 && i_in2 >= 0) copy_buf(a.in2, i_in2, n);
+            }
+            if constexpr (LineRingOf<M>::value) {
+                if (warp == 1 && line_ring && valid) {
+                    const uint32_t np = min(G, L - (lq_total - s_taken[lane]));
+                    const char* sp = reinterpret_cast<const char*>(a.line + ((size_t)lq_slot * V + v));
+                    uint32_t dp = smem_u32 + ((NG * nb * G + lq_pos) * RW + lane) * 4u;
+                    uint32_t done = 0;
+                    while (done < np) {  // straight pieces: up to the wrap of the line or of the queue
+                        const uint32_t piece = min(np - done, min(a.delay_samples - lq_slot, L - lq_pos));
+#pragma unroll 4
+                        for (uint32_t j = 0; j < piece; j++) {
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dp), "l"(sp) : "memory");
+                            sp += V * 4u;
+                            dp += RW * 4u;
+                        }
+                        done += piece;
+                        lq_slot += piece;
+                        lq_pos += piece;
+                        if (lq_slot == a.delay_samples) {
+                            lq_slot = 0;
+                            sp = reinterpret_cast<const char*>(a.line + v);
+                        }
+                        if (lq_pos == L) {
+                            lq_pos = 0;
+                            dp = smem_u32 + (NG * nb * G * RW + lane) * 4u;
+                        }
+                    }
+                    lq_total += np;
+                }
+            }
+            iss_f0 += G;
+            iss_slot = iss_slot + 1 == NG ? 0u : iss_slot + 1;
+        }
+        __pipeline_commit();
+    };
+    auto write_back = [&](uint32_t slot, uint32_t f0) {  // finished output tile -> HBM (rows of 128 bytes)
+        if (warp < 2 || !col_ok || !s_painted[slot]) return;
+        const uint32_t n = min(G, frames - f0);
+        const float* st = smem + ((size_t)(slot * nb) * G + rsub) * RW + chunk;
+        float* dg = a.out + ((size_t)(f0 + rsub) * V + v0 + chunk);
+        if (vec4) {
+#pragma unroll 4
+            for (uint32_t j = rsub; j < n; j += rstep) {
+                *reinterpret_cast<float4*>(dg) = *reinterpret_cast<const float4*>(st);
+                dg += V * rstep;
+                st += rstep * RW;
+            }
+        } else {
+#pragma unroll 4
+            for (uint32_t j = rsub; j < n; j += rstep) {
+                *dg = *st;
+                dg += V * rstep;
+                st += rstep * RW;
+            }
+        }
+    };
+    if constexpr (LineRingOf<M>::value) {
+        if (warp == 1 && line_ring && valid) {  // the line is fetched from the bank's index on
+            M mp;
+            mp.load(a, v);
+            lq_slot = LineRingCall<M>::index(mp);
+        }
+    }
+    __syncthreads();
+    const bool producer = warp != 0;
+    if (producer) {
+        for (uint32_t g = 0; g + 1 < NG; g++) issue();  // groups 0 .. NG-2
+    }
+
+    // ---- walker --------------------------------------------------------------------------------------------------------
+    M m;
+    uint32_t k = 0, ke = 0;
+    uint32_t s_start = 0xFFFFFFFFu, s_end = 0xFFFFFFFFu, s_flags = 0, s_param = 0;
+    uint4 nxt = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);  // the span after the one under the cursor, already fetched
+    bool active = false;
+    if (!producer && valid) {
+        m.load(a, v);
+        if (line_ring) LineRingCall<M>::bind(m, lq + lane, RW, L);
+        k = a.off[v];
+        ke = a.off[v + 1];
+        if (k < ke) {
+            const uint4 s = *reinterpret_cast<const uint4*>(a.spans + k);
+            s_start = s.x; s_end = s.y; s_flags = s.z; s_param = s.w;
+        }
+        if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
+    }
+    for (int i = 0; i < ngroups; i++) {
+        if (producer) pipeline_wait_prior_rt(NG - 2);
+        __syncthreads();  // group i has landed; group i - 1 is walked
+        const uint32_t slot = (uint32_t)i % NG;
+        if (producer) {
+            if (i >= 1) write_back(slot == 0 ? NG - 1 : slot - 1, (uint32_t)(i - 1) * G);
+            issue();  // group i + NG - 1 into the slot of group i - 1
+        } else {
+            const uint32_t f0 = (uint32_t)i * G, n = min(G, frames - f0);
+            float* so_t = smem + (size_t)(slot * nb) * G * RW + lane;
+            const float* s0_t = i_in0 >= 0 ? so_t + (size_t)i_in0 * G * RW : so_t;
+            const float* s1_t = i_in1 >= 0 ? so_t + (size_t)i_in1 * G * RW : so_t;
+            const float* s2_t = i_in2 >= 0 ? so_t + (size_t)i_in2 * G * RW : so_t;
+            bool painted = false;
+            uint32_t j = 0;
+            while (j < n) {
+                const uint32_t f = f0 + j;
+                if (active && f == s_end) {
+                    m.end_span(a);
+                    active = false;
+                    k++;
+                    s_start = nxt.x; s_end = nxt.y; s_flags = nxt.z; s_param = nxt.w;
+                    nxt = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
+                    if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
+                }
+                if (!active && f == s_start) {
+                    m.begin_span(a, s_param, s_flags, s_end - s_start);
+                    active = true;
+                }
+                const uint32_t dist = (active ? s_end : s_start) - f;
+                const uint32_t run = min(n - j, __reduce_min_sync(0xffffffffu, dist));
+                if (active) {
+                    painted = true;
+                    float* so = so_t + j * RW;
+                    const float* s0 = s0_t + j * RW;
+                    const float* s1 = s1_t + j * RW;
+                    const float* s2 = s2_t + j * RW;
+                    uint32_t r = 0;
+                    for (; r + 4 <= run; r += 4) {
+                        float acc[4], x0[4], x1[4], x2[4];
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            // (an input that is absent aliases the output tile: its value is read but no module variant
+                            // that can run without the buffer looks at it)
+                            acc[q] = so[(r + q) * RW];
+                            x0[q] = M::NIN >= 1 ? s0[(r + q) * RW] : 0.0f;
+                            x1[q] = M::NIN >= 2 ? s1[(r + q) * RW] : 0.0f;
+                            x2[q] = M::NIN >= 3 ? s2[(r + q) * RW] : 0.0f;
+                        }
+                        Sample4<M>::call(m, acc, x0, x1, x2);
+#pragma unroll
+                        for (int q = 0; q < 4; q++) so[(r + q) * RW] = acc[q];
+                    }
+                    for (; r < run; r++) {
+                        float acc = so[r * RW];
+                        m.sample(acc, i_in0 >= 0 ? s0[r * RW] : 0.0f, i_in1 >= 0 ? s1[r * RW] : 0.0f, i_in2 >= 0 ? s2[r * RW] : 0.0f);
+                        so[r * RW] = acc;
+                    }
+                }
+                j += run;
+            }
+            const bool any = __any_sync(0xffffffffu, painted);
+            if (lane == 0) s_painted[slot] = any ? 1u : 0u;
+            if constexpr (LineRingOf<M>::value) {
+                if (line_ring) s_taken[lane] = LineRingCall<M>::taken(m);
+            }
+        }
+    }
+    __syncthreads();
+    if (producer) {
+        if (ngroups >= 1) write_back((uint32_t)(ngroups - 1) % NG, (uint32_t)(ngroups - 1) * G);
+        return;
+    }
+    if (!valid) return;
+    if (active) m.end_span(a);
+    m.store(a, v);
+}
+
 constexpr int kPaintWarps = 4;    // warps per CTA: rows of 128 voices = 512 bytes
 constexpr int kPaintStages = 3;   // tiles in the cp.async ring
 
