@@ -230,10 +230,16 @@ def sfx_leg(ctx, torch, dist, timed, rank, world, peak, jobs_total=65536, job_fr
         bank.paint_block_fused(0, job_frames, mix, prepared=prepared)
         if dist is not None:
             dist.reduce(mix_t, dst=0)
+    # tolerance mode, as for the module chain above: with fewer jobs per GPU than fill it, the graph is cut into time segments
+    # (the Filter starts each from a verified warm-up window, tests/test_gpu_graph.py::test_sfx_graph_filter_time_segments)
+    ctx.set_paint_mode(L.PAINT_TOLERANCE)
     l0 = ctx.launch_count
     step_fused()
     launches_f = ctx.launch_count - l0
     ms_f = timed(step_fused, 3)
+    seg_info = bank.graph.segment_info()
+    seg_info["warm_retries"] = bank.graph.warm_retries()
+    ctx.set_paint_mode(L.PAINT_EXACT)
     fused_vs_dropin = float((mix_t - dropin_mix).abs().max()) if rank == 0 else 0.0
     mix_scale = float(dropin_mix.abs().max()) if rank == 0 else 0.0
     t = torch.tensor([sum(ms) / len(ms), sum(ms_f) / len(ms_f)], dtype=torch.float64, device="cuda")
@@ -250,6 +256,7 @@ def sfx_leg(ctx, torch, dist, timed, rank, world, peak, jobs_total=65536, job_fr
                         "reduce of the mix; value = the fused graph kernel (zcu_graph_*), dropin = the module chain (ZCU_PAINT_TOLERANCE)",
             "jobs_total": jobs_total, "jobs_per_gpu": V, "job_frames": job_frames, "n_gpus": world, "scaling": "strong",
             "ms_per_step": ms_fused, "value": vs, "unit": METRIC, "steps": 3, "gpu_launches_per_step": int(launches_f),
+            "fused_time_segments": seg_info,
             "mix_max_abs_diff_fused_vs_dropin": fused_vs_dropin, "mix_abs_max": mix_scale,
             "dropin": {"ms_per_step": ms_step, "value": vs_d, "gpu_launches_per_step": int(launches), "algorithmic_bytes_per_voice_sample": 100,
                        "algorithmic_gbs_all_gpus": gbs, "frac_of_hbm_peak_per_gpu": gbs / world / peak}}

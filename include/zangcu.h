@@ -637,6 +637,13 @@ int zcu_graph_paint(zcu_ctx*, zcu_graph*, const zcu_spans* const* tables, zcu_bu
  * its start state since the last call (it synchronises; the painted block is then invalid). */
 int zcu_graph_set_segments(zcu_graph*, uint32_t segments);
 int zcu_graph_segment_info(zcu_ctx*, zcu_graph*, uint32_t* segments, uint32_t* segment_frames, uint32_t* replay_frames, uint32_t* failed);
+/* A graph with a Filter (src/modules/Filter.zig) is cut into time segments only under ZCU_PAINT_TOLERANCE: a segment runs the
+ * whole graph silently over a window before its start, the Filter from zero state, and paints once the window's homogeneous
+ * map is below 1e-8 on every voice of the warp (the Filter has then forgotten where it started); a window that fails is
+ * lengthened fourfold and the segment starts over, down to frame 0 = the loaded state, which is exact.  Voices that paint
+ * nothing before the window keep their loaded state.  zcu_graph_warm_retries: (warp, segment) pairs that lengthened their
+ * window since the last call (it synchronises).  Exact mode keeps such a graph in one segment. */
+int zcu_graph_warm_retries(zcu_ctx*, zcu_graph*, uint32_t* retries);
 
 /* ---- multi-GPU: sum of per-GPU partial mixes --------------------------------------------------- */
 /* NCCL is loaded with dlopen("libnccl.so.2") at first use; id is the 128-byte ncclUniqueId. */

@@ -324,3 +324,100 @@ def test_graph_feedback_echo_and_libm_arith(ctx):
     assert_close(outs[1].download(), np.sin(y.astype(np.float64)).astype(np.float32), 2e-6, "sin")
     assert_close(outs[2].download(), np.power(2.0, np.cos(y.astype(np.float64))).astype(np.float32), 4e-6, "pow(2, cos)")
     g.free()
+
+
+def test_graph_filter_with_constant_coefficients_in_time_segments(ctx):
+    """The shape of examples/modules.zig's NiceInstrument as a graph: PulseOsc -> Filter (cutoff constant per note) -> x Envelope.
+    In tolerance mode the graph is cut into time segments sized to the GPU; the warm-up window comes from the Filter rows
+    (the frames after which the homogeneous map of the slowest row is below 1e-8), so no window has to be lengthened.
+    1e-5 of full scale against one segment (exact mode); PulseOsc and Envelope states bit-equal."""
+    sr, V, total = 48000.0, 90, 40 * 1024
+    wl = synth.polyphony_bank(V, total, sr, seed=3, mean_on=0.08, mean_off=0.03)
+    from zang_b200.events import BankTrigger
+    off, spans = BankTrigger(wl["event_off"], wl["events"], total, 1024).spans(0, total)
+    ev = wl["events"]
+    pp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_PULSE_OSC])
+    pp["sample_rate"], pp["freq"], pp["color"] = sr, ev["freq"], 0.3
+    fp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_FILTER])
+    fp["type"] = L.FILTER_LOW_PASS
+    fp["cutoff"] = [E.Filter.cutoffFromFrequency(float(f) * 8.0, sr) for f in ev["freq"]]  # modules.zig:236
+    fp["res"] = 0.7
+    ep = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_ENVELOPE])
+    ep["sample_rate"], ep["attack"], ep["decay"], ep["release"] = sr, (L.CURVE_CUBED, 0.01), (L.CURVE_CUBED, 0.1), (L.CURVE_CUBED, 0.3)
+    ep["sustain_volume"], ep["note_on"] = 0.8, ev["note_on"]
+    results = []
+    for mode in (L.PAINT_EXACT, L.PAINT_TOLERANCE):
+        b = E.GraphBuilder()
+        b.zero(E.T(0))
+        f_osc = b.call(L.MOD_PULSE_OSC, E.T(0))
+        b.multiplyWithScalar(E.T(0), 2.5)
+        b.zero(E.T(1))
+        f_flt = b.call(L.MOD_FILTER, E.T(1), (E.T(0),))
+        b.zero(E.T(2))
+        f_env = b.call(L.MOD_ENVELOPE, E.T(2))
+        b.multiply(E.OUT(0), E.T(1), E.T(2))
+        g = E.Graph(ctx, E.graph_config(V, b, 3), b)
+        osc, flt, env = E.PulseOsc(ctx, V), E.Filter(ctx, V), E.Envelope(ctx, V)
+        g.set_field(f_osc, osc.bank, pp)
+        g.set_field(f_flt, flt.bank, fp)
+        g.set_field(f_env, env.bank, ep)
+        out = ctx.buf(total, V)
+        ctx.zero(None, out)
+        sp = ctx.spans(V, total, off, spans)
+        ctx.set_paint_mode(mode)
+        try:
+            g.paint([sp], [out])
+            info = g.segment_info()
+            retries = g.warm_retries()
+        finally:
+            ctx.set_paint_mode(L.PAINT_EXACT)
+        assert info["failed"] == 0 and retries == 0, (info, retries)
+        assert (info["segments"] > 1) == (mode == L.PAINT_TOLERANCE), info
+        if mode == L.PAINT_TOLERANCE:
+            assert 8 < info["replay_frames"] <= 16384, info
+        results.append((out.download(), osc.bank.get_state().tobytes() + env.bank.get_state().tobytes(), flt.bank.get_state().view(np.float32).copy()))
+        g.free()
+    assert float(np.abs(results[0][0]).max()) > 0.2
+    assert_close(results[1][0], results[0][0], 1e-5, "Filter graph in time segments vs one segment")
+    assert results[1][1] == results[0][1], "carried PulseOsc / Envelope state"
+    assert np.abs(results[1][2] - results[0][2]).max() <= 1e-5, "carried Filter state"
+
+
+@pytest.mark.parametrize("segments,warm", [(0, None), (5, None), (7, "48")], ids=["planned", "5seg", "7seg-short-window"])
+def test_sfx_graph_filter_time_segments(ctx, segments, warm, monkeypatch):
+    """A graph with a Filter in time segments (ZCU_PAINT_TOLERANCE): a segment skips the exact modules ahead to a window before
+    its start (Noise by its GF(2) jump, Curve and Envelope in closed form), runs the whole graph silently over the window with
+    the Filter starting from zero, and paints only if the window's homogeneous map has shrunk below 1e-8 on every voice of the
+    warp; otherwise it lengthens the window and starts over (forced here with a 48-frame first guess).  Voices that paint
+    nothing before the window keep their loaded state.  Two blocks, so the second starts from carried Filter states.
+    Bar: 1e-5 of full scale against the per-module path in exact mode; Noise / Curve / Envelope states bit-equal."""
+    if warm:
+        monkeypatch.setenv("ZCU_GRAPH_WARM", warm)
+    sr, jobs, job_frames, block = 48000.0, 70, 24576, 12288
+    wl = synth.sfx_bank(jobs, job_frames, seed=5)
+    ref = banks.SfxBank(ctx, wl, sr, job_frames, first_seed=9)
+    unfused = _render(ctx, ref, job_frames, block, 3, fused=False)
+    bank = banks.SfxBank(ctx, wl, sr, job_frames, first_seed=9)
+    g = bank.build_graph()
+    g.set_segments(segments)
+    ctx.set_paint_mode(L.PAINT_TOLERANCE)
+    try:
+        got = _render(ctx, bank, job_frames, block, 3, fused=True)
+        info = g.segment_info()
+        retries = g.warm_retries()
+    finally:
+        ctx.set_paint_mode(L.PAINT_EXACT)
+    assert info["failed"] == 0, info
+    # the cutoff comes from a buffer: nothing is known about the decay, so segments only when asked for
+    assert (info["segments"] > 1) == (segments != 0), info
+    if warm is not None:
+        assert retries > 0, "the 48-frame guess cannot have been enough"
+    assert np.abs(unfused).max() > 0.05
+    assert_close(got, unfused, 1e-5, "sfx graph in time segments vs per-module path")
+    a, b = _states(bank), _states(ref)
+    for k in a:
+        if k == "filter":
+            fa, fb = a[k].view(np.float32), b[k].view(np.float32)
+            assert np.abs(fa - fb).max() <= 1e-5, "carried Filter state"
+        else:
+            assert a[k].tobytes() == b[k].tobytes(), f"carried state of {k}"

@@ -155,6 +155,7 @@ PROTOTYPES = {
     "zcu_graph_paint": (_I, [_P, _P, _P, _P, _P]),
     "zcu_graph_set_segments": (_I, [_P, _U]),
     "zcu_graph_segment_info": (_I, [_P, _P, _P, _P, _P, _P]),
+    "zcu_graph_warm_retries": (_I, [_P, _P, _P]),
     "zcu_nccl_unique_id": (_I, [_P]),
     "zcu_nccl_init": (_I, [_P, _I, _I, _P]),
     "zcu_nccl_reduce_mix": (_I, [_P, _P, _I]),

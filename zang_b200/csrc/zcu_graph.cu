@@ -163,6 +163,7 @@ struct FieldInfo {
     bool used = false;
     bool has_run = false;  // the module offers run_limit / run_begin / sample_run / run_end (zcu_modules.cuh: HAS_RUN)
     bool skippable = false;  // exact skip-ahead from its own params alone (advance()), or a Decimator (counter + replay window)
+    bool warmable = false;   // a Filter: a time segment may start it from a verified warm-up window (ZCU_PAINT_TOLERANCE)
     bool is_delay = false;   // a zang.Delay(N) served by DELAY_READ / DELAY_WRITE
     int delay_reads = 0, delay_writes = 0;
 };
@@ -217,7 +218,7 @@ bool module_type(int kind, const zcu_graph_instr& in, std::string& type, std::st
 }
 
 bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, const int32_t* field_kinds, std::string& src, std::string& err,
-             bool* segmentable_out = nullptr) {
+             bool* segmentable_out = nullptr, bool* needs_tolerance_out = nullptr, std::vector<int>* filter_buffered_out = nullptr) {
     auto fail = [&](uint32_t i, const char* what) {
         char b[256];
         snprintf(b, sizeof b, "instruction %u: %s", i, what);
@@ -345,12 +346,13 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     };
     // one instruction on one sample: d, a, b, cc are the C expressions of its operands
     auto statement = [&](const zcu_graph_instr& x, const std::string& d, const std::string& a, const std::string& b, const std::string& cc,
-                         bool run_form) -> std::string {
+                         bool run_form, bool silent = false) -> std::string {
         const std::string sc = float_lit(x.scalar);
         std::string stmt;
         if (x.op == ZCU_GI_CALL) {
             char t[200];
-            snprintf(t, sizeof t, "m%u.%s(%s, %s, %s, %s);", x.field, (run_form && fields[x.field].has_run) ? "sample_run" : "sample", d.c_str(),
+            snprintf(t, sizeof t, "m%u.%s(%s, %s, %s, %s);", x.field,
+                     (silent && fields[x.field].warmable) ? "sample_silent" : ((run_form && fields[x.field].has_run) ? "sample_run" : "sample"), d.c_str(),
                      a.c_str(), b.c_str(), cc.c_str());
             stmt = t;
         } else if (x.op == ZCU_GI_DELAY_READ) {
@@ -453,7 +455,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         return s;
     };
     // the per-sample body; live[k] = expression telling whether table k is live on this lane ("true" in the all-live copy)
-    auto body = [&](bool all_live, const char* ind, const char* row, bool emit = true) {
+    auto body = [&](bool all_live, const char* ind, const char* row, bool emit = true, bool silent = false) {
         std::string s;
         auto live = [&](uint32_t k) -> std::string {
             if (all_live) return "true";
@@ -479,7 +481,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         }
         for (uint32_t i = 0; i < n; i++) {
             const zcu_graph_instr& x = ins[i];
-            const std::string stmt = statement(x, ref(x.out), ref(x.in[0]), ref(x.in[1]), ref(x.in[2]), all_live);
+            const std::string stmt = statement(x, ref(x.out), ref(x.in[0]), ref(x.in[1]), ref(x.in[2]), all_live, silent);
             if (all_live)
                 appendf(s, "%s%s\n", ind, stmt.c_str());
             else
@@ -497,9 +499,22 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     };
 
     // time segments: every module must be able to skip ahead exactly from its own params (FieldInfo::skippable)
-    bool segmentable = c.num_fields > 0;
-    for (uint32_t f = 0; f < c.num_fields; f++) segmentable = segmentable && fields[f].skippable;
+    // ... or be a Filter, which a segment starts from a warm-up over the frames before it (tolerance mode only: the launcher
+    // keeps such a graph in one segment otherwise)
+    bool segmentable = c.num_fields > 0, warm_any = false;
+    for (uint32_t f = 0; f < c.num_fields; f++) {
+        fields[f].warmable = fields[f].kind == ZCU_MOD_FILTER;
+        segmentable = segmentable && (fields[f].skippable || fields[f].warmable);
+        warm_any = warm_any || fields[f].warmable;
+    }
+    warm_any = warm_any && segmentable;
     if (segmentable_out) *segmentable_out = segmentable;
+    if (needs_tolerance_out) *needs_tolerance_out = warm_any;
+    if (filter_buffered_out) {  // per field: a Filter whose cutoff or resonance comes from a buffer (its decay is not known from the params)
+        filter_buffered_out->assign(c.num_fields, 0);
+        for (uint32_t f = 0; f < c.num_fields; f++)
+            (*filter_buffered_out)[f] = fields[f].warmable && fields[f].type != "FilterMod<false, false>" ? 1 : 0;
+    }
 
     src.clear();
     src += "// generated by libzangcu (zcu_graph.cu) from a zcu_graph_instr list\n#include \"zcu_graph_rt.cuh\"\nusing namespace zcu;\n\n";
@@ -518,6 +533,11 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         src += "    __syncwarp();\n";
         src += "    const uint32_t gwarp = blockIdx.x * 4u + warp;\n";
     }
+    if (warm_any) {
+        // a Filter's warm-up window that fails its check is lengthened and the segment starts over (W == F_begin: from the
+        // loaded state, which is exact)
+        src += "    uint32_t W = g.replay;\nretry:;\n";
+    }
     for (uint32_t k = 0; k < K; k++) appendf(src, "    SpanCursor c%u;\n    c%u.init(g.tab[%u], v, valid);\n", k, k, k);
     for (uint32_t f = 0; f < c.num_fields; f++) appendf(src, "    %s m%u;\n", fields[f].type.c_str(), f);
     src += "    if (valid) {\n";
@@ -530,7 +550,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         src += "    const uint32_t F_begin = blockIdx.y * g.seg_frames;\n";
         src += "    if (F_begin >= g.frames) return;\n";
         src += "    const uint32_t F_end = min(g.frames, F_begin + g.seg_frames);\n";
-        src += "    const uint32_t F_play = F_begin > g.replay ? F_begin - g.replay : 0u;\n";
+        src += warm_any ? "    const uint32_t F_play = F_begin > W ? F_begin - W : 0u;\n" : "    const uint32_t F_play = F_begin > g.replay ? F_begin - g.replay : 0u;\n";
         src += "    if (F_play > 0 && valid) {\n";
         for (uint32_t k = 0; k < K; k++) {
             appendf(src, "        while (c%u.s_end <= F_play) {\n", k);
@@ -551,12 +571,26 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         for (uint32_t f = 0; f < c.num_fields; f++)
             if (fields[f].kind == ZCU_MOD_NOISE) appendf(src, "        m%u.advance_done();  // the draws skipped so far, as one jump\n", f);
         src += "    }\n";
+        if (warm_any) {
+            src += "    if (F_play > 0) {\n";
+            for (uint32_t f = 0; f < c.num_fields; f++)
+                if (fields[f].warmable)
+                    appendf(src, "        m%u.warm_begin_graph(!valid || (c%u.k == g.tab[%u].off[v] && !c%u.active));\n", f, fields[f].table, fields[f].table,
+                            fields[f].table);
+            src += "    }\n";
+        }
     } else {
         src += "    const uint32_t F_begin = 0, F_end = g.frames, F_play = 0;\n    (void)F_begin;\n";
     }
     if (mix) src += "    uint32_t j = 0, T0 = F_begin;\n";
     src += "    uint32_t f = F_play;\n";
     src += "    while (f < F_end) {\n";
+    if (warm_any) {
+        src += "        if (f == F_begin && F_play > 0) {  // every Filter must have forgotten the start of its warm-up window\n            bool ok = true;\n";
+        for (uint32_t f = 0; f < c.num_fields; f++)
+            if (fields[f].warmable) appendf(src, "            ok = ok && m%u.warm_ok_graph();\n            m%u.track_map = false;\n", f, f);
+        src += "            if (!__all_sync(FULL, ok)) {\n                if (lane == 0 && g.err) atomicAdd(g.err + 1, 1u);\n                W = W >= F_begin / 4u ? F_begin : W * 4u;\n                goto retry;\n            }\n        }\n";
+    }
     if (segmentable) {
         bool any_dec = false;
         for (uint32_t f = 0; f < c.num_fields; f++) any_dec = any_dec || fields[f].kind == ZCU_MOD_DECIMATOR;
@@ -612,7 +646,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     appendf(src, "        const bool lane_live = %s;\n        const bool lane_idle = !(%s);\n", all.c_str(), any.c_str());
     if (segmentable) {
         src += "        if (silent) {\n            for (uint32_t r = 0; r < run; r++) {\n";
-        src += body(false, "                ", "r", false);
+        src += body(false, "                ", "r", false, true);
         src += "            }\n        } else\n";
     }
     src += "        if (__all_sync(FULL, (lane_live && !careful) || lane_idle) && __any_sync(FULL, lane_live)) {\n";
@@ -717,18 +751,57 @@ struct zcu_graph {
         const zcu_sample* sample = nullptr;
         uint32_t replay = 0;     // frames a segment must re-run before its start to re-establish this module's state
         bool seg_ok = true;      // false: these params rule time segments out
+        bool guess = false;      // a Filter with buffer-driven coefficients: the window is a guess (segments only when forced)
     };
     std::vector<Field> fields;
     float* d_gains = nullptr;
     float* d_partial = nullptr;
     size_t partial_bytes = 0;
     // time segments
-    bool segmentable = false;     // every module can skip ahead exactly (codegen)
+    bool segmentable = false;     // every module can skip ahead exactly, or is a Filter (codegen)
+    bool needs_tolerance = false; // ... the latter: time segments only under ZCU_PAINT_TOLERANCE
     uint32_t forced_nseg = 0;     // zcu_graph_set_segments: 0 = sized to the GPU
     int resident_per_sm = 0;      // occupancy of the compiled kernel
     uint32_t last_nseg = 1, last_seg_frames = 0, last_replay = 0;
     uint32_t* d_err = nullptr;
 };
+
+// Frames after which the Filter's homogeneous map (FilterMod::hom_step, zcu_modules.cuh) is below 1e-8 in every entry, for
+// constant (cutoff, res) as FilterMod::begin_span clamps them; + 12 % + 8 as in warm_estimate; 0xFFFFFFFF if > 2^16.
+uint32_t filter_forget_window(float cutoff, float res_param) {
+    const float cut = std::min(std::max(cutoff, 0.0f), 1.0f), res = 1.0f - std::min(std::max(res_param, 0.0f), 1.0f);
+    auto hom = [&](float& l, float& b) {
+        l += cut * b;
+        b += cut * (0.0f - b * res - l);
+        l += cut * b;
+        const float h = 0.0f - b * res - l;
+        b += cut * h;
+    };
+    auto small = [](const double* m) { return std::max(std::max(std::fabs(m[0]), std::fabs(m[1])), std::max(std::fabs(m[2]), std::fabs(m[3]))) <= 1e-8; };
+    float c1l = 1.0f, c1b = 0.0f, c2l = 0.0f, c2b = 1.0f;
+    hom(c1l, c1b);
+    hom(c2l, c2b);
+    double p[17][4];
+    double a[4] = {c1l, c2l, c1b, c2b};  // row-major 2x2: columns are the images of (1,0) and (0,1)
+    int k = 0;
+    for (;; k++) {
+        if (small(a)) break;
+        if (k == 16) return 0xFFFFFFFFu;
+        for (int i = 0; i < 4; i++) p[k][i] = a[i];
+        const double b[4] = {a[0] * a[0] + a[1] * a[2], a[0] * a[1] + a[1] * a[3], a[2] * a[0] + a[3] * a[2], a[2] * a[1] + a[3] * a[3]};
+        for (int i = 0; i < 4; i++) a[i] = b[i];
+    }
+    double q[4] = {1.0, 0.0, 0.0, 1.0};
+    uint32_t n = 0;
+    for (int j = k - 1; j >= 0; j--) {
+        const double b[4] = {q[0] * p[j][0] + q[1] * p[j][2], q[0] * p[j][1] + q[1] * p[j][3], q[2] * p[j][0] + q[3] * p[j][2], q[2] * p[j][1] + q[3] * p[j][3]};
+        if (!small(b)) {
+            for (int i = 0; i < 4; i++) q[i] = b[i];
+            n += 1u << j;
+        }
+    }
+    return n + 1 + (n >> 3) + 8;
+}
 
 void zcu_launch_partial_reduce(zcu_ctx* ctx, const float* partial, float* mix, uint32_t nwarps, size_t n);  // zcu_render.cu
 
@@ -763,8 +836,9 @@ int zcu_graph_create(zcu_ctx* ctx, const zcu_graph_config* cfg, const zcu_graph_
     *out = nullptr;
     ZCU_REQUIRE(ctx, cfg != nullptr, "null config");
     std::string src, err;
-    bool segmentable = false;
-    if (!codegen(*cfg, instrs, num_instrs, field_kinds, src, err, &segmentable))
+    bool segmentable = false, needs_tolerance = false;
+    std::vector<int> filter_buffered;
+    if (!codegen(*cfg, instrs, num_instrs, field_kinds, src, err, &segmentable, &needs_tolerance, &filter_buffered))
         return zcu_fail(ctx, ZCU_ERR_INVALID, "zcu_graph_create: %s", err.c_str());
     std::vector<char> cubin;
     if (!nvrtc_compile(src, cubin, err)) return zcu_fail(ctx, ZCU_ERR_UNSUPPORTED, "zcu_graph_create: NVRTC: %s", err.c_str());
@@ -774,7 +848,9 @@ int zcu_graph_create(zcu_ctx* ctx, const zcu_graph_config* cfg, const zcu_graph_
     g->kinds.assign(field_kinds, field_kinds + cfg->num_fields);
     g->source = src;
     g->segmentable = segmentable;
+    g->needs_tolerance = needs_tolerance;
     g->fields.resize(cfg->num_fields);
+    for (uint32_t f = 0; f < cfg->num_fields; f++) g->fields[f].guess = filter_buffered[f] != 0;
     cudaError_t e = cudaLibraryLoadData(&g->lib, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
     if (e == cudaSuccess) e = cudaLibraryGetKernel(&g->kernel, g->lib, "zcu_graph_kernel");
     if (e != cudaSuccess) {
@@ -790,7 +866,8 @@ int zcu_graph_create(zcu_ctx* ctx, const zcu_graph_config* cfg, const zcu_graph_
         }
     }
     if (segmentable) {
-        if (cudaMalloc((void**)&g->d_err, sizeof(uint32_t)) != cudaSuccess || cudaMemsetAsync(g->d_err, 0, sizeof(uint32_t), ctx->stream) != cudaSuccess) {
+        // [0] a segment could not establish its start state, [1] warm-up windows that had to be lengthened
+        if (cudaMalloc((void**)&g->d_err, 2 * sizeof(uint32_t)) != cudaSuccess || cudaMemsetAsync(g->d_err, 0, 2 * sizeof(uint32_t), ctx->stream) != cudaSuccess) {
             zcu_graph_free(g);
             return zcu_fail(ctx, ZCU_ERR_OOM, "zcu_graph_create: status word allocation failed");
         }
@@ -822,6 +899,18 @@ int zcu_graph_segment_info(zcu_ctx* ctx, zcu_graph* g, uint32_t* segments, uint3
             ZCU_CUDA(ctx, cudaMemcpy(failed, g->d_err, sizeof(uint32_t), cudaMemcpyDeviceToHost));
             ZCU_CUDA(ctx, cudaMemset(g->d_err, 0, sizeof(uint32_t)));
         }
+    }
+    return ZCU_OK;
+}
+
+int zcu_graph_warm_retries(zcu_ctx* ctx, zcu_graph* g, uint32_t* retries) {
+    if (!ctx) return ZCU_ERR_INVALID;
+    ZCU_REQUIRE(ctx, g != nullptr && retries != nullptr, "null argument");
+    *retries = 0;
+    if (g->d_err) {
+        ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        ZCU_CUDA(ctx, cudaMemcpy(retries, g->d_err + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        ZCU_CUDA(ctx, cudaMemset(g->d_err + 1, 0, sizeof(uint32_t)));
     }
     return ZCU_OK;
 }
@@ -864,6 +953,19 @@ int zcu_graph_set_field(zcu_ctx* ctx, zcu_graph* g, uint32_t field, zcu_bank* ba
     ZCU_REQUIRE(ctx, row_bytes == params_row_bytes(kind), "row_bytes is not the sizeof of this module's params struct");
     f.replay = 0;
     f.seg_ok = true;
+    if (kind == ZCU_MOD_FILTER && !f.guess) {
+        // constant coefficients per span: the window after which a segment's warm-up has forgotten its start follows from the
+        // rows (the largest over the rows; a row that needs more than 16384 frames rules segments out)
+        const zcu_filter_params* p = (const zcu_filter_params*)params_host;
+        for (uint32_t i = 0; i < nparams; i++) {
+            if (p[i].type == ZCU_FILTER_BYPASS) continue;
+            const uint32_t w = filter_forget_window(p[i].cutoff, p[i].res);
+            if (w > 16384u)
+                f.seg_ok = false;
+            else
+                f.replay = std::max(f.replay, w);
+        }
+    }
     if (kind == ZCU_MOD_DECIMATOR) {
         // a time segment re-latches the held value by running the frames before its start again: the window must hold a
         // latch for every row (Decimator.zig:40-55: one latch per 1/ratio samples); a row that paints nothing (fake rate <= 0)
@@ -1030,6 +1132,20 @@ int zcu_graph_paint(zcu_ctx* ctx, zcu_graph* g, const zcu_spans* const* tables, 
             ok = ok && fd.seg_ok;
             replay = std::max(replay, fd.replay);
         }
+        if (g->needs_tolerance) {
+            // a Filter starts a segment from a warm-up window: only in tolerance mode; the window is a first guess that the
+            // kernel verifies (and lengthens where it was too short)
+            ok = ok && ctx->paint_mode == ZCU_PAINT_TOLERANCE;
+            for (const auto& fd : g->fields) {
+                if (!fd.guess) continue;
+                // coefficients from a buffer: nothing is known about the decay (a sweep towards a low cutoff forgets slowly and
+                // the retries then cost more than the segments bring): segments only on request, from a first guess
+                ok = ok && g->forced_nseg != 0;
+                uint32_t w = 1024;
+                if (const char* e = getenv("ZCU_GRAPH_WARM")) w = (uint32_t)std::max(1, atoi(e));  // tuning
+                replay = std::max(replay, w);
+            }
+        }
         bool has_noise = false;
         for (uint32_t f = 0; f < c.num_fields; f++) has_noise = has_noise || g->kinds[f] == ZCU_MOD_NOISE;
         if (has_noise) {  // jumps are tabulated for fewer than 16^6 draws per call
@@ -1049,6 +1165,7 @@ int zcu_graph_paint(zcu_ctx* ctx, zcu_graph* g, const zcu_spans* const* tables, 
             seg_frames = (frames + nseg - 1) / nseg;
             if (!g->forced_nseg) seg_frames = std::max(seg_frames, std::min(frames, 512u));
             seg_frames = std::max(seg_frames, replay + 1);
+            if (g->needs_tolerance && !g->forced_nseg) seg_frames = std::max(seg_frames, 2 * replay);  // warm-up at most a third of a segment's work
             seg_frames = (seg_frames + kMixTileFrames - 1) / kMixTileFrames * kMixTileFrames;
             nseg = (frames + seg_frames - 1) / seg_frames;
         }

@@ -858,6 +858,12 @@ class Graph:
         _check(self.ctx, lib.zcu_graph_segment_info(self.ctx._h, self._h, *[C.byref(x) for x in v]))
         return dict(zip(("segments", "segment_frames", "replay_frames", "failed"), (x.value for x in v)))
 
+    def warm_retries(self):
+        """(warp, segment) pairs whose Filter warm-up window had to be lengthened since the last call; synchronises"""
+        n = C.c_uint32()
+        _check(self.ctx, lib.zcu_graph_warm_retries(self.ctx._h, self._h, C.byref(n)))
+        return int(n.value)
+
     def free(self):
         if self._h:
             lib.zcu_graph_free(self._h)
