@@ -62,6 +62,20 @@ def test_delay_random_spans(ctx, kind):
     _run_blocks(ctx, kind, V, NB, D, lambda: random_spans(rng, V, NB, BF, 4), rng)
 
 
+@pytest.mark.parametrize("parallel", ["0", "1"], ids=["sequential", "time-parallel"])
+@pytest.mark.parametrize("D", [5, 333, 2500])
+def test_simple_delay_both_forms(ctx, D, parallel, monkeypatch):
+    """SimpleDelay has two device forms with the same results: the sequential walk (every painted frame reads and writes its
+    slot) and, for banks too small to fill the GPU that way, time segments (zcu_modules.cuh SimpleDelayParMod: the k-th painted
+    frame adds the old line for k < N and the input N painted frames back otherwise; the line is brought up to date by a
+    second kernel).  Random spans with gaps, delays shorter than, comparable to and longer than the spans, a long block so
+    that the paint is really cut in time, two calls: outputs, index and line bit-equal to the oracle in both forms."""
+    monkeypatch.setenv("ZCU_DELAY_PARALLEL", parallel)
+    V, NB = 150, 40
+    rng = np.random.default_rng(D)
+    _run_blocks(ctx, L.MOD_SIMPLE_DELAY, V, NB, D, lambda: random_spans(rng, V, NB, BF, 4, max_cuts=2, p_empty=0.2, p_gap=0.3), rng)
+
+
 def test_delay_line_checkpoint_resume(ctx):
     V, NB, D = 64, 4, 700
     rng = np.random.default_rng(4)
