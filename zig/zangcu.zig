@@ -348,4 +348,22 @@ pub const Graph = struct {
     pub fn paint(self: *Graph, tables: []const ?*const c.zcu_spans, outputs: []const ?*c.zcu_buf, inputs: []const ?*const c.zcu_buf) !void {
         try check(c.zcu_graph_paint(self.ctx.h, self.h, tables.ptr, outputs.ptr, if (inputs.len > 0) inputs.ptr else null));
     }
+    /// 0 = sized to the GPU, 1 = off.  A graph with a Filter is cut in time only after
+    /// zcu_ctx_set_paint_mode(ZCU_PAINT_TOLERANCE) (and, if a buffer drives its cutoff or resonance, only when forced here).
+    pub fn setSegments(self: *Graph, segments: u32) !void {
+        try check(c.zcu_graph_set_segments(self.h, segments));
+    }
+    /// (warp, segment) pairs whose Filter warm-up window had to be lengthened since the last call; synchronises
+    pub fn warmRetries(self: *Graph) !u32 {
+        var n: u32 = 0;
+        try check(c.zcu_graph_warm_retries(self.ctx.h, self.h, &n));
+        return n;
+    }
 };
+
+/// zang.mixDown (src/zang/mixdown.zig:8-86) into `dst` (s16le or s8), through device scratch that is part of the library
+/// image: the call allocates nothing (hosts that must not call cudaMalloc).  dst.len <= ZCU_MIX_DOWN_STATIC_MAX_BYTES.
+/// No counterpart in the reference; added at the request of the run's operators.
+pub fn mixDownStatic(ctx: Context, mix: *const c.zcu_buf, audio_format: c_int, vol: f32, dst: []u8) !void {
+    try check(c.zcu_mix_down_static(ctx.h, mix, audio_format, vol, dst.ptr, dst.len));
+}
