@@ -62,16 +62,29 @@ def test_delay_random_spans(ctx, kind):
     _run_blocks(ctx, kind, V, NB, D, lambda: random_spans(rng, V, NB, BF, 4), rng)
 
 
+@pytest.mark.parametrize("kind", [L.MOD_SIMPLE_DELAY, L.MOD_FILTERED_ECHOES], ids=["SimpleDelay", "FilteredEchoes"])
+@pytest.mark.parametrize("D,V", [(300, 200), (1500, 133)])
+def test_delay_lockstep_line_queue(ctx, kind, D, V, monkeypatch):
+    """Large banks run the delay modules in the lockstep kernel, with the line fetched in slot order into a per-thread queue
+    behind the tile ring (zcu_paint_kernel.cuh, M::LINE_RING).  Small banks normally take the walker kernel or (SimpleDelay)
+    the time-parallel form: both are switched off here so that the lockstep form is the one that runs."""
+    monkeypatch.setenv("ZCU_PAINT_NO_WALK", "1")
+    monkeypatch.setenv("ZCU_DELAY_PARALLEL", "0")
+    rng = np.random.default_rng(D + V)
+    NB = 12
+    _run_blocks(ctx, kind, V, NB, D, lambda: random_spans(rng, V, NB, BF, 4, max_cuts=2, p_empty=0.1, p_gap=0.3), rng)
+
+
 @pytest.mark.parametrize("parallel", ["0", "1"], ids=["sequential", "time-parallel"])
-@pytest.mark.parametrize("D", [5, 333, 2500])
-def test_simple_delay_both_forms(ctx, D, parallel, monkeypatch):
+@pytest.mark.parametrize("D,NB", [(5, 40), (333, 40), (2500, 40), (2500, 4)], ids=["5", "333", "2500", "2500-longer-than-the-block"])
+def test_simple_delay_both_forms(ctx, D, NB, parallel, monkeypatch):
     """SimpleDelay has two device forms with the same results: the sequential walk (every painted frame reads and writes its
     slot) and, for banks too small to fill the GPU that way, time segments (zcu_modules.cuh SimpleDelayParMod: the k-th painted
     frame adds the old line for k < N and the input N painted frames back otherwise; the line is brought up to date by a
     second kernel).  Random spans with gaps, delays shorter than, comparable to and longer than the spans, a long block so
     that the paint is really cut in time, two calls: outputs, index and line bit-equal to the oracle in both forms."""
     monkeypatch.setenv("ZCU_DELAY_PARALLEL", parallel)
-    V, NB = 150, 40
+    V = 150
     rng = np.random.default_rng(D)
     _run_blocks(ctx, L.MOD_SIMPLE_DELAY, V, NB, D, lambda: random_spans(rng, V, NB, BF, 4, max_cuts=2, p_empty=0.2, p_gap=0.3), rng)
 

@@ -314,16 +314,17 @@ def test_pulse_gain_division_is_exact(ctx):
 RELAY_CASES = [c for c in CASES if c[0] in ("sine bc", "sine bb", "trisaw ctrl", "cycle buffer")]
 
 
+@pytest.mark.parametrize("Vn", [150, 152], ids=["150v", "152v-16B-copies"])
 @pytest.mark.parametrize("nseg", [0, 7, 24], ids=["planned", "7seg", "24seg"])
 @pytest.mark.parametrize("case", RELAY_CASES, ids=[c[0] for c in RELAY_CASES])
-def test_buffer_frequency_phase_relay(ctx, case, nseg, monkeypatch):
+def test_buffer_frequency_phase_relay(ctx, case, nseg, Vn, monkeypatch):
     """Oscillators driven by a frequency (speed) buffer carry an order-dependent f32 phase sum: no skip-ahead exists, so
     a walk of its own (zcu_paint_kernel.cuh, k_paint_prefix_ring, M::PREFIX_RING) tabulates the phase at every segment start: one warp
     per 32 voices runs the frames state-only through a cp.async ring, then the segments paint in parallel.  A long block (spans that straddle, end on
     and start on segment boundaries; two voice blocks), planned and forced segment counts, two consecutive calls: the carried
     phase is bit-equal to the sequential loop's, TriSawOsc and Cycle outputs bit-exact, SineOsc within the sinf tolerance."""
     name, kind, variant, ins, bf, exact = case
-    Vn, NB = 150, 24
+    NB = 24
     frames = NB * bf
     if nseg:
         monkeypatch.setenv("ZCU_PAINT_SEGMENTS", str(nseg))
