@@ -92,8 +92,9 @@ ZCU_HD uint32_t accum_core(float& t, float step, uint32_t n, bool& finished) {
             }
             if (settled) {
                 if (d == 0) return n;  // step is below half an ulp: t never moves again
-                k = (0xFFFFFFu - m) / d;  // adds that stay inside the binade
-                if (k > n - done) k = n - done;
+                // adds that stay inside the binade: min(room / d, n - done), without the division when the rest of the run fits
+                const uint32_t room = 0xFFFFFFu - m, want = n - done;
+                k = (unsigned long long)want * d <= room ? want : room / d;
                 if (k > 0) {
                     t = ea_float((et << 23) | ((m + k * d) & 0x7FFFFFu));
                     done += k;

@@ -1104,6 +1104,7 @@ int zcu_graph_paint(zcu_ctx* ctx, zcu_graph* g, const zcu_spans* const* tables, 
             p.smp.num_channels = fd.sample->num_channels;
             p.smp.sample_rate = fd.sample->sample_rate;
             p.smp.format = fd.sample->format;
+            zcu_sample_desc_finish(p.smp);
         }
     }
     if (frames == 0) return ZCU_OK;

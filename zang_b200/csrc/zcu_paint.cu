@@ -409,6 +409,7 @@ int zcu_launch_paint(zcu_ctx* ctx, const PaintLaunch& pl) {
     a.smp.num_channels = pl.smp_channels;
     a.smp.sample_rate = pl.smp_rate;
     a.smp.format = pl.smp_format;
+    zcu_sample_desc_finish(a.smp);
     a.line = pl.line;
     a.delay_samples = pl.delay_samples;
     a.xjump = nullptr;
