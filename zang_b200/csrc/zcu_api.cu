@@ -102,6 +102,7 @@ void zcu_ctx_destroy(zcu_ctx* ctx) {
     delete ctx;
 }
 
+
 int zcu_ctx_sync(zcu_ctx* ctx) {
     if (!ctx) return ZCU_ERR_INVALID;
     ZCU_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

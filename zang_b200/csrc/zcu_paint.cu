@@ -250,6 +250,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
             return ZCU_OK;
         }
     }
+    a.seg_base = 0;
     a.chain = nullptr;
     a.chain_flags = nullptr;
     a.epoch = 0;
@@ -289,7 +290,26 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         }
         a.prefix = ctx->prefix;
         a.prefix_stride = (uint32_t)stride;
-        if constexpr (PrefixRingOf<M>::value) {
+        if constexpr (!PrefixRingOf<M>::value) {
+            k_paint_prefix<M><<<(a.V + 127) / 128, 128, 0, ctx->stream>>>(a, p.seg_frames, p.nseg);
+            ctx->launches++;
+            ZCU_CUDA(ctx, cudaGetLastError());
+        }
+    }
+    // ZCU_OUT_OVERWRITE: `zero; paint` in one call (modules that overwrite anyway have a single form)
+    const bool ovr = ctx->paint_output == ZCU_OUT_OVERWRITE && !WriteOnlyOf<M>::value;
+    auto kern = ovr ? k_paint_lockstep<M, true> : k_paint_lockstep<M, false>;
+    if (!ctx->attr_done.count((const void*)kern)) {  // the attribute is per device: tracked per context
+        ZCU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
+        ctx->attr_done.insert((const void*)kern);
+    }
+    a.seg_base = 0;
+    if constexpr (PrefixRingOf<M>::value) {
+        if (a.prefix != nullptr) {
+            // The phase walk runs first, on the context's stream, then all segments are painted.  (Tried, r02ay: the walk in
+            // up to four pieces on a second stream, each piece's segments painted while the next piece walks.  Correct, but
+            // 1.45 -> 2.2 ms in two pieces and 3.0 ms in four for SineOsc at 4096 voices: a walker is one warp per SM that lives on
+            // latency, and with eight paint CTAs beside it on the SM and the paint's traffic in front of its loads it crawls.)
             const bool v4 = a.V % 4 == 0 && ((uintptr_t)a.in0 & 15u) == 0;
             auto pk = k_paint_prefix_ring<M>;
             constexpr size_t ring_bytes = kRingRows * 32 * sizeof(float);
@@ -299,19 +319,10 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
             }
             uint32_t ahead = kRingAhead;
             if (const char* e = getenv("ZCU_RING_AHEAD")) ahead = (uint32_t)std::max(0, atoi(e));  // tuning
-            pk<<<(a.V + 31) / 32, kRingThreads, ring_bytes, ctx->stream>>>(a, p.seg_frames, p.nseg, v4 ? 1u : 0u, ahead);
-        } else {
-            k_paint_prefix<M><<<(a.V + 127) / 128, 128, 0, ctx->stream>>>(a, p.seg_frames, p.nseg);
+            pk<<<(a.V + 31) / 32, kRingThreads, ring_bytes, ctx->stream>>>(a, p.seg_frames, 0u, p.nseg - 1, v4 ? 1u : 0u, ahead);
+            ctx->launches++;
+            ZCU_CUDA(ctx, cudaGetLastError());
         }
-        ctx->launches++;
-        ZCU_CUDA(ctx, cudaGetLastError());
-    }
-    // ZCU_OUT_OVERWRITE: `zero; paint` in one call (modules that overwrite anyway have a single form)
-    const bool ovr = ctx->paint_output == ZCU_OUT_OVERWRITE && !WriteOnlyOf<M>::value;
-    auto kern = ovr ? k_paint_lockstep<M, true> : k_paint_lockstep<M, false>;
-    if (!ctx->attr_done.count((const void*)kern)) {  // the attribute is per device: tracked per context
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
-        ctx->attr_done.insert((const void*)kern);
     }
     kern<<<dim3(p.grid_x, p.nseg), 32 * kPaintWarps, p.smem, ctx->stream>>>(a, p.T, p.seg_frames, p.vec4, p.stages);
     ctx->launches++;

@@ -197,15 +197,17 @@ constexpr uint32_t kRingProducers = 8; // producer warps (two per scheduler: the
 constexpr uint32_t kRingThreads = 32 * (1 + kRingProducers);  // warp 0 walks
 
 template <class M>
-__global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a, uint32_t seg_frames, uint32_t nseg, uint32_t vec4, uint32_t ahead) {
+__global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a, uint32_t seg_frames, uint32_t row_lo, uint32_t row_hi, uint32_t vec4, uint32_t ahead) {
     extern __shared__ __align__(16) float ring[];  // [kRingRows][32]
     constexpr uint32_t G = kRingGroup, NG = kRingRows / kRingGroup;
     const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
     const uint32_t v0 = blockIdx.x * 32u, v = v0 + lane;
     const bool valid = v < a.V;
     const size_t V = a.V;
-    const uint32_t f_stop = (nseg - 1) * seg_frames;  // the state at the last segment start is the last one anybody needs
-    const int ngroups = (int)((f_stop + G - 1) / G);
+    // this launch walks the frames [row_lo, row_hi) x seg_frames and records the rows row_lo + 1 .. row_hi (row s = the state at
+    // the start of segment s; row_lo > 0: the walk starts from row row_lo, which an earlier launch recorded)
+    const uint32_t f_lo = row_lo * seg_frames, f_stop = row_hi * seg_frames;
+    const int ngroups = (int)((f_stop - f_lo + G - 1) / G);
     const uint32_t ring_u32 = (uint32_t)__cvta_generic_to_shared(ring);
     const bool producer = warp != 0;
     constexpr uint32_t P = kRingProducers;
@@ -217,12 +219,12 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
     const uint32_t rstep = vec4 ? 4u * P : P;                      // rows between two copies of a thread
     const size_t src_rstep = (size_t)V * 4u * rstep, src_gstep = (size_t)V * 4u * G;
     const uint32_t dst_rstep = rstep * 128u;
-    const char* iss_src = reinterpret_cast<const char*>(a.in0 + ((size_t)rsub * V + v0 + chunk));
+    const char* iss_src = reinterpret_cast<const char*>(a.in0 + ((size_t)(f_lo + rsub) * V + v0 + chunk));
     // L2 prefetch, one 32-byte sector per producer thread (a prefetch brings in the sector it names, not the 128-byte line)
     const uint32_t pf_row = pt >> 2, pf_col = (pt & 3u) * 8u;
     const bool pf_ok = pf_row < G && v0 + pf_col < a.V;
-    const char* iss_pf = reinterpret_cast<const char*>(a.in0 + ((size_t)(ahead + pf_row) * V + v0 + pf_col));
-    uint32_t iss_slot = 0, iss_f0 = 0;
+    const char* iss_pf = reinterpret_cast<const char*>(a.in0 + ((size_t)(f_lo + ahead + pf_row) * V + v0 + pf_col));
+    uint32_t iss_slot = 0, iss_f0 = f_lo;
     auto issue = [&]() {
         if (iss_f0 < f_stop) {
             const uint32_t n = min(G, f_stop - iss_f0);
@@ -260,8 +262,12 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
 
     M m = M();
     uint32_t k = 0, ke = 0;
+    PaintArgs row = a;
     if (valid) {
-        if (!producer) m.load(a, v);
+        if (!producer) {
+            if (row_lo > 0) row.state = (char*)a.prefix + (size_t)row_lo * a.V * a.prefix_stride;
+            m.load(row, v);
+        }
         k = a.off[v];
         ke = a.off[v + 1];
     }
@@ -276,10 +282,10 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
         nxt = kNoSpan;
         if (k + 1 < ke) nxt = *reinterpret_cast<const uint4*>(a.spans + k + 1);
     };
-    // walker state
-    bool active = false;
-    PaintArgs row = a;
-    uint32_t s = 1, next_b = seg_frames;
+    // walker state (a launch that starts inside the block: behind the spans that ended, inside the one that straddles)
+    while (cur.y <= f_lo) next_span();
+    bool active = !producer && cur.x < f_lo;
+    uint32_t s = row_lo + 1, next_b = f_lo + seg_frames;
     auto record = [&]() {
         row.state = (char*)a.prefix + (size_t)s * a.V * a.prefix_stride;
         if (valid) m.store(row, v);
@@ -299,7 +305,7 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
             issue();  // group i + NG - 1
             const int g = i + 1;
             if (g < ngroups) {
-                const uint32_t f0 = (uint32_t)g * G, n = min(G, f_stop - f0);
+                const uint32_t f0 = f_lo + (uint32_t)g * G, n = min(G, f_stop - f0);
                 float* gp0 = ring + (size_t)prep_slot * G * 32u + lane;
                 prep_slot = prep_slot + 1 == NG ? 0u : prep_slot + 1;
 #pragma unroll 1
@@ -336,7 +342,7 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
                 }
             }
         } else if (i >= 0) {
-            const uint32_t f0 = (uint32_t)i * G, n = min(G, f_stop - f0);
+            const uint32_t f0 = f_lo + (uint32_t)i * G, n = min(G, f_stop - f0);
             const float* gp = ring + (size_t)walk_slot * G * 32u + lane;
             walk_slot = walk_slot + 1 == NG ? 0u : walk_slot + 1;
             uint32_t j = 0;
@@ -384,7 +390,7 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
     }
     if (producer) return;
     if (active && cur.y == f_stop) m.end_span(a);
-    while (s < nseg) record();
+    while (s <= row_hi) record();
 }
 
 // cp.async.wait_group takes an immediate: dispatch the ring depths in use
@@ -651,7 +657,7 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     constexpr uint32_t W = kPaintWarps, RV = 32 * W;  // S = tiles in the cp.async ring (3..8: deeper when few CTAs share an SM)
     const uint32_t tid = threadIdx.x;
     // (voice block, segment) of this CTA: blockIdx, or — in launches whose segments wait for each other — a ticket
-    uint32_t bx = blockIdx.x, by = blockIdx.y;
+    uint32_t bx = blockIdx.x, by = blockIdx.y + a.seg_base;
     if (a.ticket != nullptr) {
         __shared__ uint32_t s_ticket;
         if (tid == 0) s_ticket = atomicAdd(a.ticket, 1u) - a.ticket_base;
