@@ -102,7 +102,9 @@ ZCU_HD uint32_t accum_core(float& t, float step, uint32_t n, bool& finished) {
                 }
             }
         }
-        if (!jump) {
+        // no jump: one real add.  After a jump the next add usually leaves the binade: it is done here as a real add too
+        // (a real add is always right), so that a binade costs one trip round this loop instead of two
+        if (!jump || (!ONE && done < n)) {
             t = ea_add(t, step);
             done++;
             if (STOP && t >= 1.0f) {
