@@ -229,7 +229,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
         const bool line_ok = !LineRingOf<M>::value || a.delay_samples >= kWalkGroup * kWalkGroups + 64u;
         uint32_t max_ctas = 4 * sms;
         if (const char* e = getenv("ZCU_PAINT_WALK_MAX_CTAS")) max_ctas = (uint32_t)std::max(1, atoi(e));  // tuning
-        if (one_segment && !WriteOnlyOf<M>::value && !ovr_now && ctas <= max_ctas && line_ok && a.frames > 0 && !getenv("ZCU_PAINT_NO_WALK")) {
+        if (one_segment && !WriteOnlyOf<M>::value && ctas <= max_ctas && line_ok && a.frames > 0 && !getenv("ZCU_PAINT_NO_WALK")) {
             a.line_ring = LineRingOf<M>::value ? 1u : 0u;
             a.chain = nullptr;
             a.prefix = nullptr;
@@ -239,7 +239,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
             const size_t group = (size_t)(nb_tiles + (a.line_ring ? 1 : 0)) * kWalkGroup * rw * sizeof(float);
             const uint32_t per_sm = std::min(4u, (ctas + sms - 1) / sms);
             const uint32_t ng = (size_t)kWalkGroups * group * per_sm <= (size_t)kPaintMaxSmem ? kWalkGroups : kWalkGroups / 2;
-            auto wk = k_paint_walk<M>;
+            auto wk = ovr_now ? k_paint_walk<M, true> : k_paint_walk<M, false>;
             if (!ctx->attr_done.count((const void*)wk)) {
                 ZCU_CUDA(ctx, cudaFuncSetAttribute(wk, cudaFuncAttributeMaxDynamicSharedMemorySize, kPaintMaxSmem));
                 ctx->attr_done.insert((const void*)wk);

@@ -418,7 +418,9 @@ constexpr uint32_t kWalkGroup = 32;    // frames per group
 constexpr uint32_t kWalkGroups = 8;    // groups in the ring, at most
 constexpr uint32_t kWalkThreads = 128;
 
-template <class M>
+// OVR (ZCU_OUT_OVERWRITE): `zero(span, out); paint(span, out)`: inside its spans the output starts from 0 (the tile is still
+// staged: frames outside the spans go back unchanged)
+template <class M, bool OVR = false>
 __global__ void __launch_bounds__(kWalkThreads) k_paint_walk(PaintArgs a, uint32_t vec4, uint32_t RW, uint32_t NG) {
     extern __shared__ __align__(16) float smem[];
     // RW = voices of this CTA (32, 16 or 8: rows of RW floats, lanes >= RW idle), NG = groups in the ring
@@ -612,7 +614,7 @@ __global__ void __launch_bounds__(kWalkThreads) k_paint_walk(PaintArgs a, uint32
                         for (int q = 0; q < 4; q++) {
                             // (an input that is absent aliases the output tile: its value is read but no module variant
                             // that can run without the buffer looks at it)
-                            acc[q] = so[(r + q) * RW];
+                            acc[q] = OVR ? 0.0f : so[(r + q) * RW];
                             x0[q] = M::NIN >= 1 ? s0[(r + q) * RW] : 0.0f;
                             x1[q] = M::NIN >= 2 ? s1[(r + q) * RW] : 0.0f;
                             x2[q] = M::NIN >= 3 ? s2[(r + q) * RW] : 0.0f;
@@ -622,7 +624,7 @@ __global__ void __launch_bounds__(kWalkThreads) k_paint_walk(PaintArgs a, uint32
                         for (int q = 0; q < 4; q++) so[(r + q) * RW] = acc[q];
                     }
                     for (; r < run; r++) {
-                        float acc = so[r * RW];
+                        float acc = OVR ? 0.0f : so[r * RW];
                         m.sample(acc, i_in0 >= 0 ? s0[r * RW] : 0.0f, i_in1 >= 0 ? s1[r * RW] : 0.0f, i_in2 >= 0 ? s2[r * RW] : 0.0f);
                         so[r * RW] = acc;
                     }
