@@ -129,6 +129,13 @@ struct LineRingCall<M, true> {
     static __device__ __forceinline__ uint32_t index(M& m) { return m.delay_line().index; }
 };
 
+// M::RESETS: a call with ZCU_SPAN_NOTE_ID_CHANGED for which m.resets(a, param) holds sets the module's whole carried state,
+// whatever it was before (see the skip-ahead of k_paint_lockstep)
+template <class M, class = void>
+struct ResetsOf { static constexpr bool value = false; };
+template <class M>
+struct ResetsOf<M, std::void_t<decltype(M::RESETS)>> { static constexpr bool value = M::RESETS; };
+
 // m.advance_done() for modules whose advance() only accumulates (M::LAZY)
 template <class M, class = void>
 struct LazyCall { static __device__ __forceinline__ void done(M&) {} };
@@ -1130,6 +1137,23 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
             }
         }
     } else if (M::SKIP && f_begin > 0) {
+        if constexpr (ResetsOf<M>::value) {
+            // A module whose whole state is reset by a call with a new note id (Sampler: t = 0) need not be walked through
+            // anything before the last such call ahead of the segment: the span headers are scanned (no module work) and the
+            // walk starts there.  Every lane then does its one walk from a fresh note in the same trip of the loop below,
+            // instead of the warp paying such a walk at nearly every span because some lane's note starts there.
+            uint32_t kr = k;
+            for (uint32_t kk = k; kk < ke; kk++) {
+                const uint4 sp = *reinterpret_cast<const uint4*>(a.spans + kk);
+                if (sp.x >= f_begin) break;
+                if ((sp.z & ZCU_SPAN_NOTE_ID_CHANGED) && m.resets(a, sp.w)) kr = kk;
+            }
+            if (kr != k) {
+                k = kr;
+                const uint4 sp = *reinterpret_cast<const uint4*>(a.spans + k);
+                s_start = sp.x; s_end = sp.y; s_flags = sp.z; s_param = sp.w;
+            }
+        }
         // spans that end before the segment: state only
         while (s_end <= f_begin) {
             m.begin_span(a, s_param, s_flags, s_end - s_start);
