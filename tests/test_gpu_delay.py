@@ -89,6 +89,47 @@ def test_simple_delay_both_forms(ctx, D, NB, parallel, monkeypatch):
     _run_blocks(ctx, L.MOD_SIMPLE_DELAY, V, NB, D, lambda: random_spans(rng, V, NB, BF, 4, max_cuts=2, p_empty=0.2, p_gap=0.3), rng)
 
 
+@pytest.mark.parametrize("kind,D,par", [(L.MOD_SIMPLE_DELAY, 400, "0"), (L.MOD_SIMPLE_DELAY, 400, "1"), (L.MOD_SIMPLE_DELAY, 9, "1"),
+                                        (L.MOD_FILTERED_ECHOES, 400, "0"), (L.MOD_FILTERED_ECHOES, 9, "0")],
+                         ids=["delay-seq", "delay-par", "delay-par-short", "echoes", "echoes-short"])
+def test_delay_overwrite_mode(ctx, kind, D, par, monkeypatch):
+    """ZCU_OUT_OVERWRITE through every form of the delay modules (walker kernel, time-parallel SimpleDelay, in-place reads for
+    short lines): one call = `zang.zero(span, out); module.paint(span, {out}, ...)`; frames outside the spans keep their garbage."""
+    monkeypatch.setenv("ZCU_DELAY_PARALLEL", par)
+    V, NB = 150, 10
+    frames = NB * BF
+    rng = np.random.default_rng(900 + D + int(par))
+    mod = (E.SimpleDelay if kind == L.MOD_SIMPLE_DELAY else E.FilteredEchoes)(ctx, V, D)
+    ostate = np.zeros(V, dtype=L.state_dtypes[kind])
+    oline = np.zeros((D, V), dtype=np.float32)
+    params = np.zeros(4, dtype=L.param_dtypes[kind])
+    if kind == L.MOD_FILTERED_ECHOES:
+        params["feedback_volume"] = rng.uniform(0.3, 0.9, 4)
+        params["cutoff"] = rng.uniform(0.05, 0.8, 4)
+    ctx.set_paint_output(L.OUT_OVERWRITE)
+    try:
+        for block in range(2):
+            off, spans = random_spans(rng, V, NB, BF, 4, max_cuts=2, p_empty=0.15, p_gap=0.3)
+            out0 = rng.uniform(-1, 1, size=(frames, V)).astype(np.float32)
+            x = rng.uniform(-1, 1, size=(frames, V)).astype(np.float32)
+            want = out0.copy()
+            oracle.basic(0, off, spans, want)  # zero(span, out)
+            oracle.paint_delay(kind, off, spans, params, ostate, oline, want, x)
+            d_out, d_x = ctx.buf(frames, V, out0), ctx.buf(frames, V, x)
+            sp = ctx.spans(V, frames, off, spans)
+            if kind == L.MOD_SIMPLE_DELAY:
+                mod.paint(sp, [d_out], [], d_x)
+            else:
+                mod.paint(sp, [d_out], [], params, d_x)
+            assert_bit_exact(d_out.download(), want, f"block {block}")
+            assert state_equal(mod.bank.get_state(), ostate)
+            assert_bit_exact(mod.bank.get_delay_line(), oline, f"delay line after block {block}")
+            for b in (d_out, d_x, sp):
+                b.free()
+    finally:
+        ctx.set_paint_output(L.OUT_ACCUMULATE)
+
+
 def test_delay_line_checkpoint_resume(ctx):
     V, NB, D = 64, 4, 700
     rng = np.random.default_rng(4)
