@@ -383,6 +383,65 @@ def test_graph_filter_with_constant_coefficients_in_time_segments(ctx):
     assert np.abs(results[1][2] - results[0][2]).max() <= 1e-5, "carried Filter state"
 
 
+def test_graph_decimator_replay_and_filter_warmup_together(ctx):
+    """PulseOsc -> Decimator (held value re-latched in a replay window) -> Filter (constant coefficients: warm-up window from its
+    rows) -> x Envelope: the silent window before a segment serves both, and is the longer of the two.  Tolerance mode, forced
+    and GPU-sized segments, against one segment in exact mode: 1e-5; PulseOsc / Decimator / Envelope states bit-equal."""
+    sr, V, total = 48000.0, 70, 24 * 1024 + 77
+    wl = synth.polyphony_bank(V, total, sr, seed=8, mean_on=0.1, mean_off=0.04)
+    from zang_b200.events import BankTrigger
+    off, spans = BankTrigger(wl["event_off"], wl["events"], total, 1024).spans(0, total)
+    ev = wl["events"]
+    pp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_PULSE_OSC])
+    pp["sample_rate"], pp["freq"], pp["color"] = sr, ev["freq"], 0.4
+    dp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_DECIMATOR])
+    dp["sample_rate"], dp["fake_sample_rate"] = sr, 3000.0 + 500.0 * (np.arange(ev.size) % 7)
+    fp = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_FILTER])
+    fp["type"], fp["cutoff"], fp["res"] = L.FILTER_LOW_PASS, 0.15 + 0.05 * (np.arange(ev.size) % 5), 0.5
+    ep = np.zeros(ev.size, dtype=L.param_dtypes[L.MOD_ENVELOPE])
+    ep["sample_rate"], ep["attack"], ep["decay"], ep["release"] = sr, (L.CURVE_CUBED, 0.01), (L.CURVE_SQUARED, 0.08), (L.CURVE_LINEAR, 0.2)
+    ep["sustain_volume"], ep["note_on"] = 0.6, ev["note_on"]
+    results = []
+    for mode, segments in ((L.PAINT_EXACT, 0), (L.PAINT_TOLERANCE, 6), (L.PAINT_TOLERANCE, 0)):
+        b = E.GraphBuilder()
+        b.zero(E.T(0))
+        f_osc = b.call(L.MOD_PULSE_OSC, E.T(0))
+        b.zero(E.T(1))
+        f_dec = b.call(L.MOD_DECIMATOR, E.T(1), (E.T(0),))
+        b.zero(E.T(2))
+        f_flt = b.call(L.MOD_FILTER, E.T(2), (E.T(1),))
+        b.zero(E.T(0))
+        f_env = b.call(L.MOD_ENVELOPE, E.T(0))
+        b.multiply(E.OUT(0), E.T(2), E.T(0))
+        g = E.Graph(ctx, E.graph_config(V, b, 3), b)
+        osc, dec, flt, env = E.PulseOsc(ctx, V), E.Decimator(ctx, V), E.Filter(ctx, V), E.Envelope(ctx, V)
+        for f, m, rows in ((f_osc, osc, pp), (f_dec, dec, dp), (f_flt, flt, fp), (f_env, env, ep)):
+            g.set_field(f, m.bank, rows)
+        g.set_segments(segments)
+        out = ctx.buf(total, V)
+        ctx.zero(None, out)
+        sp = ctx.spans(V, total, off, spans)
+        ctx.set_paint_mode(mode)
+        try:
+            g.paint([sp], [out])
+            info = g.segment_info()
+            retries = g.warm_retries()
+        finally:
+            ctx.set_paint_mode(L.PAINT_EXACT)
+        assert info["failed"] == 0 and retries == 0, (info, retries)
+        assert (info["segments"] > 1) == (mode == L.PAINT_TOLERANCE), info
+        if mode == L.PAINT_TOLERANCE:
+            assert info["replay_frames"] >= int(np.ceil(sr / 3000.0)) + 2, info
+        results.append((out.download(), osc.bank.get_state().tobytes() + dec.bank.get_state().tobytes() + env.bank.get_state().tobytes(),
+                        flt.bank.get_state().view(np.float32).copy()))
+        g.free()
+    assert float(np.abs(results[0][0]).max()) > 0.1
+    for r in results[1:]:
+        assert_close(r[0], results[0][0], 1e-5, "Decimator + Filter graph in time segments vs one segment")
+        assert r[1] == results[0][1], "carried PulseOsc / Decimator / Envelope state"
+        assert np.abs(r[2] - results[0][2]).max() <= 1e-5, "carried Filter state"
+
+
 @pytest.mark.parametrize("segments,warm", [(0, None), (5, None), (7, "48")], ids=["planned", "5seg", "7seg-short-window"])
 def test_sfx_graph_filter_time_segments(ctx, segments, warm, monkeypatch):
     """A graph with a Filter in time segments (ZCU_PAINT_TOLERANCE): a segment skips the exact modules ahead to a window before
