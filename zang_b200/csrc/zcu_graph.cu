@@ -398,6 +398,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     // granularity of four frames instead of a whole span.  Every temp is a register quad; modules with a four-sample form
     // (sample4: branch-free sines, exact divisions and PCM taps arranged so that the four evaluations overlap) use it.  The
     // operands of the four frames are loaded before the first instruction, the results stored after the last.
+    const bool pipelined = (c.voices + 31u) / 32u < 2u * 592u && !getenv("ZCU_GRAPH_NO_PIPELINE");
     auto body4 = [&](const char* ind) {
         std::string s;
         auto arr = [&](const zcu_graph_ref& r) -> std::string {
@@ -412,16 +413,31 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         };
         auto elem = [&](const zcu_graph_ref& r) -> std::string { return r.kind == ZCU_GREF_NONE ? std::string("0.0f") : arr(r) + "[q]"; };
         appendf(s, "%sconst float z4_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n%s(void)z4_;\n", ind, ind);
+        // Small banks (fewer than about two warps per scheduler): external operands are software-pipelined one batch deep: this batch takes what the previous one loaded (xn / on), and
+        // the loads of the next batch are issued before this batch's arithmetic (a bank that puts one warp on a scheduler has
+        // nothing else to hide the HBM latency behind; ncu on the FmDetuned graph: 2.5 long-scoreboard stalls per issue)
+        // (large banks have the warps to hide it and keep the registers: plain loads)
         for (uint32_t i = 0; i < c.num_inputs; i++)
-            if (in_used[i]) {
+            if (in_used[i] && !pipelined)
                 appendf(s, "%sfloat x%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) x%u_[q] = __ldg(g.in[%u] + base + (size_t)(r + q) * g.V);\n", ind, i,
                         ind, i, i);
+        for (uint32_t o = 0; o < c.num_outputs; o++)
+            if (!mix && !pipelined)
+                appendf(s, "%sfloat o%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) o%u_[q] = g.out[%u][base + (size_t)(r + q) * g.V];\n", ind, o, ind, o, o);
+        for (uint32_t i = 0; i < c.num_inputs; i++)
+            if (in_used[i] && pipelined) {
+                appendf(s, "%sfloat x%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) x%u_[q] = xn%u_[q];\n", ind, i, ind, i, i);
+                appendf(s, "%sif (r + 8 <= run) {\n#pragma unroll\n%s    for (int q = 0; q < 4; q++) xn%u_[q] = __ldg(g.in[%u] + base + (size_t)(r + 4 + q) * g.V);\n%s}\n",
+                        ind, ind, i, i, ind);
             }
         for (uint32_t o = 0; o < c.num_outputs; o++) {
-            if (mix)
+            if (mix) {
                 appendf(s, "%sfloat o%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n", ind, o);
-            else
-                appendf(s, "%sfloat o%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) o%u_[q] = g.out[%u][base + (size_t)(r + q) * g.V];\n", ind, o, ind, o, o);
+            } else if (pipelined) {
+                appendf(s, "%sfloat o%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) o%u_[q] = on%u_[q];\n", ind, o, ind, o, o);
+                appendf(s, "%sif (r + 8 <= run) {\n#pragma unroll\n%s    for (int q = 0; q < 4; q++) on%u_[q] = g.out[%u][base + (size_t)(r + 4 + q) * g.V];\n%s}\n",
+                        ind, ind, o, o, ind);
+            }
         }
         for (uint32_t t = 0; t < c.num_temps; t++) appendf(s, "%sfloat t%u_[4] = {t%u, t%u, t%u, t%u};\n", ind, t, t, t, t, t);
         for (uint32_t i = 0; i < n; i++) {
@@ -656,6 +672,17 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     bool has_delay = false;  // a delay line is read and written slot by slot: no four-sample batches
     for (uint32_t f = 0; f < c.num_fields; f++) has_delay = has_delay || fields[f].is_delay;
     src += "            uint32_t r = 0;\n";
+    {  // the first batch's external operands (a graph with a delay line has no batches: the arrays only have to exist)
+        const char* first = (has_delay || !pipelined) ? "false" : "run >= 4";
+        for (uint32_t i = 0; i < c.num_inputs; i++)
+            if (in_used[i])
+                appendf(src, "            float xn%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n            if (%s) {\n#pragma unroll\n                for (int q = 0; q < 4; q++) xn%u_[q] = "
+                             "__ldg(g.in[%u] + base + (size_t)q * g.V);\n            }\n", i, first, i, i);
+        if (!mix)
+            for (uint32_t o = 0; o < c.num_outputs; o++)
+                appendf(src, "            float on%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n            if (%s) {\n#pragma unroll\n                for (int q = 0; q < 4; q++) on%u_[q] = "
+                             "g.out[%u][base + (size_t)q * g.V];\n            }\n", o, first, o, o);
+    }
     src += has_delay ? "            for (; false;) {\n" : "            for (; r + 4 <= run; r += 4) {\n";
     {
         std::string pf;
