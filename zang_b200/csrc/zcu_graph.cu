@@ -573,6 +573,20 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         src += warm_any ? "    const uint32_t F_play = F_begin > W ? F_begin - W : 0u;\n" : "    const uint32_t F_play = F_begin > g.replay ? F_begin - g.replay : 0u;\n";
         src += "    if (F_play > 0 && valid) {\n";
         for (uint32_t k = 0; k < K; k++) {
+            // a table whose modules are all reset by a call with a new note id (the Sampler: t = 0) is walked from the voice's
+            // last such call before the segment only (zcu_paint_kernel.cuh, M::RESETS): the span headers are scanned first
+            bool resets = false, others = false;
+            for (uint32_t f = 0; f < c.num_fields; f++)
+                if (fields[f].table == k) (fields[f].kind == ZCU_MOD_SAMPLER ? resets : others) = true;
+            if (resets && !others) {
+                appendf(src, "        {\n            uint32_t kr = c%u.k;\n            for (uint32_t kk = c%u.k; kk < c%u.ke; kk++) {\n"
+                             "                const uint4 sp = *reinterpret_cast<const uint4*>(g.tab[%u].spans + kk);\n"
+                             "                if (sp.x >= F_play) break;\n                if ((sp.z & ZCU_SPAN_NOTE_ID_CHANGED)", k, k, k, k);
+                for (uint32_t f = 0; f < c.num_fields; f++)
+                    if (fields[f].table == k) appendf(src, " && m%u.resets(g.pa[%u], sp.w)", f, f);
+                appendf(src, ") kr = kk;\n            }\n            if (kr != c%u.k) {\n                c%u.k = kr;\n                c%u.fetch(g.tab[%u]);\n            }\n        }\n",
+                        k, k, k, k);
+            }
             appendf(src, "        while (c%u.s_end <= F_play) {\n", k);
             for (uint32_t f = 0; f < c.num_fields; f++)
                 if (fields[f].table == k)
