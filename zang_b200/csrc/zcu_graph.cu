@@ -428,7 +428,7 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         for (uint32_t i = 0; i < c.num_inputs; i++)
             if (in_used[i] && pipelined) {
                 appendf(s, "%sfloat x%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) x%u_[q] = xn%u_[q];\n", ind, i, ind, i, i);
-                appendf(s, "%sif (r + 8 <= run) {\n#pragma unroll\n%s    for (int q = 0; q < 4; q++) xn%u_[q] = __ldg(g.in[%u] + base + (size_t)(r + 4 + q) * g.V);\n%s}\n",
+                appendf(s, "%sif (f + r + 8 <= g.frames) {\n#pragma unroll\n%s    for (int q = 0; q < 4; q++) xn%u_[q] = __ldg(g.in[%u] + base + (size_t)(r + 4 + q) * g.V);\n%s}\n",
                         ind, ind, i, i, ind);
             }
         for (uint32_t o = 0; o < c.num_outputs; o++) {
@@ -436,10 +436,11 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
                 appendf(s, "%sfloat o%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n", ind, o);
             } else if (pipelined) {
                 appendf(s, "%sfloat o%u_[4];\n#pragma unroll\n%sfor (int q = 0; q < 4; q++) o%u_[q] = on%u_[q];\n", ind, o, ind, o, o);
-                appendf(s, "%sif (r + 8 <= run) {\n#pragma unroll\n%s    for (int q = 0; q < 4; q++) on%u_[q] = g.out[%u][base + (size_t)(r + 4 + q) * g.V];\n%s}\n",
+                appendf(s, "%sif (f + r + 8 <= g.frames) {\n#pragma unroll\n%s    for (int q = 0; q < 4; q++) on%u_[q] = g.out[%u][base + (size_t)(r + 4 + q) * g.V];\n%s}\n",
                         ind, ind, o, o, ind);
             }
         }
+        if (pipelined) appendf(s, "%sxn_f = f + r + 8 <= g.frames ? f + r + 4 : 0xFFFFFFFFu;\n", ind);
         for (uint32_t t = 0; t < c.num_temps; t++) appendf(s, "%sfloat t%u_[4] = {t%u, t%u, t%u, t%u};\n", ind, t, t, t, t, t);
         for (uint32_t i = 0; i < n; i++) {
             const zcu_graph_instr& x = ins[i];
@@ -618,6 +619,13 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     }
     if (mix) src += "    uint32_t j = 0, T0 = F_begin;\n";
     src += "    uint32_t f = F_play;\n";
+    {  // external operands loaded ahead of their batch (body4): they outlive a run, so that the next run can start on them
+        for (uint32_t i = 0; i < c.num_inputs; i++)
+            if (in_used[i]) appendf(src, "    float xn%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n", i);
+        if (!mix)
+            for (uint32_t o = 0; o < c.num_outputs; o++) appendf(src, "    float on%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n", o);
+        src += "    uint32_t xn_f = 0xFFFFFFFFu;  // the frame whose four rows xn / on hold\n    (void)xn_f;\n";
+    }
     src += "    while (f < F_end) {\n";
     if (warm_any) {
         src += "        if (f == F_begin && F_play > 0) {  // every Filter must have forgotten the start of its warm-up window\n            bool ok = true;\n";
@@ -691,15 +699,15 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
     for (uint32_t f = 0; f < c.num_fields; f++) has_delay = has_delay || fields[f].is_delay;
     src += "            uint32_t r = 0;\n";
     {  // the first batch's external operands (a graph with a delay line has no batches: the arrays only have to exist)
-        const char* first = (has_delay || !pipelined) ? "false" : "run >= 4";
+        const char* first = (has_delay || !pipelined) ? "false" : "run >= 4 && xn_f != f";
         for (uint32_t i = 0; i < c.num_inputs; i++)
             if (in_used[i])
-                appendf(src, "            float xn%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n            if (%s) {\n#pragma unroll\n                for (int q = 0; q < 4; q++) xn%u_[q] = "
-                             "__ldg(g.in[%u] + base + (size_t)q * g.V);\n            }\n", i, first, i, i);
+                appendf(src, "            if (%s) {\n#pragma unroll\n                for (int q = 0; q < 4; q++) xn%u_[q] = "
+                             "__ldg(g.in[%u] + base + (size_t)q * g.V);\n            }\n", first, i, i);
         if (!mix)
             for (uint32_t o = 0; o < c.num_outputs; o++)
-                appendf(src, "            float on%u_[4] = {0.0f, 0.0f, 0.0f, 0.0f};\n            if (%s) {\n#pragma unroll\n                for (int q = 0; q < 4; q++) on%u_[q] = "
-                             "g.out[%u][base + (size_t)q * g.V];\n            }\n", o, first, o, o);
+                appendf(src, "            if (%s) {\n#pragma unroll\n                for (int q = 0; q < 4; q++) on%u_[q] = "
+                             "g.out[%u][base + (size_t)q * g.V];\n            }\n", first, o, o);
     }
     src += has_delay ? "            for (; false;) {\n" : "            for (; r + 4 <= run; r += 4) {\n";
     {
