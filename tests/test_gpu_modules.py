@@ -357,3 +357,75 @@ def test_buffer_frequency_phase_relay(ctx, case, nseg, Vn, monkeypatch):
         assert state_equal(mod.bank.get_state(), ostate), f"{name}: carried phase differs after block {block}"
         for b in [d_out, sp] + [x for x in d_in if x is not None]:
             b.free()
+
+
+def _xoshiro_prev(s):
+    """state before the last xoshiro256++ step (python ints; the device form is XoshiroDev::prev)"""
+    M = (1 << 64) - 1
+    rotl = lambda x, k: ((x << k) | (x >> (64 - k))) & M
+    s0, s1, s2, s3 = s
+    s3a = rotl(s3, 19)
+    c = s1 ^ s2
+    s1o = (c ^ (c << 17) ^ (c << 34) ^ (c << 51)) & M
+    s2a = s2 ^ ((s1o << 17) & M)
+    s0o = s0 ^ s3a
+    return [s0o, s1o, s2a ^ s0o, s3a ^ s1o]
+
+
+def _xoshiro_next(s):
+    M = (1 << 64) - 1
+    rotl = lambda x, k: ((x << k) | (x >> (64 - k))) & M
+    s0, s1, s2, s3 = s
+    r = (rotl((s0 + s3) & M, 23) + s0) & M
+    t = (s1 << 17) & M
+    s2 ^= s0
+    s3 ^= s1
+    s1 ^= s2
+    s0 ^= s3
+    s2 ^= t
+    s3 = rotl(s3, 45)
+    return r, [s0, s1, s2, s3]
+
+
+@pytest.mark.parametrize("color", [L.NOISE_WHITE, L.NOISE_PINK], ids=["white", "pink"])
+def test_noise_draws_with_an_empty_upper_word(ctx, color, monkeypatch):
+    """Random.float's rare branches (Noise.zig:51 -> std.rand float): a draw whose upper 32 bits are zero (lz in 32..40: no
+    refill), a draw below 2^23 (one more draw) and two zero draws in a row (a third draw).  The four-sample form of the
+    kernels tests a whole batch for them at once and, when one is there, steps the generator back and takes the batch one
+    sample at a time: states are built backwards from such a draw so that it falls on every position of a batch."""
+    monkeypatch.setenv("ZCU_PAINT_SEGMENTS", "1")  # the skip-ahead of later segments assumes one draw per sample
+    rng = np.random.default_rng(77)
+    targets = []
+    for variant in range(3):
+        for back in range(10):
+            s1, s2 = (int(x) for x in rng.integers(1, 1 << 63, size=2, dtype=np.uint64))
+            tgt = [[0, s1, s2, 5 + back], [0, s1, s2, 0], [0, 0, s2, 0]][variant]
+            r, _ = _xoshiro_next(tgt)
+            assert (r >> 32) == 0 and (variant == 0) == (r >= 1 << 23)
+            s = tgt
+            for _ in range(back):
+                s = _xoshiro_prev(s)
+            chk = s
+            for _ in range(back):
+                _, chk = _xoshiro_next(chk)
+            assert chk == tgt
+            targets.append(s)
+    Vn, frames = len(targets) + 3, 96
+    mod = E.Noise(ctx, Vn, first_seed=5)
+    ostate = oracle.state_init(L.MOD_NOISE, Vn, first_seed=5)
+    for v, s in enumerate(targets):
+        ostate["s"][v] = np.array(s, dtype=np.uint64)
+    mod.bank.set_state(ostate)
+    params = np.array([(color,)], dtype=L.param_dtypes[L.MOD_NOISE])
+    off = np.arange(Vn + 1, dtype=np.uint32)
+    spans = np.array([(v % 3, frames - (v % 5), 0, 0) for v in range(Vn)], dtype=L.span_dtype)
+    out0 = rng.uniform(-1, 1, size=(frames, Vn)).astype(np.float32)
+    want = out0.copy()
+    oracle.paint(L.MOD_NOISE, off, spans, params, ostate, want)
+    d_out = ctx.buf(frames, Vn, out0)
+    sp = ctx.spans(Vn, frames, off, spans)
+    mod.paint(sp, [d_out], [], params)
+    assert_bit_exact(d_out.download(), want, "noise with refills")
+    assert state_equal(mod.bank.get_state(), ostate)
+    d_out.free()
+    sp.free()
