@@ -687,6 +687,37 @@ def main():
                 others[m] = {"ms_per_step": sum(ms_o) / len(ms_o), "value": voice_samples / (sum(ms_o) / len(ms_o) * 1e-3), "steps": 3,
                              "render_mode": MODE_INFO[m][2]}
                 r2.free()
+            if args.mode == "segments":
+                # opt-in variant of the benched mode: the Filter recurrence with FMAs (zcu_render_set_filter_contraction).  Not the
+                # reference's bits in the Filter any more; the probe below compares it with the benched (strict) render on voice
+                # windows at the segment starts of the whole job, whose own distance to the oracle is `parity`.
+                r2 = Render(ctx, V, total_frames, wl["color"], wl["gains"], channels=2, sample_rate=SAMPLE_RATE, buffer_frames=BUFFER_FRAMES,
+                            mode=L.RENDER_SEGMENTS)
+                r2.set_events(off_host, ev_host)
+                r2.set_filter_contraction(True)
+
+                def step_contracted():
+                    mix_t.zero_()
+                    r2.run(mix)
+                step_contracted()
+                ms_o = timed(step_contracted, 3)
+                probe_err, probe_n = 0.0, 0
+                nwin = 2048
+                for first in (0, total_frames // 3, total_frames - nwin):
+                    for v0 in (0, V // 2, V - 32):
+                        wa, wb = ctx.buf(nwin, 32), ctx.buf(nwin, 32)
+                        r.run_voice_window(v0, first, wa)
+                        r2.run_voice_window(v0, first, wb)
+                        probe_err = max(probe_err, float(np.abs(wa.download().astype(np.float64) - wb.download()).max()))
+                        probe_n += nwin * 32
+                        wa.free()
+                        wb.free()
+                others["segments_contracted_filter"] = {
+                    "ms_per_step": sum(ms_o) / len(ms_o), "value": voice_samples / (sum(ms_o) / len(ms_o) * 1e-3), "steps": 3,
+                    "render_mode": "segments with zcu_render_set_filter_contraction(1): the Filter's multiply-add pairs as FMAs (10 instead of "
+                                   "16 instructions per sample); opt-in, Filter output within the mode's 1e-5 but not bit-exact anywhere",
+                    "max_abs_diff_vs_benched_render": probe_err, "voice_samples_probed": probe_n}
+                r2.free()
             line["other_modes"] = others
             # The same bank through the DROP-IN module path: the reference's paint body call by call (zero, PulseOsc,
             # multiplyWithScalar, zero, Filter, zero, Envelope, multiply = 8 C-ABI calls per block over all voices,

@@ -548,6 +548,12 @@ int zcu_render_aux_kernel_ms(zcu_ctx*, zcu_render*, float* total_ms, uint32_t* l
 int zcu_render_set_segments(zcu_render*, uint32_t segments_per_launch);
 int zcu_render_segment_info(zcu_ctx*, zcu_render*, uint32_t* segments, uint32_t* buffers_per_segment, uint32_t* warm_sum,
                             uint32_t* warm_max);
+/* ZCU_RENDER_SEGMENTS, opt-in (default off): evaluate the Filter recurrence (Filter.zig:135-146) with each multiply-add
+ * pair as one FMA: 10 instructions per sample instead of 16 in a kernel that is bound by instruction issue.  The Filter's
+ * output then no longer has the reference's bits anywhere (each FMA skips one rounding; the recurrence is contractive, the
+ * difference stays at a few 1e-7 of full scale, inside the 1e-5 this mode promises for the Filter); PulseOsc and Envelope
+ * keep their exact forms.  ZCU_ERR_INVALID for another mode. */
+int zcu_render_set_filter_contraction(zcu_render*, int enabled);
 
 /* ---- fused module graphs ---------------------------------------------------------
  * The general form of zcu_render_*: an instrument's paint() body given as an instruction list and compiled at run time

@@ -116,6 +116,42 @@ def test_segments_mode_with_one_segment_is_the_exact_render(ctx, monkeypatch):
     r.free()
 
 
+@pytest.mark.parametrize("nseg", ["1", "5"])
+def test_segments_mode_with_contracted_filter(ctx, monkeypatch, nseg):
+    """zcu_render_set_filter_contraction: the Filter recurrence with FMAs.  Per-voice output within the mode's tolerance (long
+    sustained and slowly damped notes included: the rounding differences must not pile up), measurably not the exact
+    bits any more, and the mix within its own tolerance.  Off again = the strict render.  Other modes refuse it."""
+    monkeypatch.setenv("ZCU_RENDER_SEGMENTS_PER_LAUNCH", nseg)
+    voices, total = 64, 40 * 1024
+    wl = synth.polyphony_bank(voices, total, SR, seed=91, mean_on=0.3, mean_off=0.05)
+    wl["events"]["freq"][::3] *= np.float32(0.125)  # every third event three octaves down: slow filters
+    want_mix, want, _ = oracle.render_nice(wl, total, SR, want_mix=True, window=(0, total))
+    r = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=16, mode=L.RENDER_SEGMENTS)
+    r.set_events(wl["event_off"], wl["events"])
+    vo = ctx.buf(total, voices)
+    r.run_voices(0, vo)
+    strict = vo.download()
+    r.set_filter_contraction(True)
+    r.run_voices(0, vo)
+    got = vo.download()
+    assert np.abs(want).max() > 0.1
+    assert_close(got, want, SCAN_TOL, "contracted Filter, voices")
+    err = float(np.abs(got.astype(np.float64) - want).max())
+    assert err < 2e-6, err  # a few ulp of the filter state, far inside the tolerance
+    assert (got != strict).any()
+    mix = ctx.buf(total, 2)
+    r.run(mix)
+    assert_close(mix.download(), want_mix, 1e-5 * float(np.abs(wl["gains"]).sum(axis=0).max()), "contracted Filter, mix")
+    r.set_filter_contraction(False)
+    r.run_voices(0, vo)
+    assert_bit_exact(vo.download(), strict, "contraction off again")
+    r.free()
+    r2 = E.Render(ctx, voices, total, wl["color"], wl["gains"], channels=2, sample_rate=SR, block_buffers=16, mode=L.RENDER_EXACT)
+    with pytest.raises(E.ZangCuError):
+        r2.set_filter_contraction(True)
+    r2.free()
+
+
 def test_segments_mode_warm_up_is_adaptive(ctx, monkeypatch):
     """Low notes (cutoff = 8 x freq, resonance 0.7) damp slowly: the warm-up window must grow until its homogeneous
     map is <= 1e-8, and the result must still be within tolerance."""

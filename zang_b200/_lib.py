@@ -143,6 +143,7 @@ PROTOTYPES = {
     "zcu_render_kernel_ms": (_I, [_P, _P, _P, _P]),
     "zcu_render_aux_kernel_ms": (_I, [_P, _P, _P, _P]),
     "zcu_render_set_segments": (_I, [_P, _U]),
+    "zcu_render_set_filter_contraction": (_I, [_P, C.c_int]),
     "zcu_render_segment_info": (_I, [_P, _P, _P, _P, _P, _P]),
     "zcu_graph_create": (_I, [_P, _P, _P, _U, _P, _P]),
     "zcu_graph_free": (None, [_P]),

@@ -78,6 +78,7 @@ struct zcu_render {
     uint32_t seg_slots;    // resident warps of k_nice_seg_render on this device
     uint32_t last_nseg, last_seg_chunks;
     uint32_t forced_nseg;  // zcu_render_set_segments: segments per launch (0 = as many as fill the resident warps)
+    bool filter_contraction;  // zcu_render_set_filter_contraction
     bool attr_set[3];      // cudaFuncSetAttribute done for the scan / segment / exact kernels on this render's device
 };
 
@@ -211,6 +212,17 @@ int render_blocks_scan(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& v
     return ZCU_OK;
 }
 
+typedef void (*SegKernel)(SegArgs, const float2*, float2*);
+template <int RT>
+static SegKernel seg_kernel(int channels, bool vout, bool contracted) {
+    if (contracted) {
+        if (vout) return channels == 2 ? k_nice_seg_render<2, true, RT, true> : k_nice_seg_render<1, true, RT, true>;
+        return channels == 2 ? k_nice_seg_render<2, false, RT, true> : k_nice_seg_render<1, false, RT, true>;
+    }
+    if (vout) return channels == 2 ? k_nice_seg_render<2, true, RT, false> : k_nice_seg_render<1, true, RT, false>;
+    return channels == 2 ? k_nice_seg_render<2, false, RT, false> : k_nice_seg_render<1, false, RT, false>;
+}
+
 // ZCU_RENDER_SEGMENTS: one launch per block of mix buffers; (voice groups x segments) fills the resident warps once
 int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo, uint32_t end_frame) {
     const zcu_render_config& c = r->cfg;
@@ -218,15 +230,14 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo
     const size_t smem = seg_render_smem_bytes<RT>();
     bool& attr_set = r->attr_set[1];
     if (!attr_set) {
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<1, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<2, false, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<1, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ZCU_CUDA(ctx, cudaFuncSetAttribute(k_nice_seg_render<2, true, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        for (int combo = 0; combo < 8; combo++)
+            ZCU_CUDA(ctx, cudaFuncSetAttribute(seg_kernel<RT>(1 + (combo & 1), (combo & 2) != 0, (combo & 4) != 0),
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
     if (r->seg_slots == 0) {
         int per_sm = 0;
-        ZCU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_nice_seg_render<2, false, RT>, 128, smem));
+        ZCU_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, seg_kernel<RT>(2, false, false), 128, smem));
         r->seg_slots = (uint32_t)std::max(1, per_sm) * (uint32_t)ctx->sm_count * 4u;
     }
     ZCU_CUDA(ctx, cudaMemsetAsync(r->d_carry[0], 0, (size_t)c.voices * sizeof(float2), ctx->stream));
@@ -289,21 +300,16 @@ int render_blocks_seg(zcu_ctx* ctx, zcu_render* r, float* mix, const VoutReq& vo
         const float2* cin = r->d_carry[flip];
         float2* cout = r->d_carry[flip ^ 1];
         flip ^= 1;
+        const SegKernel kern = seg_kernel<RT>((int)c.channels, vo.d != nullptr, r->filter_contraction);
         if (vo.d) {
-            if (c.channels == 2)
-                k_nice_seg_render<2, true, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
-            else
-                k_nice_seg_render<1, true, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
+            kern<<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
             ctx->launches++;
         } else {
             if (r->profiling) {
                 int rc = record_pair_begin(ctx, r->ev, r->ev_used);
                 if (rc != ZCU_OK) return rc;
             }
-            if (c.channels == 2)
-                k_nice_seg_render<2, false, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
-            else
-                k_nice_seg_render<1, false, RT><<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
+            kern<<<grid, 128, smem, ctx->stream>>>(g, cin, cout);
             if (r->profiling) {
                 ZCU_CUDA(ctx, cudaEventRecord(r->ev[r->ev_used + 1], ctx->stream));
                 r->ev_used += 2;
@@ -441,6 +447,7 @@ int zcu_render_create(zcu_ctx* ctx, const zcu_render_config* cfg, const float* v
     r->last_nseg = r->last_seg_chunks = 0;
     r->attr_set[0] = r->attr_set[1] = r->attr_set[2] = false;
     r->forced_nseg = 0;
+    r->filter_contraction = false;
     r->debug_skip_mask = 0;
     r->d_debug_cycles = nullptr;
 #ifdef ZCU_DEBUG_KNOBS  // profiling aid that produces wrong audio: only in builds that ask for it, never from a stray environment variable
@@ -776,6 +783,12 @@ uint64_t zcu_render_launches_per_run(const zcu_render* r) {
 int zcu_render_set_segments(zcu_render* r, uint32_t segments_per_launch) {
     if (!r || r->cfg.mode != ZCU_RENDER_SEGMENTS) return ZCU_ERR_INVALID;
     r->forced_nseg = segments_per_launch;
+    return ZCU_OK;
+}
+
+int zcu_render_set_filter_contraction(zcu_render* r, int enabled) {
+    if (!r || r->cfg.mode != ZCU_RENDER_SEGMENTS) return ZCU_ERR_INVALID;
+    r->filter_contraction = enabled != 0;
     return ZCU_OK;
 }
 

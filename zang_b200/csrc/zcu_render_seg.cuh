@@ -94,6 +94,7 @@ __device__ inline Mat2 window_map(const ScanArgs& a, uint32_t v, uint32_t Fw, ui
 }
 
 // PulseOsc -> Filter only over the frames [f0, f1): the warm-up (no envelope, no output)
+template <bool FF>
 __device__ __forceinline__ void seg_warm_up(const ScanArgs& a, ChunkCursor& cur, PulseStage& ps, FilterStage& fs, uint32_t f0, uint32_t f1) {
     const uint32_t FULL = 0xffffffffu;
     uint32_t f = f0;
@@ -106,15 +107,16 @@ __device__ __forceinline__ void seg_warm_up(const ScanArgs& a, ChunkCursor& cur,
         const uint32_t run = min(f1 - f, __reduce_min_sync(FULL, cur.boundary - f));
         if (__all_sync(FULL, cur.active)) {
 #pragma unroll 4
-            for (uint32_t r = 0; r < run; r++) fs.sample(ps.sample());
+            for (uint32_t r = 0; r < run; r++) fs.sample_t<FF>(ps.sample());
         } else if (cur.active) {
-            for (uint32_t r = 0; r < run; r++) fs.sample(ps.sample());
+            for (uint32_t r = 0; r < run; r++) fs.sample_t<FF>(ps.sample());
         }
         f += run;
     }
 }
 
-template <int C, bool VOUT, int RT>
+// FF: the Filter's multiply-add pairs contracted to FMAs (FilterStage::sample_t<true>; zcu_render_set_filter_contraction)
+template <int C, bool VOUT, int RT, bool FF>
 __global__ void __launch_bounds__(128, 6) k_nice_seg_render(SegArgs g, const float2* __restrict__ carry_in, float2* __restrict__ carry_out) {
     const ScanArgs& a = g.s;
     extern __shared__ float smem[];
@@ -184,7 +186,7 @@ __global__ void __launch_bounds__(128, 6) k_nice_seg_render(SegArgs g, const flo
         ps.set_cnt(cur.cur.cnt0 + (Fw - cur.cur.frame) * ps.ifreq);
         fs.begin_span(cur.cur.cutoff);
     }
-    if (Fw < Fs) seg_warm_up(a, cur, ps, fs, Fw, Fs);
+    if (Fw < Fs) seg_warm_up<FF>(a, cur, ps, fs, Fw, Fs);
 
     env_reset(es.e, a.sample_rate);
     if (cur.active) {
@@ -231,12 +233,12 @@ __global__ void __launch_bounds__(128, 6) k_nice_seg_render(SegArgs g, const flo
                 if (cubed) {
 #pragma unroll 4
                     for (uint32_t r = 0; r < run; r++) {
-                        const float y = fs.sample(ps.sample());
+                        const float y = fs.sample_t<FF>(ps.sample());
                         oo[r * OS] = es.sample_fast<true>(er, lv) * y;
                     }
                 } else {
                     for (uint32_t r = 0; r < run; r++) {
-                        const float y = fs.sample(ps.sample());
+                        const float y = fs.sample_t<FF>(ps.sample());
                         oo[r * OS] = es.sample_fast<false>(er, lv) * y;
                     }
                 }
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(128, 6) k_nice_seg_render(SegArgs g, const flo
                 for (uint32_t r = 0; r < run; r++) {
                     float o = 0.0f;
                     if (cur.active) {
-                        const float y = fs.sample(ps.sample());
+                        const float y = fs.sample_t<FF>(ps.sample());
                         o = es.sample_careful() * y;
                     }
                     oo[r * OS] = o;

@@ -693,6 +693,12 @@ class Render:
         if rc != L.OK:
             raise ZangCuError("zcu_render_set_segments: not a ZCU_RENDER_SEGMENTS render")
 
+    def set_filter_contraction(self, enabled):
+        """ZCU_RENDER_SEGMENTS, opt-in: the Filter recurrence with FMAs (faster; Filter output inside the mode's 1e-5, no longer
+        the reference's bits)."""
+        if lib.zcu_render_set_filter_contraction(self._h, 1 if enabled else 0) != L.OK:
+            raise ZangCuError("zcu_render_set_filter_contraction: not a ZCU_RENDER_SEGMENTS render")
+
     def segment_info(self):
         """ZCU_RENDER_SEGMENTS: dict(segments, buffers_per_segment, warm_sum, warm_max) of the last run."""
         v = [C.c_uint32() for _ in range(4)]
