@@ -133,3 +133,40 @@ def test_phase_walk_edge_shapes(ctx, kind, V, frames, nseg, monkeypatch):
         assert state_equal(mod.bank.get_state(), ostate), f"carried state after block {block}"
         for b in (d_out, d_f, sp):
             b.free()
+
+
+@pytest.mark.parametrize("kind", [L.MOD_PULSE_OSC, L.MOD_DECIMATOR], ids=["pulse-freq-buffer", "decimator"])
+def test_second_pass_modules_on_a_large_bank(ctx, kind):
+    """Banks with >= 2.5 CTAs per SM from their voices alone: modules whose time segments cost a second pass over an input
+    (chained integer scan of PulseOsc's frequency buffer, Decimator's prefix walk) are painted in one segment there
+    (zcu_paint.cu: launch).  Two calls, state carried; bit-exact."""
+    import cases
+    V, frames = 49152 + 96, 600
+    rng = np.random.default_rng(kind * 7 + 3)
+    mod = E.MODULE_CLASSES[kind](ctx, V)
+    ostate = oracle.state_init(kind, V)
+    params = cases.make_params(kind, rng, 4, "ctrl")
+    for block in range(2):
+        # two spans per voice with a gap between them (vectorised: the generic generator loops over voices in Python)
+        cuts = np.sort(rng.integers(0, frames - 2, size=(V, 4)), axis=1) + np.arange(4)  # strictly increasing: no empty span
+        spans = np.zeros(2 * V, dtype=L.span_dtype)
+        spans["start"] = cuts[:, [0, 2]].reshape(-1)
+        spans["end"] = cuts[:, [1, 3]].reshape(-1)
+        spans["flags"] = rng.integers(0, 2, size=2 * V)
+        spans["param"] = rng.integers(0, 4, size=2 * V)
+        off = (2 * np.arange(V + 1)).astype(np.uint32)
+        out0 = rng.uniform(-1, 1, size=(frames, V)).astype(np.float32)
+        lo, hi = (-200.0, 6500.0) if kind == L.MOD_PULSE_OSC else (-1.0, 1.0)
+        x = rng.uniform(lo, hi, size=(frames, V)).astype(np.float32)
+        want = out0.copy()
+        oracle.paint(kind, off, spans, params, ostate, want, x, None, None)
+        d_out, d_x = ctx.buf(frames, V, out0), ctx.buf(frames, V, x)
+        sp = ctx.spans(V, frames, off, spans)
+        if kind == L.MOD_PULSE_OSC:
+            mod.paint(sp, [d_out], [], params, freq=d_x)
+        else:
+            mod.paint(sp, [d_out], [], params, d_x)
+        assert_bit_exact(d_out.download(), want, f"block {block}")
+        assert state_equal(mod.bank.get_state(), ostate), f"carried state after block {block}"
+        for b in (d_out, d_x, sp):
+            b.free()

@@ -202,7 +202,7 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     }
     // tolerance-mode segments pay a warm-up window each: half as many, twice as long (measured best at 4 CTAs per SM)
     // exact chained prefix sum (M::SCAN): no aliasing either, the scan pass reads inputs while earlier segments paint
-    const bool scan = ScanOf<M>::value && !getenv("ZCU_PAINT_NO_SCAN") && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
+    bool scan = ScanOf<M>::value && !getenv("ZCU_PAINT_NO_SCAN") && !overlaps(a.out, a.in0, n) && !overlaps(a.out, a.in1, n) &&
                       !overlaps(a.out, a.in2, n);
     uint32_t warm_resident = 4;
     if (const char* e = getenv("ZCU_PAINT_WARM_RESIDENT")) warm_resident = (uint32_t)std::min(8, std::max(1, atoi(e)));  // tuning
@@ -213,6 +213,16 @@ int launch(zcu_ctx* ctx, PaintArgs a, int kind) {
     if (ring && p.nseg < 12 && !getenv("ZCU_PAINT_SEGMENTS")) {  // measured: the walk pays off up to ~12000 voices (8192: 1.19 against 2.2 ms; 16384: 1.24 against 1.16)
         ring = false;
         p = zcu_paint_plan(ctx, a, nb, skip || warm || scan, 8u);
+    }
+    // Segments that cost a second pass over an input (the chained scan of M::SCAN reads its segment twice, a PREFIX module is
+    // walked once more by k_paint_prefix) stop paying once the voices alone put ~2.5 CTAs on every SM.  Measured, 16384 frames,
+    // segments / one segment: PulseOsc with a frequency buffer 32768 voices 2.22 / 2.13 ms, 49152 voices 3.26 / 2.68 ms,
+    // 65536 x 8192: 2.16 / 1.67 ms; Decimator 1.40 / 1.71, 2.05 / 1.85, 1.33 / 1.23 ms.
+    if ((scan || (PrefixOf<M>::value && !PrefixRingOf<M>::value)) && !warm && p.nseg > 1 && p.grid_x * 2u >= 5u * (uint32_t)ctx->sm_count &&
+        !getenv("ZCU_PAINT_SEGMENTS")) {
+        scan = false;
+        skip = false;
+        p = zcu_paint_plan(ctx, a, nb, false, 8u);
     }
     // A module that has to walk its frames in order, on a bank too small to fill the machine with 128-voice CTAs: the walker /
     // producer kernel (k_paint_walk).  One walker warp per CTA, so the bank is cut into as many CTAs as the SMs' four
