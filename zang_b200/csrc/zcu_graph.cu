@@ -560,7 +560,10 @@ bool codegen(const zcu_graph_config& c, const zcu_graph_instr* ins, uint32_t n, 
         src += "    uint32_t W = g.replay;\nretry:;\n";
     }
     for (uint32_t k = 0; k < K; k++) appendf(src, "    SpanCursor c%u;\n    c%u.init(g.tab[%u], v, valid);\n", k, k, k);
-    for (uint32_t f = 0; f < c.num_fields; f++) appendf(src, "    %s m%u;\n", fields[f].type.c_str(), f);
+    for (uint32_t f = 0; f < c.num_fields; f++) {
+        appendf(src, "    %s m%u;\n", fields[f].type.c_str(), f);
+        appendf(src, "    ScratchOf<decltype(m%u)>::type s%u_;\n    ScratchOf<decltype(m%u)>::bind(m%u, s%u_);\n", f, f, f, f, f);
+    }
     src += "    if (valid) {\n";
     for (uint32_t f = 0; f < c.num_fields; f++) appendf(src, "        m%u.load(g.pa[%u], v);\n", f, f);
     src += "    }\n";

@@ -156,6 +156,8 @@ __global__ void __launch_bounds__(128) k_paint_prefix(PaintArgs a, uint32_t seg_
     const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= a.V) return;
     M m;
+    typename ScratchOf<M>::type m_scratch;  // a module's run-time indexed table, kept apart so that m itself stays in registers
+    ScratchOf<M>::bind(m, m_scratch);
     m.load(a, v);
     PaintArgs row = a;
     uint32_t s = 1;
@@ -268,6 +270,8 @@ __global__ void __launch_bounds__(kRingThreads) k_paint_prefix_ring(PaintArgs a,
     }
 
     M m = M();
+    typename ScratchOf<M>::type m_scratch;
+    ScratchOf<M>::bind(m, m_scratch);
     uint32_t k = 0, ke = 0;
     PaintArgs row = a;
     if (valid) {
@@ -562,6 +566,8 @@ __global__ void __launch_bounds__(kWalkThreads) k_paint_walk(PaintArgs a, uint32
 
     // ---- walker --------------------------------------------------------------------------------------------------------
     M m;
+    typename ScratchOf<M>::type m_scratch;  // a module's run-time indexed table, kept apart so that m itself stays in registers
+    ScratchOf<M>::bind(m, m_scratch);
     uint32_t k = 0, ke = 0;
     uint32_t s_start = 0xFFFFFFFFu, s_end = 0xFFFFFFFFu, s_flags = 0, s_param = 0;
     uint4 nxt = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);  // the span after the one under the cursor, already fetched
@@ -722,6 +728,8 @@ __global__ void __launch_bounds__(32 * kPaintWarps) k_paint_lockstep(PaintArgs a
     const bool c_valid = v0 + c < a.V;
 
     M m;
+    typename ScratchOf<M>::type m_scratch;  // a module's run-time indexed table, kept apart so that m itself stays in registers
+    ScratchOf<M>::bind(m, m_scratch);
     // delay modules: the line prefetch queue behind the tile ring, [S * T][RV]
     const bool line_ring = LineRingOf<M>::value && a.line_ring != 0u;
     const uint32_t lq_len = S * T;
