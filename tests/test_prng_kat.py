@@ -92,3 +92,88 @@ def test_jump_matrices_equal_plain_stepping():
         assert np.array_equal(jumped, s), n
     bad = np.zeros(4, dtype=np.uint64)
     assert lib.zcu_xoshiro_jump_host(L.ptr(bad), 1 << 24) != 0  # beyond the table
+
+
+M64 = (1 << 64) - 1
+
+
+def _rotl(x, k):
+    return ((x << k) | (x >> (64 - k))) & M64
+
+
+def py_next(s):
+    s0, s1, s2, s3 = s
+    r = (_rotl((s0 + s3) & M64, 23) + s0) & M64
+    t = (s1 << 17) & M64
+    s2 ^= s0
+    s3 ^= s1
+    s1 ^= s2
+    s0 ^= s3
+    s2 ^= t
+    s3 = _rotl(s3, 45)
+    return r, [s0, s1, s2, s3]
+
+
+def py_prev(s):
+    """the state before the last step: the form XoshiroDev::prev uses on the device (zcu_modules.cuh) when a batch of four
+    draws has to be taken again one sample at a time"""
+    s0, s1, s2, s3 = s
+    s3a = _rotl(s3, 19)
+    c = s1 ^ s2
+    s1o = (c ^ (c << 17) ^ (c << 34) ^ (c << 51)) & M64
+    s2a = s2 ^ ((s1o << 17) & M64)
+    s0o = s0 ^ s3a
+    return [s0o, s1o, s2a ^ s0o, s3a ^ s1o]
+
+
+def test_xoshiro_step_and_its_inverse():
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        s = [int(x) for x in rng.integers(0, 1 << 63, size=4, dtype=np.uint64)]
+        arr = np.array(s, dtype=np.uint64)
+        out = np.zeros(3, dtype=np.uint64)
+        oracle.orc.orc_xoshiro_next(ptr(arr), ptr(out), 3)
+        st, draws = s, []
+        for _ in range(3):
+            r, st = py_next(st)
+            draws.append(r)
+        assert draws == [int(x) for x in out] and st == [int(x) for x in arr]
+        for _ in range(3):
+            st = py_prev(st)
+        assert st == s
+
+
+def py_float_full(state):
+    """Random.float(f32) with its refill branches; returns (bits, state after, draws taken)"""
+    clz = lambda x, w: w - x.bit_length()
+    r, state = py_next(state)
+    lz, taken = clz(r, 64), 1
+    if lz >= 41:
+        r2, state = py_next(state)
+        lz, taken = 41 + clz(r2, 64), 2
+        if lz == 41 + 64:
+            r3, state = py_next(state)
+            lz += clz((r3 & 0xFFFFFFFF) | 0x7FF, 32)
+            taken = 3
+    return ((126 - lz) << 23) | (r & 0x7FFFFF), state, taken
+
+
+def test_float_refill_branches():
+    """Draws the float conversion refills on: an empty upper word without a refill (lz 32..40), a draw below 2^23 (one more
+    draw decides the exponent) and two zero draws in a row (a third draw).  States are built so that the first draw is such a
+    value; the oracle's conversion must take as many draws as the restatement and give its bits."""
+    rng = np.random.default_rng(6)
+    seen = set()
+    for variant in range(3):
+        for _ in range(5):
+            s1, s2 = (int(x) for x in rng.integers(1, 1 << 63, size=2, dtype=np.uint64))
+            s = [[0, s1, s2, 3 + int(rng.integers(0, 500))], [0, s1, s2, 0], [0, 0, s2, 0]][variant]
+            bits, after, taken = py_float_full(s)
+            seen.add(taken)
+            arr = np.array(s, dtype=np.uint64)
+            fl = np.zeros(1, dtype=np.float32)
+            oracle.orc.orc_xoshiro_floats(ptr(arr), ptr(fl), 1)
+            assert int(fl.view(np.uint32)[0]) == bits, (variant, hex(bits))
+            assert [int(x) for x in arr] == after, (variant, taken)
+            assert 0.0 <= float(fl[0]) < 1.0
+    assert seen == {1, 2, 3}
