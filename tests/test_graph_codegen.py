@@ -75,3 +75,28 @@ def test_delay_block_instructions_are_checked():
 
 def test_struct_sizes_match_the_header():
     assert C.sizeof(L.GraphRef) == 8 and C.sizeof(L.GraphInstr) == 56 and C.sizeof(L.GraphConfig) == 32
+
+
+def test_curve_graph_keeps_only_the_node_list_in_local_memory(tmp_path, monkeypatch):
+    """A module object that holds a run-time indexed array lives in local memory as a whole (measured on Curve: every
+    `pos == sub_end` a local load).  CurveMod's node list is therefore declared beside the module (ScratchOf<M>,
+    zcu_modules.cuh); the compiled graph's stack frame must be the list (32 nodes x 8 bytes) and nothing else."""
+    import re
+    import shutil
+    import subprocess
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not on PATH")
+    monkeypatch.setenv("ZCU_GRAPH_DUMP", str(tmp_path))
+    b = E.GraphBuilder()
+    b.zero(E.T(0))
+    b.call(L.MOD_CURVE, E.T(0), ())
+    b.addInto(E.OUT(0), E.T(0))
+    cfg = E.graph_config(4096, b, 1)
+    rc, log, n = E.graph_compile_check(cfg, b)
+    assert rc == L.OK, log
+    src = (tmp_path / "zcu_graph_kernel.cu").read_text()
+    assert "ScratchOf<decltype(m0)>::bind(m0, s0_)" in src
+    res = subprocess.run(["cuobjdump", "-res-usage", str(tmp_path / "zcu_graph_kernel.cubin")], capture_output=True, text=True).stdout
+    m = re.search(r"STACK:(\d+)", res)
+    assert m, res
+    assert int(m.group(1)) <= 256 + 32, res
